@@ -1,0 +1,196 @@
+"""MeshManager: gmsh 2.2 ASCII reader, element connectivity, BC table, partitioning.
+
+Host-side mirror of the reference class (same method names, same array
+conventions) -- /root/reference/include/MeshManager.hpp:74-215,
+/root/reference/src/MeshManager.cpp:130-544.  Output tables:
+
+  EToV, EToE, EToF, BCType : int32 [K*Nf], flattened row-major [K][Nf]
+  Vert                     : float64 [Nv*3]  (x,y,z per vertex)
+
+Local face f joins local vertices (f, (f+1) mod Nf) (MeshManager.cpp:386-393);
+boundary faces self-reference in EToE/EToF (:473-479) and carry BCTag.Wall in
+BCType (:315-329).  Connectivity is found by sorting faces on their vertex
+pair -- O(n log n) instead of the reference's sparse VToF^T*VToF product
+(:398-427), same result on conforming meshes.
+"""
+import numpy as np
+
+from .bctypes import BCTag
+
+
+class MeshManager:
+    def __init__(self):
+        self.Dim = 3
+        self.NumVerts = 0
+        self.NumFaces = 3
+        self.NumElements = 0
+        self.Vert = None
+        self.EToV = None
+        self.EToE = None
+        self.EToF = None
+        self.BCType = None
+        self.ElementPartitionMap = None
+        self.VertexPartitionMap = None
+
+    # ------------------------------------------------------------------ readers
+    def readMesh(self, gmshInputFile):
+        """Parse a gmsh 2.x ASCII .msh file (MeshManager.cpp:130-313)."""
+        with open(gmshInputFile, "r") as fh:
+            lines = [ln.strip() for ln in fh]
+        pos = 0
+        if lines[pos] != "$MeshFormat":
+            raise RuntimeError("Missing $MeshFormat header in .msh file!")
+        vers, fileType, floatSize = lines[pos + 1].split()[:3]
+        if float(vers) < 2.0 or float(vers) >= 3.0:
+            raise RuntimeError("Unsupported Gmsh version. Only 2.x is currently supported.")
+        if int(fileType) != 0:
+            raise RuntimeError("Only ASCII-type Gmsh formats are supported.")
+        if int(floatSize) != 8:
+            raise RuntimeError("Only 8-byte reals in Gmsh files are supported!")
+        pos += 3  # header, version line, $EndMeshFormat
+        if lines[pos] != "$Nodes":
+            raise RuntimeError("Unexpected line marker in .msh file! Expected '$Nodes' but was:" + lines[pos] + ".")
+        nv = int(lines[pos + 1])
+        pos += 2
+        vert = np.zeros((nv, 3))
+        for i in range(nv):
+            tok = lines[pos + i].split()
+            vert[i] = [float(tok[1]), float(tok[2]), float(tok[3])]
+        pos += nv
+        if lines[pos] != "$EndNodes":
+            raise RuntimeError("Unexpected line marker in .msh file! Expected '$EndNodes' but was:" + lines[pos] + ".")
+        if lines[pos + 1] != "$Elements":
+            raise RuntimeError("Unexpected line marker in .msh file! Expected '$Elements' but was:" + lines[pos + 1] + ".")
+        nrows = int(lines[pos + 2])
+        pos += 3
+        tris, quads = [], []
+        for i in range(nrows):
+            tok = [int(t) for t in lines[pos + i].split()]
+            elemType, numTags = tok[1], tok[2]
+            nloc = len(tok) - numTags - 3
+            verts = tok[3 + numTags:]
+            if nloc == 1 and elemType != 15:
+                raise RuntimeError("Incorrect Element Type for point element!")
+            if nloc == 2 and elemType != 1:
+                raise RuntimeError("Incorrect Element Type for line element!")
+            if nloc == 3:
+                if elemType != 2:
+                    raise RuntimeError("Incorrect Element Type for triangle element!")
+                tris.append(verts)
+            if nloc == 4:
+                if elemType != 3:
+                    raise RuntimeError("Incorrect Element Type for quadrangle element!")
+                quads.append(verts)
+        etov = np.array(quads if quads else tris, dtype=np.int64) - 1  # 1-based -> 0-based
+        self._finish(etov, vert)
+
+    def buildMesh(self, EToV, Vert):
+        """Build from arrays [K][Nf] and [Nv][dim] (MeshManager.cpp:74-121)."""
+        vert = np.asarray(Vert, dtype=np.float64)
+        if vert.shape[1] == 2:
+            vert = np.concatenate([vert, np.zeros((vert.shape[0], 1))], axis=1)
+        self._finish(np.asarray(EToV).astype(np.int64), vert)
+
+    def _finish(self, etov, vert):
+        K, Nf = etov.shape
+        self.NumFaces = Nf
+        self.NumElements = K
+        self.NumVerts = vert.shape[0]
+        # CCW enforcement looks at the first three vertices only and swaps 1<->2 (:292-306)
+        a, b, c = vert[etov[:, 0]], vert[etov[:, 1]], vert[etov[:, 2]]
+        det = (a[:, 0] - c[:, 0]) * (b[:, 1] - c[:, 1]) - (b[:, 0] - c[:, 0]) * (a[:, 1] - c[:, 1])
+        flip = det < 0
+        etov = etov.copy()
+        if Nf == 3:
+            etov[flip, 1], etov[flip, 2] = etov[flip, 2].copy(), etov[flip, 1].copy()
+        else:
+            # DEVIATION (documented in DESIGN.md): the reference swaps entries 1<->2 for quads too,
+            # which turns a clockwise quad into a bow-tie; reversing the orientation (1<->3) is the
+            # repair that keeps the element valid.  CCW input (the only input the reference handles
+            # correctly) is untouched by either rule.
+            etov[flip, 1], etov[flip, 3] = etov[flip, 3].copy(), etov[flip, 1].copy()
+        self.Vert = np.ascontiguousarray(vert.reshape(-1))
+        self.EToV = np.ascontiguousarray(etov.reshape(-1).astype(np.int32))
+        self.buildConnectivity()
+        self.buildBCTable(BCTag.Wall)
+
+    # ------------------------------------------------------------ connectivity
+    def buildConnectivity(self):
+        K, Nf = self.NumElements, self.NumFaces
+        etov = self.EToV.reshape(K, Nf).astype(np.int64)
+        v0 = etov.reshape(-1)
+        v1 = np.roll(etov, -1, axis=1).reshape(-1)
+        lo, hi = np.minimum(v0, v1), np.maximum(v0, v1)
+        key = lo * (self.NumVerts + 1) + hi
+        order = np.argsort(key, kind="stable")
+        ks = key[order]
+        same = ks[1:] == ks[:-1]
+        fa, fb = order[:-1][same], order[1:][same]
+        e2e = np.repeat(np.arange(K, dtype=np.int64), Nf)
+        e2f = np.tile(np.arange(Nf, dtype=np.int64), K)
+        e2e[fa], e2f[fa] = fb // Nf, fb % Nf
+        e2e[fb], e2f[fb] = fa // Nf, fa % Nf
+        self.EToE = e2e.astype(np.int32)
+        self.EToF = e2f.astype(np.int32)
+
+    def buildBCTable(self, tagNumber):
+        K, Nf = self.NumElements, self.NumFaces
+        own = np.repeat(np.arange(K, dtype=np.int32), Nf)
+        self.BCType = np.where(self.EToE == own, np.int32(tagNumber), np.int32(0)).astype(np.int32)
+
+    def set_BCType(self, bcType):
+        self.BCType = np.ascontiguousarray(np.asarray(bcType, dtype=np.int32).reshape(-1))
+
+    # -------------------------------------------------------------- partitions
+    def partitionMesh(self, numPartitions, method="auto"):
+        """Element -> rank map (reference: METIS_PartMeshNodal k-way, MeshManager.cpp:491-544).
+
+        metis.h / a callable METIS are absent from this image, so the map is
+        produced by recursive coordinate bisection of element centroids
+        (contiguous, balanced parts); the output contract is the reference's:
+        ElementPartitionMap[k] in [0,P), VertexPartitionMap[v] in [0,P).
+        """
+        from .partition import rcb_partition
+
+        K, Nf = self.NumElements, self.NumFaces
+        etov = self.EToV.reshape(K, Nf)
+        vert = self.Vert.reshape(-1, 3)
+        cx = vert[etov, 0].mean(axis=1)
+        cy = vert[etov, 1].mean(axis=1)
+        epart = rcb_partition(cx, cy, numPartitions)
+        vpart = np.zeros(self.NumVerts, dtype=np.int32)
+        vpart[etov.reshape(-1)] = np.repeat(epart, Nf)
+        self.ElementPartitionMap = epart.astype(np.int32)
+        self.VertexPartitionMap = vpart
+        return self.ElementPartitionMap
+
+    # ----------------------------------------------------------------- getters
+    def get_NumElements(self):
+        return self.NumElements
+
+    def get_NumVerts(self):
+        return self.NumVerts
+
+    def get_NumFaces(self):
+        return self.NumFaces
+
+    def get_Elements(self):
+        return self.EToV
+
+    def get_Vertices(self):
+        return self.Vert
+
+    def get_EToE(self):
+        return self.EToE
+
+    def get_EToF(self):
+        return self.EToF
+
+    def get_BCType(self):
+        return self.BCType
+
+    def get_ElementPartitionMap(self):
+        return self.ElementPartitionMap
+
+    def get_VertexPartitionMap(self):
+        return self.VertexPartitionMap
