@@ -1,0 +1,142 @@
+/* blitzdg_b200 -- C ABI of the B200-native sw2d nodal-DG RHS + LSERK4 hot path.
+ *
+ * The reference (WQCG/blitzdg) has no FFI seam around this path: the RHS is a
+ * free function in a driver translation unit,
+ *     void sw2d::computeRHS(fields, const numParams&, const physParams&,
+ *                           const DGContext2D&, real_type t)
+ *                                     (reference src/sw2d/SW2d.hpp:53, src/sw2d/main.cpp:279-484;
+ *                                      simple variant src/sw2d-simple/SW2d.hpp:15, main.cpp:181-356)
+ * fed by the DGContext2D accessor bag (reference include/DGContext2D.hpp:82-196).
+ * This header is the seam a maintainer binds instead: plain
+ * C, opaque handle, int status returns, no exceptions across the boundary.
+ *
+ * Ownership: the caller keeps every host pointer; the library copies at create /
+ * set_* time and never retains host pointers.  One handle = one GPU (= one rank).
+ * Calls on one handle are not thread-safe; distinct handles are independent.
+ *
+ * Host array layouts are the reference's native ones:
+ *   volume arrays  [Np][K]  row-major, element index fastest  (blitz default storage)
+ *   face arrays    [Nfaces*Nfp][K] row-major
+ *   vmapM/vmapP    [Nfaces*Nfp*K], element-major then face then face node, values n + Np*k
+ *   BC lists       face-node indices i in [0, Nfaces*Nfp*K)       (DGContext2D::bcmap())
+ */
+#ifndef BLITZDG_B200_H
+#define BLITZDG_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct bdg_sw2d bdg_sw2d; /* opaque solver handle */
+
+/* status codes */
+#define BDG_OK 0
+#define BDG_E_INVALID 1    /* bad argument / inconsistent context                         */
+#define BDG_E_CUDA 2       /* CUDA runtime error (message in bdg_last_error)              */
+#define BDG_E_UNSTABLE 3   /* the reference's "A numerical instability has occurred!"     */
+#define BDG_E_NCCL 4       /* NCCL error                                                  */
+#define BDG_E_UNSUPPORTED 5
+
+/* Mirrors DGContext2D (reference include/DGContext2D.hpp:11-39). */
+typedef struct {
+  int32_t N, Np, Nfp, Nfaces, K;          /* order, nodes/element, nodes/face, faces/element, elements */
+  const double *Dr, *Ds;                  /* [Np][Np]                                       */
+  const double *Lift;                     /* [Np][Nfaces*Nfp]                               */
+  const double *Filt;                     /* [Np][Np] or NULL                               */
+  const double *rx, *sx, *ry, *sy;        /* [Np][K]                                        */
+  const double *nx, *ny, *Fscale;         /* [Nfaces*Nfp][K]                                */
+  const int32_t *vmapM, *vmapP;           /* [Nfaces*Nfp*K]                                 */
+  const int32_t *bc_face_nodes[9];        /* BCmap lists by BCTag 1..8 (reference include/BCtypes.hpp:7-16) */
+  int32_t bc_count[9];                    /* absent tag = count 0, never an error           */
+} bdg_dgcontext2d;
+
+/* physParams + numParams (reference src/sw2d/SW2d.hpp:15-30, src/sw2d/main.cpp:49-60,281-283). */
+typedef struct {
+  double g;            /* 9.81                                                               */
+  double CD;           /* bottom drag, 2.5e-3                                                */
+  double f;            /* Coriolis, 1.0070e-4                                                */
+  double CFL;          /* 0.25 (sw2d) / 0.65 (sw2d-simple)                                   */
+  int32_t lf_mode;     /* 0: per-face Lax-Friedrichs speed (sw2d-simple main.cpp:305-312)
+                          1: global max over all face nodes (sw2d main.cpp:413-414)          */
+  int32_t sources;     /* 1: star states + bathymetry/drag/Coriolis (sw2d main.cpp:355-368,460-483) */
+  int32_t filter;      /* 1: RHS := Filt*RHS (sw2d-simple main.cpp:134-136)                  */
+  int32_t reserved;
+  double tide_amp;     /* 3.0                       (sw2d main.cpp:283)                      */
+  double tide_period;  /* 3600*12.42                (sw2d main.cpp:281)                      */
+  double tide_ramp;    /* 0.15/3600                 (sw2d main.cpp:352)                      */
+} bdg_sw2d_params;
+
+/* Halo description of one rank of an element-partitioned mesh (the reference
+ * only computes MeshManager::partitionMesh, src/MeshManager.cpp:491-544, and never consumes it).
+ * Local vmapP entries >= Np*K address ghost slots: ghost g lives at index Np*K + g.
+ * Ghost slots are grouped by neighbour rank: recv_offset[i]..recv_offset[i+1].
+ * send_nodes[send_offset[i]..send_offset[i+1]) are LOCAL volume node ids whose values the
+ * neighbour nbr_rank[i] expects, in that neighbour's ghost order. */
+typedef struct {
+  int32_t rank, nranks;
+  int32_t n_ghost;
+  int32_t n_neighbors;
+  const int32_t *nbr_rank;     /* [n_neighbors]   */
+  const int32_t *send_offset;  /* [n_neighbors+1] */
+  const int32_t *send_nodes;   /* [send_offset[n_neighbors]] */
+  const int32_t *recv_offset;  /* [n_neighbors+1] */
+  int32_t n_interior;          /* elements [0,n_interior) touch no ghost slot (0 = unknown) */
+} bdg_halo;
+
+/* --- lifetime ---------------------------------------------------------------------------- */
+/* halo may be NULL (single GPU). device = CUDA ordinal. */
+int bdg_sw2d_create(bdg_sw2d **out, const bdg_dgcontext2d *ctx, const bdg_sw2d_params *prm,
+                    const bdg_halo *halo, int device);
+void bdg_sw2d_destroy(bdg_sw2d *s);
+const char *bdg_last_error(const bdg_sw2d *s); /* s may be NULL: error of the last failed create */
+
+/* --- state (host arrays [Np][K]) ---------------------------------------------------------- */
+/* fields H, Hx, Hy of sw2d::fields (reference src/sw2d/SW2d.hpp:32-49); NULL H => flat bottom unused */
+int bdg_sw2d_set_bathymetry(bdg_sw2d *s, const double *H, const double *Hx, const double *Hy);
+/* sets h, hu, hv and the time; zeroes the RK residuals (reference src/sw2d/main.cpp:117-119) */
+int bdg_sw2d_set_state(bdg_sw2d *s, const double *h, const double *hu, const double *hv, double t);
+int bdg_sw2d_get_state(bdg_sw2d *s, double *h, double *hu, double *hv, double *t);
+
+/* --- the hot path ------------------------------------------------------------------------- */
+/* one evaluation of sw2d::computeRHS on the current state at the current time; host out [Np][K] */
+int bdg_sw2d_rhs(bdg_sw2d *s, double *RHS1, double *RHS2, double *RHS3);
+/* sw2d::computeTimeStep (reference src/sw2d/main.cpp:253-277); global over ranks when a comm is set */
+int bdg_sw2d_timestep(bdg_sw2d *s, double *dt_out);
+/* nsteps LSERK4 steps of 5 fused RHS+stage launches, all on device (reference
+ * include/LSERK4.hpp:16-27 + src/advec1d/main.cpp:92-102).  dt <= 0: adaptive, dt recomputed on
+ * device each step.  Asynchronous: returns after enqueueing; bdg_sw2d_sync waits. */
+int bdg_sw2d_step(bdg_sw2d *s, int32_t nsteps, double dt);
+int bdg_sw2d_sync(bdg_sw2d *s);
+/* blow-up guard of the drivers (reference src/sw2d/main.cpp:238-240): max|h-H| > 1e8 or NaN
+ * => BDG_E_UNSTABLE.  eta_max may be NULL. */
+int bdg_sw2d_check(bdg_sw2d *s, double *eta_max);
+
+/* --- plumbing ----------------------------------------------------------------------------- */
+/* kernel variant used by step(): 0 = auto, 1 = generic two-kernel path, 2 = fused DMMA path */
+int bdg_sw2d_set_variant(bdg_sw2d *s, int32_t variant);
+int bdg_sw2d_get_variant(const bdg_sw2d *s);
+/* number of kernel launches enqueued by this handle since create */
+int64_t bdg_sw2d_launch_count(const bdg_sw2d *s);
+/* the CUDA stream (cudaStream_t) all work of this handle is enqueued on, for event timing */
+void *bdg_sw2d_stream(bdg_sw2d *s);
+/* algorithmic bytes of one RHS+stage over this handle's elements (B_alg) */
+double bdg_sw2d_algorithmic_bytes_per_stage(const bdg_sw2d *s);
+
+/* --- multi-GPU (one process per GPU) ------------------------------------------------------- */
+#define BDG_NCCL_ID_BYTES 128
+int bdg_nccl_unique_id(void *id_out /* BDG_NCCL_ID_BYTES */);
+/* joins the communicator; collective over all ranks of the halo description */
+int bdg_sw2d_comm_init(bdg_sw2d *s, const void *id /* BDG_NCCL_ID_BYTES */);
+/* test hook: pack this rank's send buffer to host / load ghost values from host, so the
+ * exchange can be emulated without NCCL (world_size-2 gloo tests on CPU boxes use the oracle) */
+int bdg_sw2d_halo_pack_to_host(bdg_sw2d *s, double *send_buf /* 3*n_send */);
+int bdg_sw2d_halo_set_ghosts(bdg_sw2d *s, const double *recv_buf /* 3*n_ghost */);
+
+int bdg_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BLITZDG_B200_H */

@@ -1,0 +1,92 @@
+"""TEST INFRASTRUCTURE -- ctypes access to oracle/liboracle.so (built by oracle/Makefile).
+
+Importable only from tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from blitzdg_b200.capi import bdg_dgcontext2d, bdg_sw2d_params, make_params, pack_context
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "liboracle.so")
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int32)
+_lib = None
+
+
+def build():
+    subprocess.check_call(["make", "-C", _HERE, "-s"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB):
+            build()
+        L = C.CDLL(_LIB)
+        L.oracle_sw2d_rhs.argtypes = [C.POINTER(bdg_dgcontext2d), C.POINTER(bdg_sw2d_params), _dp, _dp, _dp, _dp, _dp, _dp,
+                                      C.c_double, C.c_int, _dp, _dp, _dp, _dp]
+        L.oracle_sw2d_timestep.argtypes = [C.POINTER(bdg_dgcontext2d), C.POINTER(bdg_sw2d_params), _dp, _dp, _dp, C.c_int, _dp]
+        L.oracle_sw2d_timestep.restype = C.c_double
+        L.oracle_sw2d_step.argtypes = [C.POINTER(bdg_dgcontext2d), C.POINTER(bdg_sw2d_params), _dp, _dp, _dp, _dp, _dp, _dp,
+                                       _dp, _dp, _dp, C.c_int, C.c_double, _dp]
+        L.oracle_lserk4_stage.argtypes = [C.c_int, C.c_double, C.c_size_t, _dp, _dp, _dp]
+        L.oracle_lserk4_stage.restype = None
+        L.oracle_lserk4_coeffs.argtypes = [_dp, _dp]
+        L.oracle_full_to_vector.argtypes = [_dp, _dp, C.c_int, C.c_int]
+        L.oracle_vector_to_full.argtypes = [_dp, _dp, C.c_int, C.c_int]
+        L.oracle_apply_index_map.argtypes = [_dp, _ip, _dp, C.c_int]
+        _lib = L
+    return _lib
+
+
+def _d(a):
+    return a.ctypes.data_as(_dp) if a is not None else _dp()
+
+
+def _c(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.float64)
+
+
+class Oracle:
+    """CPU restatement bound to one DGContext2D + parameter set."""
+
+    def __init__(self, ctx, **params):
+        self.ctx = ctx
+        self.cctx, self._keep = pack_context(ctx)
+        self.prm = make_params(**params)
+        self.H = self.Hx = self.Hy = None
+
+    def set_bathymetry(self, H, Hx, Hy):
+        self.H, self.Hx, self.Hy = _c(H), _c(Hx), _c(Hy)
+
+    def rhs(self, h, hu, hv, t=0.0, ghost=None):
+        h, hu, hv = _c(h), _c(hu), _c(hv)
+        out = [np.empty_like(h) for _ in range(3)]
+        ng = 0
+        if ghost is not None:
+            ghost = _c(ghost)
+            ng = ghost.shape[1]
+        lib().oracle_sw2d_rhs(C.byref(self.cctx), C.byref(self.prm), _d(self.H), _d(self.Hx), _d(self.Hy), _d(h), _d(hu),
+                              _d(hv), t, ng, _d(ghost), _d(out[0]), _d(out[1]), _d(out[2]))
+        return out
+
+    def timestep(self, h, hu, hv, use_abs=False):
+        h, hu, hv = _c(h), _c(hu), _c(hv)
+        mx = C.c_double(0)
+        dt = lib().oracle_sw2d_timestep(C.byref(self.cctx), C.byref(self.prm), _d(h), _d(hu), _d(hv), int(use_abs), C.byref(mx))
+        return dt, mx.value
+
+    def step(self, h, hu, hv, res, nsteps, dt, t=0.0):
+        """In-place nsteps LSERK4 steps; returns the new time."""
+        tt = C.c_double(t)
+        lib().oracle_sw2d_step(C.byref(self.cctx), C.byref(self.prm), _d(self.H), _d(self.Hx), _d(self.Hy), _d(h), _d(hu), _d(hv),
+                               _d(res[0]), _d(res[1]), _d(res[2]), nsteps, dt, C.byref(tt))
+        return tt.value
+
+    @staticmethod
+    def stage(stage, dt, rhs, res, q):
+        lib().oracle_lserk4_stage(stage, dt, rhs.size, _d(rhs), _d(res), _d(q))
