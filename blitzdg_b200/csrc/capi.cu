@@ -1,0 +1,664 @@
+// C ABI of the sw2d device path (include/blitzdg_b200.h): upload once, keep all state on the GPU,
+// enqueue 5 fused RHS+stage launches per LSERK4 step, exchange face-trace halos over NCCL.
+#include <nccl.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "sw2d_common.cuh"
+
+namespace {
+
+char g_create_err[512] = "";
+
+const double rk4a[5] = {0.0, -567301805773.0 / 1357537059087.0, -2404267990393.0 / 2016746695238.0,
+                        -3550918686646.0 / 2091501179385.0, -1275806237668.0 / 842570457699.0};
+const double rk4b[5] = {1432997174477.0 / 9575080441755.0, 5161836677717.0 / 13612068292357.0,
+                        1720146321549.0 / 2090206949498.0, 3134564353537.0 / 4481467310338.0,
+                        2277821191437.0 / 14882151754819.0};  // reference include/LSERK4.hpp:17-27
+
+int fail(bdg_sw2d *s, int code, const char *fmt, ...) {
+  char *dst = s ? s->err : g_create_err;
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(dst, 512, fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define CU(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) return fail(s, BDG_E_CUDA, "%s -> %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+#define NC(call)                                                                                   \
+  do {                                                                                             \
+    ncclResult_t r_ = (call);                                                                      \
+    if (r_ != ncclSuccess) return fail(s, BDG_E_NCCL, "%s -> %s (%s:%d)", #call, ncclGetErrorString(r_), __FILE__, __LINE__); \
+  } while (0)
+
+// ---- layout conversion on the device -------------------------------------------------------------
+// in: row-major [R][K] (k fastest, the reference's blitz storage) -> out: element-major [K][R]
+__global__ void k_rowmajor_to_elem(const double *__restrict__ in, double *__restrict__ out, int R, long long K, int KB) {
+  extern __shared__ double tile[];  // [R][KB+1]
+  const long long k0 = (long long)blockIdx.x * KB;
+  const int nk = (int)min((long long)KB, K - k0);
+  for (int x = threadIdx.x; x < R * KB; x += blockDim.x) {
+    const int n = x / KB, tk = x - n * KB;
+    if (tk < nk) tile[n * (KB + 1) + tk] = in[(long long)n * K + k0 + tk];
+  }
+  __syncthreads();
+  for (int x = threadIdx.x; x < nk * R; x += blockDim.x) {
+    const int tk = x / R, n = x - tk * R;
+    out[k0 * R + x] = tile[n * (KB + 1) + tk];
+  }
+}
+__global__ void k_elem_to_rowmajor(const double *__restrict__ in, double *__restrict__ out, int R, long long K, int KB) {
+  extern __shared__ double tile[];
+  const long long k0 = (long long)blockIdx.x * KB;
+  const int nk = (int)min((long long)KB, K - k0);
+  for (int x = threadIdx.x; x < nk * R; x += blockDim.x) {
+    const int tk = x / R, n = x - tk * R;
+    tile[n * (KB + 1) + tk] = in[k0 * R + x];
+  }
+  __syncthreads();
+  for (int x = threadIdx.x; x < R * KB; x += blockDim.x) {
+    const int n = x / KB, tk = x - n * KB;
+    if (tk < nk) out[(long long)n * K + k0 + tk] = tile[n * (KB + 1) + tk];
+  }
+}
+
+int tile_kb(int R) {
+  int kb = 5800 / R - 1;
+  if (kb > 128) kb = 128;
+  if (kb < 4) kb = 4;
+  return kb;
+}
+
+struct Staging {
+  double *buf = nullptr;
+  size_t cap = 0;
+};
+Staging g_stage[16];
+
+double *staging(bdg_sw2d *s, size_t n) {
+  Staging &st = g_stage[s->device & 15];
+  if (st.cap < n) {
+    if (st.buf) cudaFree(st.buf);
+    st.buf = nullptr;
+    st.cap = 0;
+    if (cudaMalloc(&st.buf, n * sizeof(double)) != cudaSuccess) return nullptr;
+    st.cap = n;
+  }
+  return st.buf;
+}
+
+// host row-major [R][K] -> device element-major [K][R]
+int upload_transposed(bdg_sw2d *s, const double *host, double *dev, int R, long long K) {
+  double *tmp = staging(s, (size_t)R * K);
+  if (!tmp) return fail(s, BDG_E_CUDA, "staging allocation of %zu doubles failed", (size_t)R * K);
+  CU(cudaMemcpyAsync(tmp, host, sizeof(double) * (size_t)R * K, cudaMemcpyHostToDevice, s->stream));
+  const int KB = tile_kb(R);
+  k_rowmajor_to_elem<<<(unsigned)((K + KB - 1) / KB), 256, sizeof(double) * R * (KB + 1), s->stream>>>(tmp, dev, R, K, KB);
+  s->launches++;
+  CU(cudaGetLastError());
+  return BDG_OK;
+}
+int download_transposed(bdg_sw2d *s, const double *dev, double *host, int R, long long K) {
+  double *tmp = staging(s, (size_t)R * K);
+  if (!tmp) return fail(s, BDG_E_CUDA, "staging allocation failed");
+  const int KB = tile_kb(R);
+  k_elem_to_rowmajor<<<(unsigned)((K + KB - 1) / KB), 256, sizeof(double) * R * (KB + 1), s->stream>>>(dev, tmp, R, K, KB);
+  s->launches++;
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(host, tmp, sizeof(double) * (size_t)R * K, cudaMemcpyDeviceToHost, s->stream));
+  return BDG_OK;
+}
+
+template <typename T>
+int dev_alloc(bdg_sw2d *s, T **p, size_t n) {
+  CU(cudaMalloc((void **)p, sizeof(T) * (n ? n : 1)));
+  return BDG_OK;
+}
+template <typename T>
+int dev_upload(bdg_sw2d *s, T **p, const T *host, size_t n) {
+  int rc = dev_alloc(s, p, n);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(*p, host, sizeof(T) * n, cudaMemcpyHostToDevice, s->stream));
+  return BDG_OK;
+}
+
+}  // namespace
+
+// ====================================================================================== lifetime
+extern "C" int bdg_version(void) { return 100; }
+
+extern "C" const char *bdg_last_error(const bdg_sw2d *s) { return s ? s->err : g_create_err; }
+
+extern "C" void bdg_sw2d_destroy(bdg_sw2d *s) {
+  if (!s) return;
+  cudaSetDevice(s->device);
+  cudaStreamSynchronize(s->stream);
+  if (s->comm) ncclCommDestroy((ncclComm_t)s->comm);
+  fused_release(s);
+  void *ptrs[] = {s->q[0], s->q[1], s->res, s->rhs, s->sflux, s->d_Dr, s->d_Ds, s->d_Lift, s->d_Filt, s->d_rx, s->d_sx,
+                  s->d_ry, s->d_sy, s->d_nx, s->d_ny, s->d_Fscale, s->d_aff, s->d_H, s->d_Hx, s->d_Hy, s->d_vmapP,
+                  s->d_fmask, s->d_bctag, s->d_facetag, s->d_scal, s->d_send_nodes, s->d_sendbuf};
+  for (void *p : ptrs)
+    if (p) cudaFree(p);
+  free(s->h_nbr); free(s->h_send_off); free(s->h_recv_off);
+  if (s->ev_pack) cudaEventDestroy(s->ev_pack);
+  if (s->ev_recv) cudaEventDestroy(s->ev_recv);
+  if (s->comm_stream) cudaStreamDestroy(s->comm_stream);
+  if (s->stream) cudaStreamDestroy(s->stream);
+  delete s;
+}
+
+static int create_impl(bdg_sw2d *s, const bdg_dgcontext2d *c, const bdg_sw2d_params *prm, const bdg_halo *halo) {
+  const int Np = c->Np, Nfp = c->Nfp, Nf = c->Nfaces, K = c->K, Nfn = Nf * Nfp;
+  if (Np <= 0 || Nfp <= 0 || K <= 0 || (Nf != 3 && Nf != 4)) return fail(s, BDG_E_INVALID, "bad sizes Np=%d Nfp=%d Nfaces=%d K=%d", Np, Nfp, Nf, K);
+  if (Np > 1024) return fail(s, BDG_E_UNSUPPORTED, "Np=%d > 1024", Np);
+  if (!c->Dr || !c->Ds || !c->Lift || !c->rx || !c->sx || !c->ry || !c->sy || !c->nx || !c->ny || !c->Fscale || !c->vmapM || !c->vmapP)
+    return fail(s, BDG_E_INVALID, "NULL array in bdg_dgcontext2d");
+  if ((long long)Np * K + (halo ? halo->n_ghost : 0) >= (1LL << 31)) return fail(s, BDG_E_UNSUPPORTED, "Np*K exceeds int32 (reference index_type)");
+  if (prm->filter && !c->Filt) return fail(s, BDG_E_INVALID, "filter requested but Filt is NULL");
+  s->prm = *prm;
+  s->n_ghost = halo ? halo->n_ghost : 0;
+  s->nT = (size_t)Np * K;
+  s->nF = (size_t)Nfn * K;
+  const long long nTot = (long long)s->nT + s->n_ghost;
+  const long long stride = (nTot + 15) / 16 * 16;
+
+  // Fmask from vmapM of element 0, then check vmapM[k][sl] == Fmask[sl] + Np*k everywhere (reference
+  // src/TriangleNodesProvisioner.cpp:930-936): the device path derives '-' traces from Fmask alone.
+  std::vector<int32_t> fmask(Nfn);
+  for (int sl = 0; sl < Nfn; ++sl) {
+    fmask[sl] = c->vmapM[sl];
+    if (fmask[sl] < 0 || fmask[sl] >= Np) return fail(s, BDG_E_INVALID, "vmapM[%d]=%d is not a local node of element 0", sl, fmask[sl]);
+  }
+  for (long long k = 0; k < K; ++k)
+    for (int sl = 0; sl < Nfn; ++sl)
+      if (c->vmapM[k * Nfn + sl] != fmask[sl] + Np * k) return fail(s, BDG_E_INVALID, "vmapM is not Fmask + Np*k at element %lld slot %d", k, sl);
+  for (size_t i = 0; i < s->nF; ++i)
+    if (c->vmapP[i] < 0 || c->vmapP[i] >= nTot) return fail(s, BDG_E_INVALID, "vmapP[%zu]=%d out of range", i, c->vmapP[i]);
+
+  // per-face-node BC tags from the BCmap lists (reference include/DGContext2D.hpp bcmap())
+  std::vector<uint8_t> bctag(s->nF, 0), facetag((size_t)K * Nf, 0);
+  for (int tag = 1; tag < 9; ++tag)
+    for (int j = 0; j < c->bc_count[tag]; ++j) {
+      const int32_t i = c->bc_face_nodes[tag][j];
+      if (i < 0 || (size_t)i >= s->nF) return fail(s, BDG_E_INVALID, "BC list %d entry %d out of range", tag, i);
+      bctag[i] = (uint8_t)tag;
+    }
+  bool face_uniform = true;
+  for (size_t fc = 0; fc < (size_t)K * Nf; ++fc) {
+    const uint8_t t0 = bctag[fc * Nfp];
+    facetag[fc] = t0;
+    for (int j = 1; j < Nfp; ++j)
+      if (bctag[fc * Nfp + j] != t0) { facetag[fc] = 255; face_uniform = false; }
+  }
+
+  CU(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&s->comm_stream, cudaStreamNonBlocking));
+  CU(cudaEventCreateWithFlags(&s->ev_pack, cudaEventDisableTiming));
+  CU(cudaEventCreateWithFlags(&s->ev_recv, cudaEventDisableTiming));
+
+  int rc;
+  for (int b = 0; b < 2; ++b) {
+    if ((rc = dev_alloc(s, &s->q[b], (size_t)3 * stride))) return rc;
+    CU(cudaMemsetAsync(s->q[b], 0, sizeof(double) * 3 * stride, s->stream));
+  }
+  if ((rc = dev_alloc(s, &s->res, 3 * s->nT))) return rc;
+  CU(cudaMemsetAsync(s->res, 0, sizeof(double) * 3 * s->nT, s->stream));
+  if ((rc = dev_alloc(s, &s->sflux, 3 * s->nF))) return rc;
+  if ((rc = dev_alloc(s, &s->d_scal, (size_t)S_COUNT))) return rc;
+  CU(cudaMemsetAsync(s->d_scal, 0, sizeof(double) * S_COUNT, s->stream));
+  if ((rc = dev_upload(s, &s->d_Dr, c->Dr, (size_t)Np * Np))) return rc;
+  if ((rc = dev_upload(s, &s->d_Ds, c->Ds, (size_t)Np * Np))) return rc;
+  if ((rc = dev_upload(s, &s->d_Lift, c->Lift, (size_t)Np * Nfn))) return rc;
+  if (c->Filt && (rc = dev_upload(s, &s->d_Filt, c->Filt, (size_t)Np * Np))) return rc;
+  if ((rc = dev_upload(s, &s->d_vmapP, c->vmapP, s->nF))) return rc;
+  if ((rc = dev_upload(s, &s->d_fmask, fmask.data(), (size_t)Nfn))) return rc;
+  if ((rc = dev_upload(s, &s->d_bctag, bctag.data(), s->nF))) return rc;
+  if ((rc = dev_upload(s, &s->d_facetag, facetag.data(), (size_t)K * Nf))) return rc;
+  struct { double **dst; const double *src; int R; } geo[] = {
+      {&s->d_rx, c->rx, Np}, {&s->d_sx, c->sx, Np}, {&s->d_ry, c->ry, Np}, {&s->d_sy, c->sy, Np},
+      {&s->d_nx, c->nx, Nfn}, {&s->d_ny, c->ny, Nfn}, {&s->d_Fscale, c->Fscale, Nfn}};
+  for (auto &gm : geo) {
+    if ((rc = dev_alloc(s, gm.dst, (size_t)gm.R * K))) return rc;
+    if ((rc = upload_transposed(s, gm.src, *gm.dst, gm.R, K))) return rc;
+  }
+
+  // affine detection: metrics constant per element, normals / Fscale constant per face (straight-sided
+  // triangles, reference src/TriangleNodesProvisioner.cpp:807-821 stores them per node regardless)
+  s->is_affine = 0;
+  if (Nf == 3) {
+    const int W = 4 + 3 * Nf;
+    std::vector<double> aff((size_t)K * W, 0.0), lo((size_t)K), hi((size_t)K);
+    bool ok = true;
+    const double *vol[4] = {c->rx, c->sx, c->ry, c->sy};
+    double scale = 0.0;
+    for (int a = 0; a < 4 && ok; ++a) {
+      for (long long k = 0; k < K; ++k) { lo[k] = hi[k] = vol[a][k]; aff[k * W + a] = 0.0; }
+      for (int n = 0; n < Np; ++n) {
+        const double *row = vol[a] + (size_t)n * K;
+        for (long long k = 0; k < K; ++k) {
+          const double x = row[k];
+          aff[k * W + a] += x;
+          if (x < lo[k]) lo[k] = x;
+          if (x > hi[k]) hi[k] = x;
+        }
+      }
+      for (long long k = 0; k < K; ++k) { aff[k * W + a] /= Np; scale = fmax(scale, fabs(aff[k * W + a])); }
+      for (long long k = 0; k < K; ++k)
+        if (hi[k] - lo[k] > 1e-9 * scale) { ok = false; break; }
+    }
+    const double *fac[3] = {c->nx, c->ny, c->Fscale};
+    for (int a = 0; a < 3 && ok; ++a)
+      for (int f = 0; f < Nf && ok; ++f) {
+        for (long long k = 0; k < K; ++k) { lo[k] = hi[k] = fac[a][(size_t)(f * Nfp) * K + k]; }
+        for (int j = 0; j < Nfp; ++j) {
+          const double *row = fac[a] + (size_t)(f * Nfp + j) * K;
+          for (long long k = 0; k < K; ++k) {
+            const double x = row[k];
+            aff[k * W + 4 + 3 * f + a] += x;
+            if (x < lo[k]) lo[k] = x;
+            if (x > hi[k]) hi[k] = x;
+          }
+        }
+        for (long long k = 0; k < K; ++k) {
+          aff[k * W + 4 + 3 * f + a] /= Nfp;
+          if (hi[k] - lo[k] > 1e-9 * fmax(1.0, fabs(aff[k * W + 4 + 3 * f + a]))) { ok = false; break; }
+        }
+      }
+    if (ok) {
+      s->is_affine = 1;
+      if ((rc = dev_upload(s, &s->d_aff, aff.data(), aff.size()))) return rc;
+      CU(cudaStreamSynchronize(s->stream));
+    }
+  }
+
+  // halo
+  s->rank = halo ? halo->rank : 0;
+  s->nranks = halo ? halo->nranks : 1;
+  s->n_nbr = halo ? halo->n_neighbors : 0;
+  s->n_interior = (halo && halo->n_interior > 0 && halo->n_interior <= K) ? halo->n_interior : (halo && s->n_nbr > 0 ? 0 : K);
+  if (s->n_nbr > 0) {
+    const int nn = s->n_nbr;
+    s->h_nbr = (int32_t *)malloc(sizeof(int32_t) * nn);
+    s->h_send_off = (int32_t *)malloc(sizeof(int32_t) * (nn + 1));
+    s->h_recv_off = (int32_t *)malloc(sizeof(int32_t) * (nn + 1));
+    memcpy(s->h_nbr, halo->nbr_rank, sizeof(int32_t) * nn);
+    memcpy(s->h_send_off, halo->send_offset, sizeof(int32_t) * (nn + 1));
+    memcpy(s->h_recv_off, halo->recv_offset, sizeof(int32_t) * (nn + 1));
+    s->n_send = s->h_send_off[nn];
+    if (s->h_recv_off[nn] != s->n_ghost) return fail(s, BDG_E_INVALID, "recv_offset end %d != n_ghost %d", s->h_recv_off[nn], s->n_ghost);
+    std::vector<int32_t> pk((size_t)2 * s->n_send + nn + 1);
+    for (int i = 0; i < nn; ++i)
+      for (int j = s->h_send_off[i]; j < s->h_send_off[i + 1]; ++j) {
+        const int32_t m = halo->send_nodes[j];
+        if (m < 0 || (size_t)m >= s->nT) return fail(s, BDG_E_INVALID, "send_nodes[%d]=%d out of range", j, m);
+        pk[j] = m;
+        pk[s->n_send + j] = i;
+      }
+    memcpy(pk.data() + 2 * (size_t)s->n_send, s->h_send_off, sizeof(int32_t) * (nn + 1));
+    if ((rc = dev_upload(s, &s->d_send_nodes, pk.data(), pk.size()))) return rc;
+    if ((rc = dev_alloc(s, &s->d_sendbuf, (size_t)4 * s->n_send))) return rc;
+    CU(cudaStreamSynchronize(s->stream));
+  }
+
+  Sw2dView &v = s->v;
+  v.N = c->N; v.Np = Np; v.Nfp = Nfp; v.Nf = Nf; v.Nfn = Nfn; v.K = K;
+  v.full = prm->sources != 0; v.lf_global = prm->lf_mode == 1; v.use_filter = prm->filter != 0;
+  v.stride = stride;
+  v.g = prm->g; v.CD = prm->CD; v.fcor = prm->f;
+  v.tide_amp = prm->tide_amp; v.tide_period = prm->tide_period; v.tide_ramp = prm->tide_ramp;
+  v.Dr = s->d_Dr; v.Ds = s->d_Ds; v.Lift = s->d_Lift; v.Filt = s->d_Filt;
+  v.rx = s->d_rx; v.sx = s->d_sx; v.ry = s->d_ry; v.sy = s->d_sy;
+  v.nx = s->d_nx; v.ny = s->d_ny; v.Fscale = s->d_Fscale; v.aff = s->d_aff;
+  v.vmapP = s->d_vmapP; v.fmask = s->d_fmask; v.bctag = s->d_bctag; v.facetag = s->d_facetag;
+  v.H = v.Hx = v.Hy = nullptr;
+  v.scal = s->d_scal;
+
+  s->fused_ok = 0;
+  if (s->is_affine && face_uniform && !v.use_filter && fused_supported(s)) {
+    cudaError_t e = fused_prepare(s);
+    if (e != cudaSuccess) return fail(s, BDG_E_CUDA, "fused_prepare: %s", cudaGetErrorString(e));
+    s->fused_ok = 1;
+  }
+  CU(cudaStreamSynchronize(s->stream));
+  return BDG_OK;
+}
+
+extern "C" int bdg_sw2d_create(bdg_sw2d **out, const bdg_dgcontext2d *ctx, const bdg_sw2d_params *prm, const bdg_halo *halo,
+                               int device) {
+  if (!out || !ctx || !prm) return fail(nullptr, BDG_E_INVALID, "NULL argument");
+  *out = nullptr;
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) return fail(nullptr, BDG_E_CUDA, "cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+  bdg_sw2d *s = new (std::nothrow) bdg_sw2d();
+  if (!s) return fail(nullptr, BDG_E_INVALID, "out of host memory");
+  memset(s, 0, sizeof(*s));
+  s->device = device;
+  int rc = create_impl(s, ctx, prm, halo);
+  if (rc != BDG_OK) {
+    snprintf(g_create_err, sizeof(g_create_err), "%s", s->err);
+    bdg_sw2d_destroy(s);
+    return rc;
+  }
+  *out = s;
+  return BDG_OK;
+}
+
+// ========================================================================================= state
+extern "C" int bdg_sw2d_set_bathymetry(bdg_sw2d *s, const double *H, const double *Hx, const double *Hy) {
+  if (!s) return BDG_E_INVALID;
+  CU(cudaSetDevice(s->device));
+  const int Np = s->v.Np;
+  const long long K = s->v.K;
+  int rc;
+  if (!H) {
+    s->v.H = s->v.Hx = s->v.Hy = nullptr;
+    return BDG_OK;
+  }
+  if (!s->d_H) {
+    if ((rc = dev_alloc(s, &s->d_H, s->nT + s->n_ghost))) return rc;
+    if ((rc = dev_alloc(s, &s->d_Hx, s->nT))) return rc;
+    if ((rc = dev_alloc(s, &s->d_Hy, s->nT))) return rc;
+    CU(cudaMemsetAsync(s->d_H, 0, sizeof(double) * (s->nT + s->n_ghost), s->stream));
+    CU(cudaMemsetAsync(s->d_Hx, 0, sizeof(double) * s->nT, s->stream));
+    CU(cudaMemsetAsync(s->d_Hy, 0, sizeof(double) * s->nT, s->stream));
+  }
+  if ((rc = upload_transposed(s, H, s->d_H, Np, K))) return rc;
+  if (Hx && (rc = upload_transposed(s, Hx, s->d_Hx, Np, K))) return rc;
+  if (Hy && (rc = upload_transposed(s, Hy, s->d_Hy, Np, K))) return rc;
+  s->v.H = s->d_H; s->v.Hx = s->d_Hx; s->v.Hy = s->d_Hy;
+  CU(cudaStreamSynchronize(s->stream));
+  return BDG_OK;
+}
+
+extern "C" int bdg_sw2d_set_state(bdg_sw2d *s, const double *h, const double *hu, const double *hv, double t) {
+  if (!s || !h || !hu || !hv) return BDG_E_INVALID;
+  CU(cudaSetDevice(s->device));
+  double *q = s->q[s->cur];
+  const double *src[3] = {h, hu, hv};
+  for (int c = 0; c < 3; ++c) {
+    int rc = upload_transposed(s, src[c], q + c * s->v.stride, s->v.Np, s->v.K);
+    if (rc) return rc;
+  }
+  CU(cudaMemsetAsync(s->res, 0, sizeof(double) * 3 * s->nT, s->stream));  // reference src/sw2d/main.cpp:117-119
+  s->t = t;
+  CU(cudaMemcpyAsync(s->d_scal + S_T, &s->t, sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  CU(cudaStreamSynchronize(s->stream));
+  return BDG_OK;
+}
+
+extern "C" int bdg_sw2d_get_state(bdg_sw2d *s, double *h, double *hu, double *hv, double *t) {
+  if (!s) return BDG_E_INVALID;
+  CU(cudaSetDevice(s->device));
+  const double *q = s->q[s->cur];
+  double *dst[3] = {h, hu, hv};
+  for (int c = 0; c < 3; ++c)
+    if (dst[c]) {
+      int rc = download_transposed(s, q + c * s->v.stride, dst[c], s->v.Np, s->v.K);
+      if (rc) return rc;
+      CU(cudaStreamSynchronize(s->stream));  // staging buffer is reused by the next plane
+    }
+  if (t) {
+    CU(cudaMemcpyAsync(&s->t, s->d_scal + S_T, sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    *t = s->t;
+  }
+  return BDG_OK;
+}
+
+// ========================================================================================== halo
+// Per stage: pack the face traces the neighbours need (main stream) -> grouped ncclSend/ncclRecv on the
+// comm stream straight into the ghost slots of the live state buffer; the caller overlaps the interior
+// elements and waits on ev_recv before touching cut elements.
+static int halo_begin(bdg_sw2d *s, double *q) {
+  if (!s->comm || s->n_nbr == 0) return BDG_OK;
+  const int np = s->v.full ? 4 : 3;
+  cudaError_t e = launch_pack(s, q, np == 4);
+  if (e != cudaSuccess) return fail(s, BDG_E_CUDA, "pack: %s", cudaGetErrorString(e));
+  CU(cudaEventRecord(s->ev_pack, s->stream));
+  CU(cudaStreamWaitEvent(s->comm_stream, s->ev_pack, 0));
+  ncclComm_t comm = (ncclComm_t)s->comm;
+  NC(ncclGroupStart());
+  for (int i = 0; i < s->n_nbr; ++i) {
+    const int so = s->h_send_off[i], sc = s->h_send_off[i + 1] - so;
+    const int ro = s->h_recv_off[i], rcn = s->h_recv_off[i + 1] - ro;
+    for (int c = 0; c < np; ++c) {
+      if (sc > 0) NC(ncclSend(s->d_sendbuf + (size_t)np * so + (size_t)c * sc, sc, ncclDouble, s->h_nbr[i], comm, s->comm_stream));
+      double *dst = (c < 3) ? q + c * s->v.stride + s->nT + ro : s->d_H + s->nT + ro;
+      if (rcn > 0) NC(ncclRecv(dst, rcn, ncclDouble, s->h_nbr[i], comm, s->comm_stream));
+    }
+  }
+  NC(ncclGroupEnd());
+  CU(cudaEventRecord(s->ev_recv, s->comm_stream));
+  return BDG_OK;
+}
+static int halo_wait(bdg_sw2d *s) {
+  if (!s->comm || s->n_nbr == 0) return BDG_OK;
+  CU(cudaStreamWaitEvent(s->stream, s->ev_recv, 0));
+  return BDG_OK;
+}
+// max-allreduce of one device scalar across ranks (global LF speed, adaptive dt)
+static int allreduce_max(bdg_sw2d *s, double *dptr) {
+  if (!s->comm || s->nranks == 1) return BDG_OK;
+  CU(cudaEventRecord(s->ev_pack, s->stream));
+  CU(cudaStreamWaitEvent(s->comm_stream, s->ev_pack, 0));
+  NC(ncclAllReduce(dptr, dptr, 1, ncclDouble, ncclMax, (ncclComm_t)s->comm, s->comm_stream));
+  CU(cudaEventRecord(s->ev_recv, s->comm_stream));
+  CU(cudaStreamWaitEvent(s->stream, s->ev_recv, 0));
+  return BDG_OK;
+}
+
+extern "C" int bdg_nccl_unique_id(void *id_out) {
+  static_assert(sizeof(ncclUniqueId) == BDG_NCCL_ID_BYTES, "ncclUniqueId size");
+  ncclUniqueId id;
+  if (ncclGetUniqueId(&id) != ncclSuccess) return BDG_E_NCCL;
+  memcpy(id_out, &id, sizeof(id));
+  return BDG_OK;
+}
+
+extern "C" int bdg_sw2d_comm_init(bdg_sw2d *s, const void *idp) {
+  if (!s || !idp) return BDG_E_INVALID;
+  CU(cudaSetDevice(s->device));
+  ncclUniqueId id;
+  memcpy(&id, idp, sizeof(id));
+  ncclComm_t comm;
+  NC(ncclCommInitRank(&comm, s->nranks, id, s->rank));
+  s->comm = (ncclComm *)comm;
+  return BDG_OK;
+}
+
+extern "C" int bdg_sw2d_halo_pack_to_host(bdg_sw2d *s, double *send_buf) {
+  if (!s) return BDG_E_INVALID;
+  if (s->n_send == 0) return BDG_OK;
+  CU(cudaSetDevice(s->device));
+  const int np = s->v.full ? 4 : 3;
+  cudaError_t e = launch_pack(s, s->q[s->cur], np == 4);
+  if (e != cudaSuccess) return fail(s, BDG_E_CUDA, "pack: %s", cudaGetErrorString(e));
+  CU(cudaMemcpyAsync(send_buf, s->d_sendbuf, sizeof(double) * np * s->n_send, cudaMemcpyDeviceToHost, s->stream));
+  CU(cudaStreamSynchronize(s->stream));
+  return BDG_OK;
+}
+
+// recv_buf uses the send-buffer layout of the peers: per neighbour segment, np planes of cnt values
+extern "C" int bdg_sw2d_halo_set_ghosts(bdg_sw2d *s, const double *recv_buf) {
+  if (!s) return BDG_E_INVALID;
+  CU(cudaSetDevice(s->device));
+  const int np = s->v.full ? 4 : 3;
+  double *q = s->q[s->cur];
+  for (int i = 0; i < s->n_nbr; ++i) {
+    const int ro = s->h_recv_off[i], cnt = s->h_recv_off[i + 1] - ro;
+    for (int c = 0; c < np; ++c) {
+      double *dst = (c < 3) ? q + c * s->v.stride + s->nT + ro : s->d_H + s->nT + ro;
+      if (c == 3 && !s->d_H) continue;
+      CU(cudaMemcpyAsync(dst, recv_buf + (size_t)np * ro + (size_t)c * cnt, sizeof(double) * cnt, cudaMemcpyHostToDevice, s->stream));
+    }
+  }
+  CU(cudaStreamSynchronize(s->stream));
+  return BDG_OK;
+}
+
+// ====================================================================================== hot path
+static int use_fused(const bdg_sw2d *s) {
+  if (s->variant == 1) return 0;
+  return s->fused_ok;
+}
+
+// One RHS evaluation of the live state.  write_rhs: store RHS planes into rhs_out (bdg_sw2d_rhs);
+// otherwise apply LSERK4 stage (a,b).  slot alternates the global-LF scalar between S_GMAX0/1.
+static int enqueue_stage(bdg_sw2d *s, int write_rhs, double *rhs_out, double a, double b, int slot) {
+  if (s->v.full && !s->v.H) return fail(s, BDG_E_INVALID, "sources=1 needs bdg_sw2d_set_bathymetry first");
+  double *q = s->q[s->cur];
+  const int K = s->v.K;
+  const bool halo = s->comm && s->n_nbr > 0;
+  const int ksplit = halo ? s->n_interior : K;
+  int rc;
+  cudaError_t e;
+  if ((rc = halo_begin(s, q))) return rc;
+  if (s->v.lf_global) {  // needs every trace, ghosts included: no overlap in this mode
+    if ((rc = halo_wait(s))) return rc;
+    if ((e = launch_generic_speed(s, q, slot)) != cudaSuccess) return fail(s, BDG_E_CUDA, "speed: %s", cudaGetErrorString(e));
+    if ((rc = allreduce_max(s, s->d_scal + slot))) return rc;
+  }
+  if (use_fused(s)) {
+    double *qo = s->q[s->cur ^ 1];
+    if ((e = launch_fused_stage(s, q, qo, s->res, 0, ksplit, a, b, write_rhs, rhs_out)) != cudaSuccess)
+      return fail(s, BDG_E_CUDA, "fused(interior): %s", cudaGetErrorString(e));
+    if (ksplit < K) {
+      if ((rc = halo_wait(s))) return rc;
+      if ((e = launch_fused_stage(s, q, qo, s->res, ksplit, K, a, b, write_rhs, rhs_out)) != cudaSuccess)
+        return fail(s, BDG_E_CUDA, "fused(cut): %s", cudaGetErrorString(e));
+    } else if (halo && !s->v.lf_global) {
+      if ((rc = halo_wait(s))) return rc;
+    }
+    if (!write_rhs) s->cur ^= 1;
+  } else {
+    if ((e = launch_generic_face(s, q, 0, ksplit, slot)) != cudaSuccess) return fail(s, BDG_E_CUDA, "face: %s", cudaGetErrorString(e));
+    if (halo && !s->v.lf_global && (rc = halo_wait(s))) return rc;
+    if ((e = launch_generic_face(s, q, ksplit, K, slot)) != cudaSuccess) return fail(s, BDG_E_CUDA, "face: %s", cudaGetErrorString(e));
+    if ((e = launch_generic_volume(s, q, s->res, rhs_out, write_rhs ? 0 : 1, a, b)) != cudaSuccess)
+      return fail(s, BDG_E_CUDA, "volume: %s", cudaGetErrorString(e));
+  }
+  return BDG_OK;
+}
+
+extern "C" int bdg_sw2d_rhs(bdg_sw2d *s, double *RHS1, double *RHS2, double *RHS3) {
+  if (!s) return BDG_E_INVALID;
+  CU(cudaSetDevice(s->device));
+  int rc;
+  if (!s->rhs && (rc = dev_alloc(s, &s->rhs, 3 * s->nT))) return rc;
+  if (s->v.lf_global) CU(cudaMemsetAsync(s->d_scal + S_GMAX0, 0, 2 * sizeof(double), s->stream));
+  if ((rc = enqueue_stage(s, 1, s->rhs, 0.0, 0.0, S_GMAX0))) return rc;
+  double *dst[3] = {RHS1, RHS2, RHS3};
+  for (int c = 0; c < 3; ++c)
+    if (dst[c]) {
+      if ((rc = download_transposed(s, s->rhs + c * s->nT, dst[c], s->v.Np, s->v.K))) return rc;
+      CU(cudaStreamSynchronize(s->stream));
+    }
+  CU(cudaStreamSynchronize(s->stream));
+  return BDG_OK;
+}
+
+static int enqueue_dt(bdg_sw2d *s) {
+  cudaError_t e;
+  int rc;
+  if ((e = launch_dt_reduce(s, s->q[s->cur])) != cudaSuccess) return fail(s, BDG_E_CUDA, "dt_reduce: %s", cudaGetErrorString(e));
+  if ((rc = allreduce_max(s, s->d_scal + S_DTMAX))) return rc;
+  if ((e = launch_dt_finalize(s)) != cudaSuccess) return fail(s, BDG_E_CUDA, "dt_finalize: %s", cudaGetErrorString(e));
+  return BDG_OK;
+}
+
+extern "C" int bdg_sw2d_timestep(bdg_sw2d *s, double *dt_out) {
+  if (!s || !dt_out) return BDG_E_INVALID;
+  CU(cudaSetDevice(s->device));
+  CU(cudaMemsetAsync(s->d_scal + S_DTMAX, 0, sizeof(double), s->stream));
+  int rc = enqueue_dt(s);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(dt_out, s->d_scal + S_DT, sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  CU(cudaStreamSynchronize(s->stream));
+  return BDG_OK;
+}
+
+extern "C" int bdg_sw2d_step(bdg_sw2d *s, int32_t nsteps, double dt) {
+  if (!s || nsteps < 0) return BDG_E_INVALID;
+  CU(cudaSetDevice(s->device));
+  const bool adaptive = !(dt > 0.0);
+  const bool device_time = adaptive || (s->v.full && s->prm.tide_amp != 0.0);
+  int rc;
+  cudaError_t e;
+  if (!adaptive) CU(cudaMemcpyAsync(s->d_scal + S_DT, &dt, sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  if (s->v.lf_global) CU(cudaMemsetAsync(s->d_scal + S_GMAX0, 0, 2 * sizeof(double), s->stream));
+  if (adaptive) {
+    CU(cudaMemsetAsync(s->d_scal + S_DTMAX, 0, sizeof(double), s->stream));
+    s->adaptive_used = 1;
+  }
+  int slot = S_GMAX0;
+  for (int st = 0; st < nsteps; ++st) {
+    if (adaptive && (rc = enqueue_dt(s))) return rc;
+    for (int stage = 0; stage < 5; ++stage) {  // reference src/advec1d/main.cpp:92-102
+      if ((rc = enqueue_stage(s, 0, nullptr, rk4a[stage], rk4b[stage], slot))) return rc;
+      slot ^= 1;
+    }
+    if (device_time) {
+      if ((e = launch_advance_time(s)) != cudaSuccess) return fail(s, BDG_E_CUDA, "advance: %s", cudaGetErrorString(e));
+    } else {
+      s->t += dt;
+    }
+  }
+  if (!device_time && nsteps > 0) CU(cudaMemcpyAsync(s->d_scal + S_T, &s->t, sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  return BDG_OK;
+}
+
+extern "C" int bdg_sw2d_sync(bdg_sw2d *s) {
+  if (!s) return BDG_E_INVALID;
+  CU(cudaSetDevice(s->device));
+  CU(cudaStreamSynchronize(s->stream));
+  CU(cudaStreamSynchronize(s->comm_stream));
+  return BDG_OK;
+}
+
+extern "C" int bdg_sw2d_check(bdg_sw2d *s, double *eta_max) {
+  if (!s) return BDG_E_INVALID;
+  CU(cudaSetDevice(s->device));
+  CU(cudaMemsetAsync(s->d_scal + S_ETAMAX, 0, 2 * sizeof(double), s->stream));
+  cudaError_t e = launch_check(s, s->q[s->cur]);
+  if (e != cudaSuccess) return fail(s, BDG_E_CUDA, "check: %s", cudaGetErrorString(e));
+  double r[2];
+  CU(cudaMemcpyAsync(r, s->d_scal + S_ETAMAX, 2 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  CU(cudaStreamSynchronize(s->stream));
+  if (eta_max) *eta_max = r[1] != 0.0 ? NAN : r[0];
+  if (r[1] != 0.0 || r[0] > 1e8) return fail(s, BDG_E_UNSTABLE, "A numerical instability has occurred!");  // reference main.cpp:238-240
+  return BDG_OK;
+}
+
+// ====================================================================================== plumbing
+extern "C" int bdg_sw2d_set_variant(bdg_sw2d *s, int32_t variant) {
+  if (!s || variant < 0 || variant > 2) return BDG_E_INVALID;
+  if (variant == 2 && !s->fused_ok) return fail(s, BDG_E_UNSUPPORTED, "fused path unavailable for this context (needs affine triangles, uniform face tags, no filter, supported order)");
+  s->variant = variant;
+  return BDG_OK;
+}
+extern "C" int bdg_sw2d_get_variant(const bdg_sw2d *s) { return s ? (use_fused(s) ? 2 : 1) : -1; }
+extern "C" int64_t bdg_sw2d_launch_count(const bdg_sw2d *s) { return s ? s->launches : 0; }
+extern "C" void *bdg_sw2d_stream(bdg_sw2d *s) { return s ? (void *)s->stream : nullptr; }
+
+// B_alg of SURVEY.md §8d: q r+w and res r+w (96*Np), vmapP (4*Nfn), geometry, BC tag per face,
+// plus the static bathymetry reads in full mode.
+extern "C" double bdg_sw2d_algorithmic_bytes_per_stage(const bdg_sw2d *s) {
+  if (!s) return 0.0;
+  const double Np = s->v.Np, Nfn = s->v.Nfn, Nf = s->v.Nf;
+  double per = 96.0 * Np + 4.0 * Nfn + 4.0 * Nf;
+  per += s->is_affine ? (4 * 8 + Nf * 3 * 8) : (32.0 * Np + 24.0 * Nfn);
+  if (s->v.full) per += 16.0 * Np + 16.0 * Nfn;
+  return per * (double)s->v.K;
+}

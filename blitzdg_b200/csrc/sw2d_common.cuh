@@ -1,0 +1,89 @@
+// Shared declarations of the sw2d device path: solver handle, device views, launch entry points.
+//
+// Device data layout: every field is stored ELEMENT-MAJOR, index m = n + Np*k --
+// exactly the index space vmapM/vmapP address -- so the reference's fullToVector/vectorToFull
+// sweeps (include/BlitzHelpers.hpp:215-297) disappear; conversion from the host's row-major
+// [Np][K] happens once at upload.  Ghost values of off-rank neighbours sit behind the local
+// nodes at m = Np*K + g.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/blitzdg_b200.h"
+
+struct ncclComm;
+
+// scalar slots kept on the device (no host round trips inside bdg_sw2d_step)
+enum { S_T = 0, S_DT = 1, S_GMAX0 = 2, S_GMAX1 = 3, S_DTMAX = 4, S_ETAMAX = 5, S_NANFLAG = 6, S_COUNT = 8 };
+
+// everything a kernel needs, passed by value
+struct Sw2dView {
+  int N, Np, Nfp, Nf, Nfn, K;
+  int full;        // star states + sources (prm.sources)
+  int lf_global;   // prm.lf_mode == 1
+  int use_filter;
+  long long stride;  // distance between the h, hu, hv planes of a state buffer (>= Np*K + n_ghost)
+  double g, CD, fcor, tide_amp, tide_period, tide_ramp;
+  const double *Dr, *Ds, *Lift, *Filt;   // row-major as uploaded
+  const double *rx, *sx, *ry, *sy;       // [K][Np] element-major (per node)
+  const double *nx, *ny, *Fscale;        // [K][Nfn] element-major (per face node)
+  const double *aff;                     // affine triangles: [K][4+3*Nf] = rx,sx,ry,sy, then (nx,ny,Fscale) per face; else NULL
+  const int32_t *vmapP;                  // [K][Nfn]
+  const int32_t *fmask;                  // [Nfn] local node of face-node slot
+  const uint8_t *bctag;                  // [K][Nfn] BCTag per face node (0 interior)
+  const uint8_t *facetag;                // [K][Nf]  BCTag per face (fused path), 255 = mixed
+  const double *H, *Hx, *Hy;             // H: [Np*K + n_ghost]; Hx,Hy: [Np*K]; NULL when unset
+  double *scal;                          // S_COUNT device scalars
+};
+
+struct bdg_sw2d {
+  int device;
+  cudaStream_t stream, comm_stream;
+  cudaEvent_t ev_pack, ev_recv;
+  bdg_sw2d_params prm;
+  Sw2dView v;
+  int n_ghost;
+  size_t nT, nF;        // Np*K, Nfn*K
+  int is_affine;
+  int variant;          // 0 auto, 1 generic, 2 fused
+  int cur;              // ping-pong index of the live state buffer
+  double *q[2];         // [3][stride]
+  double *res;          // [3][nT]
+  double *rhs;          // [3][nT] scratch (bdg_sw2d_rhs) -- allocated on demand
+  double *sflux;        // [3][nF] generic path: Fscale*dFlux
+  double *d_Dr, *d_Ds, *d_Lift, *d_Filt, *d_rx, *d_sx, *d_ry, *d_sy, *d_nx, *d_ny, *d_Fscale, *d_aff;
+  double *d_H, *d_Hx, *d_Hy;
+  int32_t *d_vmapP, *d_fmask;
+  uint8_t *d_bctag, *d_facetag;
+  double *d_scal;
+  void *fused_ops;      // operator fragments of the fused path (device), NULL if unsupported
+  int fused_ok;
+  double t;             // host mirror of the time (exact for fixed dt)
+  int adaptive_used;
+  // halo
+  int rank, nranks, n_nbr, n_send, n_interior;
+  int32_t *h_nbr, *h_send_off, *h_recv_off;
+  int32_t *d_send_nodes;
+  double *d_sendbuf;    // [n_nbr segments][3 (or 4)][count]
+  ncclComm *comm;
+  int64_t launches;
+  char err[512];
+};
+
+// ---- launchers (each returns cudaGetLastError()) ------------------------------------------------
+// generic two-kernel path over elements [k0,k1): face fluxes into sflux, then volume+lift+update
+cudaError_t launch_generic_speed(bdg_sw2d *s, const double *q, int slot);
+cudaError_t launch_generic_face(bdg_sw2d *s, const double *q, int k0, int k1, int slot);
+// mode 0: write RHS to out (3 planes of nT); mode 1: LSERK4 stage update of q/res in place
+cudaError_t launch_generic_volume(bdg_sw2d *s, double *q, double *res, double *out, int mode, double a, double b);
+cudaError_t launch_dt_reduce(bdg_sw2d *s, const double *q);
+cudaError_t launch_dt_finalize(bdg_sw2d *s);
+cudaError_t launch_advance_time(bdg_sw2d *s);
+cudaError_t launch_check(bdg_sw2d *s, const double *q);
+cudaError_t launch_pack(bdg_sw2d *s, const double *q, int with_H);
+// fused DMMA path (affine triangles): q_in -> q_out, res in place, elements [k0,k1)
+int fused_supported(const bdg_sw2d *s);
+cudaError_t fused_prepare(bdg_sw2d *s);
+cudaError_t launch_fused_stage(bdg_sw2d *s, const double *q_in, double *q_out, double *res, int k0, int k1, double a,
+                               double b, int write_rhs, double *rhs_out);
+void fused_release(bdg_sw2d *s);

@@ -1,0 +1,175 @@
+"""Host-side mirror of the reference's sw2d driver interface on top of the C ABI.
+
+Names follow /root/reference/src/sw2d/SW2d.hpp:15-55 (physParams, numParams, fields,
+computeRHS, computeTimeStep) and the driver loops (src/sw2d/main.cpp:192-244 with the LSERK4 stage
+idiom of src/advec1d/main.cpp:92-102).  All arithmetic runs in the CUDA library; this file only
+marshals host arrays ([Np][K], row-major) across the boundary.  No CPU fallback.
+"""
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import capi
+
+
+class NumericalInstability(RuntimeError):
+    """The reference throws std::runtime_error("A numerical instability has occurred!")."""
+
+
+@dataclass
+class physParams:  # src/sw2d/SW2d.hpp:15-22, literals src/sw2d/main.cpp:49-51
+    g: float = 9.81
+    CD: float = 2.5e-3
+    f: float = 1.0070e-4
+    initTime: float = 0.0
+    finalTime: float = 24 * 3600.0
+
+
+@dataclass
+class numParams:  # src/sw2d/SW2d.hpp:24-30
+    N: int = 4
+    CFL: float = 0.25
+    filterPercent: float = 0.90
+    filterOrder: int = 4
+    outputInterval: int = 20
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double)) if a is not None else C.POINTER(C.c_double)()
+
+
+class SW2dSolver:
+    """One handle = one GPU.  mode 'simple' = sw2d-simple physics (per-face LF, no sources);
+    'full' = src/sw2d physics (global LF, star states, bathymetry/drag/Coriolis, Out BC)."""
+
+    def __init__(self, ctx, phys=None, num=None, mode="simple", lf_mode=None, sources=None, use_filter=False,
+                 halo=None, device=0, variant=0):
+        self.lib = capi.load()
+        self.ctx = ctx
+        self.phys = phys or physParams()
+        self.num = num or numParams(N=ctx.N)
+        full = mode == "full"
+        lf = (1 if full else 0) if lf_mode is None else int(lf_mode)
+        src = (1 if full else 0) if sources is None else int(sources)
+        self.prm = capi.make_params(g=self.phys.g, CD=self.phys.CD, f=self.phys.f, CFL=self.num.CFL, lf_mode=lf,
+                                    sources=src, filter=int(use_filter))
+        self._cctx, self._keep = capi.pack_context(ctx)
+        self._chalo, self._keep_h = (capi.pack_halo(halo) if halo is not None else (None, None))
+        h = C.c_void_p()
+        rc = self.lib.bdg_sw2d_create(C.byref(h), C.byref(self._cctx), C.byref(self.prm),
+                                      C.byref(self._chalo) if self._chalo is not None else None, int(device))
+        if rc != capi.BDG_OK:
+            raise RuntimeError("bdg_sw2d_create failed (%d): %s" % (rc, self.lib.bdg_last_error(None).decode()))
+        self.h = h
+        self.shape = (ctx.Np, ctx.K)
+        if variant:
+            self.set_variant(variant)
+
+    def _ck(self, rc):
+        if rc == capi.BDG_E_UNSTABLE:
+            raise NumericalInstability(self.lib.bdg_last_error(self.h).decode())
+        if rc != capi.BDG_OK:
+            raise RuntimeError("blitzdg_b200 error %d: %s" % (rc, self.lib.bdg_last_error(self.h).decode()))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.bdg_sw2d_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # fields --------------------------------------------------------------------------------------
+    def _in(self, a):
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        assert a.shape == self.shape, (a.shape, self.shape)
+        return a
+
+    def set_bathymetry(self, H, Hx=None, Hy=None):
+        H = self._in(H)
+        Hx = self._in(Hx) if Hx is not None else np.zeros(self.shape)
+        Hy = self._in(Hy) if Hy is not None else np.zeros(self.shape)
+        self._ck(self.lib.bdg_sw2d_set_bathymetry(self.h, _dp(H), _dp(Hx), _dp(Hy)))
+
+    def set_state(self, h, hu, hv, t=0.0):
+        h, hu, hv = self._in(h), self._in(hu), self._in(hv)
+        self._ck(self.lib.bdg_sw2d_set_state(self.h, _dp(h), _dp(hu), _dp(hv), float(t)))
+
+    def get_state(self, out=None):
+        h, hu, hv = out if out is not None else (np.empty(self.shape), np.empty(self.shape), np.empty(self.shape))
+        t = C.c_double(0)
+        self._ck(self.lib.bdg_sw2d_get_state(self.h, _dp(h), _dp(hu), _dp(hv), C.byref(t)))
+        return h, hu, hv, t.value
+
+    # hot path ------------------------------------------------------------------------------------
+    def computeRHS(self):
+        """sw2d::computeRHS on the current device state; returns (RHS1, RHS2, RHS3) as [Np][K]."""
+        R = [np.empty(self.shape) for _ in range(3)]
+        self._ck(self.lib.bdg_sw2d_rhs(self.h, _dp(R[0]), _dp(R[1]), _dp(R[2])))
+        return R
+
+    def computeTimeStep(self):
+        dt = C.c_double(0)
+        self._ck(self.lib.bdg_sw2d_timestep(self.h, C.byref(dt)))
+        return dt.value
+
+    def step(self, nsteps, dt=0.0, sync=True):
+        self._ck(self.lib.bdg_sw2d_step(self.h, int(nsteps), float(dt)))
+        if sync:
+            self.sync()
+
+    def sync(self):
+        self._ck(self.lib.bdg_sw2d_sync(self.h))
+
+    def check(self):
+        """The drivers' blow-up guard; raises NumericalInstability like the reference's throw."""
+        m = C.c_double(0)
+        self._ck(self.lib.bdg_sw2d_check(self.h, C.byref(m)))
+        return m.value
+
+    # plumbing ------------------------------------------------------------------------------------
+    def set_variant(self, v):
+        self._ck(self.lib.bdg_sw2d_set_variant(self.h, int(v)))
+
+    @property
+    def variant(self):
+        return self.lib.bdg_sw2d_get_variant(self.h)
+
+    @property
+    def launch_count(self):
+        return self.lib.bdg_sw2d_launch_count(self.h)
+
+    @property
+    def stream(self):
+        return self.lib.bdg_sw2d_stream(self.h)
+
+    @property
+    def algorithmic_bytes_per_stage(self):
+        return self.lib.bdg_sw2d_algorithmic_bytes_per_stage(self.h)
+
+    def comm_init(self, unique_id_bytes):
+        buf = C.create_string_buffer(bytes(unique_id_bytes), capi.BDG_NCCL_ID_BYTES)
+        self._ck(self.lib.bdg_sw2d_comm_init(self.h, buf))
+
+    def halo_pack_to_host(self, n_send):
+        np_ = 4 if self.prm.sources else 3
+        buf = np.empty(np_ * n_send)
+        self._ck(self.lib.bdg_sw2d_halo_pack_to_host(self.h, _dp(buf)))
+        return buf
+
+    def halo_set_ghosts(self, buf):
+        buf = np.ascontiguousarray(buf, dtype=np.float64)
+        self._ck(self.lib.bdg_sw2d_halo_set_ghosts(self.h, _dp(buf)))
+
+
+def nccl_unique_id():
+    lib = capi.load()
+    buf = C.create_string_buffer(capi.BDG_NCCL_ID_BYTES)
+    rc = lib.bdg_nccl_unique_id(buf)
+    if rc != capi.BDG_OK:
+        raise RuntimeError("ncclGetUniqueId failed")
+    return buf.raw

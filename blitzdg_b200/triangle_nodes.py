@@ -219,28 +219,35 @@ class TriangleNodesProvisioner:
         etov = mesh.get_Elements().reshape(K, Nf)
         vert = mesh.get_Vertices().reshape(-1, 3)
         fm = self.Fmask.astype(np.int64)  # [Nfp][Nf]
-        karr = np.arange(K, dtype=np.int64)
-        # vmapM3[k][f][n] = Fmask[n][f] + Np*k
-        vmapM = (fm.T[None, :, :] + Np * karr[:, None, None])
         x, y = self.xGrid, self.yGrid  # [Np][K]
-        xM = x[fm.T[None, :, :], karr[:, None, None]]  # [K][Nf][Nfp]
-        yM = y[fm.T[None, :, :], karr[:, None, None]]
-        # neighbour face node coordinates [K][Nf][Nfp]
-        nodeP = fm.T[E2F]  # local ids on the neighbour's face: [K][Nf][Nfp]
-        xP = x[nodeP, E2E[:, :, None]]
-        yP = y[nodeP, E2E[:, :, None]]
         v1 = etov
         v2 = np.roll(etov, -1, axis=1)
-        refd = np.hypot(vert[v1, 0] - vert[v2, 0], vert[v1, 1] - vert[v2, 1])  # [K][Nf]
-        # distance matrix [K][Nf][n][nP]; reference keeps the LAST nP that matches (loop order, :957-968)
-        dx = xM[:, :, :, None] - xP[:, :, None, :]
-        dy = yM[:, :, :, None] - yP[:, :, None, :]
-        match = np.hypot(dx, dy) < (refd * NodeTol)[:, :, None, None]
-        has = match.any(axis=3)
-        last = Nfp - 1 - np.argmax(match[:, :, :, ::-1], axis=3)
-        nP = np.take_along_axis(nodeP, last, axis=2)
-        vmapP = np.where(has, nP + Np * E2E[:, :, None], 0)
-        mapP = np.where(has, last + E2F[:, :, None] * Nfp + E2E[:, :, None] * Nf * Nfp, 0)
+        refd_all = np.hypot(vert[v1, 0] - vert[v2, 0], vert[v1, 1] - vert[v2, 1])  # [K][Nf]
+        vmapM = np.empty((K, Nf, Nfp), dtype=np.int32)
+        vmapP = np.empty((K, Nf, Nfp), dtype=np.int32)
+        mapP = np.empty((K, Nf, Nfp), dtype=np.int32)
+        CH = 1 << 17  # elements per chunk: bounds the [K][Nf][Nfp][Nfp] distance tensor
+        for c0 in range(0, K, CH):
+            c1 = min(K, c0 + CH)
+            karr = np.arange(c0, c1, dtype=np.int64)
+            e2e, e2f, refd = E2E[c0:c1], E2F[c0:c1], refd_all[c0:c1]
+            # vmapM3[k][f][n] = Fmask[n][f] + Np*k
+            vM = fm.T[None, :, :] + Np * karr[:, None, None]
+            xM = x[fm.T[None, :, :], karr[:, None, None]]  # [k][Nf][Nfp]
+            yM = y[fm.T[None, :, :], karr[:, None, None]]
+            nodeP = fm.T[e2f]  # local ids on the neighbour's face: [k][Nf][Nfp]
+            xP = x[nodeP, e2e[:, :, None]]
+            yP = y[nodeP, e2e[:, :, None]]
+            # distance matrix [k][Nf][n][nP]; the reference keeps the LAST nP that matches (loop order, :957-968)
+            dx = xM[:, :, :, None] - xP[:, :, None, :]
+            dy = yM[:, :, :, None] - yP[:, :, None, :]
+            match = np.hypot(dx, dy) < (refd * NodeTol)[:, :, None, None]
+            has = match.any(axis=3)
+            last = Nfp - 1 - np.argmax(match[:, :, :, ::-1], axis=3)
+            nP = np.take_along_axis(nodeP, last, axis=2)
+            vmapM[c0:c1] = vM
+            vmapP[c0:c1] = np.where(has, nP + Np * e2e[:, :, None], 0)
+            mapP[c0:c1] = np.where(has, last + e2f[:, :, None] * Nfp + e2e[:, :, None] * Nf * Nfp, 0)
         self.vmapM = vmapM.reshape(-1).astype(np.int32)
         self.vmapP = vmapP.reshape(-1).astype(np.int32)
         self.mapP = mapP.reshape(-1).astype(np.int32)

@@ -1,0 +1,47 @@
+"""CPU checks of the drop-in boundary: the shared library loads and exports every symbol that
+include/blitzdg_b200.h declares (no compute calls without a GPU)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+from blitzdg_b200 import capi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    src = open(os.path.join(ROOT, "include", "blitzdg_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(bdg_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_header_and_binding_agree():
+    assert _declared() == sorted(capi.EXPORTS)
+
+
+def test_library_exports_every_declared_symbol():
+    if not os.path.exists(capi.LIB_PATH):
+        import __graft_entry__
+
+        __graft_entry__.build()
+    lib = capi.load()
+    for name in _declared():
+        assert hasattr(lib, name), name
+    assert lib.bdg_version() >= 100
+
+
+def test_create_fails_loudly_without_gpu_or_with_bad_context():
+    """No CPU fallback: on a box without CUDA, create returns BDG_E_CUDA; NULL context is BDG_E_INVALID."""
+    lib = capi.load()
+    h = ctypes.c_void_p()
+    assert lib.bdg_sw2d_create(ctypes.byref(h), None, None, None, 0) == capi.BDG_E_INVALID
+    assert b"NULL" in lib.bdg_last_error(None)
+
+
+def test_struct_layout_matches_c():
+    """sizeof of the ctypes mirrors equals the C structs (x86-64 SysV): 5*4 pad-> 24, then pointers."""
+    assert ctypes.sizeof(capi.bdg_sw2d_params) == 4 * 8 + 4 * 4 + 3 * 8
+    assert ctypes.sizeof(capi.bdg_dgcontext2d) == 24 + 13 * 8 + 9 * 8 + 9 * 4 + 4
+    assert ctypes.sizeof(capi.bdg_halo) == 16 + 4 * 8 + 8
