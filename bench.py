@@ -228,8 +228,7 @@ def run_b200(args):
     sol = SW2dSolver(ctx, mode=args.mode, halo=halo, device=local)
     if args.variant:
         sol.set_variant(args.variant)
-    if args.mode == "full":
-        sol.set_bathymetry(H, np.zeros_like(H), np.zeros_like(H))
+    sol.set_bathymetry(H, np.zeros_like(H), np.zeros_like(H))  # flat bottom; also feeds eta = h - H of the blow-up guard
     if world > 1:
         idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:

@@ -247,6 +247,7 @@ def test_full_size_properties_1M_triangles():
     H, h, hu, hv = gaussian_hump(ctx.x, ctx.y)
     w = np.linalg.inv(ctx.V @ ctx.V.T).sum(axis=0)
     mass0 = (w[:, None] * ctx.J * h).sum()
+    sol.set_bathymetry(H)  # eta = h - H in the blow-up guard (reference src/sw2d/main.cpp:193,238)
     sol.set_state(h, hu, hv)
     dt = 0.5 * sol.computeTimeStep() * (0.65 / 0.25)
     sol.step(20, dt)
