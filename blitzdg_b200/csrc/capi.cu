@@ -213,8 +213,8 @@ static int create_impl(bdg_sw2d *s, const bdg_dgcontext2d *c, const bdg_sw2d_par
     if ((rc = dev_alloc(s, &s->q[b], (size_t)3 * stride))) return rc;
     CU(cudaMemsetAsync(s->q[b], 0, sizeof(double) * 3 * stride, s->stream));
   }
-  if ((rc = dev_alloc(s, &s->res, 3 * s->nT))) return rc;
-  CU(cudaMemsetAsync(s->res, 0, sizeof(double) * 3 * s->nT, s->stream));
+  if ((rc = dev_alloc(s, &s->res, (size_t)3 * stride))) return rc;
+  CU(cudaMemsetAsync(s->res, 0, sizeof(double) * 3 * stride, s->stream));
   if ((rc = dev_alloc(s, &s->sflux, 3 * s->nF))) return rc;
   if ((rc = dev_alloc(s, &s->d_scal, (size_t)S_COUNT))) return rc;
   CU(cudaMemsetAsync(s->d_scal, 0, sizeof(double) * S_COUNT, s->stream));
@@ -391,7 +391,7 @@ extern "C" int bdg_sw2d_set_state(bdg_sw2d *s, const double *h, const double *hu
     int rc = upload_transposed(s, src[c], q + c * s->v.stride, s->v.Np, s->v.K);
     if (rc) return rc;
   }
-  CU(cudaMemsetAsync(s->res, 0, sizeof(double) * 3 * s->nT, s->stream));  // reference src/sw2d/main.cpp:117-119
+  CU(cudaMemsetAsync(s->res, 0, sizeof(double) * 3 * s->v.stride, s->stream));  // reference src/sw2d/main.cpp:117-119
   s->t = t;
   CU(cudaMemcpyAsync(s->d_scal + S_T, &s->t, sizeof(double), cudaMemcpyHostToDevice, s->stream));
   CU(cudaStreamSynchronize(s->stream));
@@ -532,11 +532,11 @@ static int enqueue_stage(bdg_sw2d *s, int write_rhs, double *rhs_out, double a, 
   }
   if (use_fused(s)) {
     double *qo = s->q[s->cur ^ 1];
-    if ((e = launch_fused_stage(s, q, qo, s->res, 0, ksplit, a, b, write_rhs, rhs_out)) != cudaSuccess)
+    if ((e = launch_fused_stage(s, q, qo, s->res, 0, ksplit, a, b, write_rhs, rhs_out, slot)) != cudaSuccess)
       return fail(s, BDG_E_CUDA, "fused(interior): %s", cudaGetErrorString(e));
     if (ksplit < K) {
       if ((rc = halo_wait(s))) return rc;
-      if ((e = launch_fused_stage(s, q, qo, s->res, ksplit, K, a, b, write_rhs, rhs_out)) != cudaSuccess)
+      if ((e = launch_fused_stage(s, q, qo, s->res, ksplit, K, a, b, write_rhs, rhs_out, slot)) != cudaSuccess)
         return fail(s, BDG_E_CUDA, "fused(cut): %s", cudaGetErrorString(e));
     } else if (halo && !s->v.lf_global) {
       if ((rc = halo_wait(s))) return rc;

@@ -48,7 +48,7 @@ struct bdg_sw2d {
   int variant;          // 0 auto, 1 generic, 2 fused
   int cur;              // ping-pong index of the live state buffer
   double *q[2];         // [3][stride]
-  double *res;          // [3][nT]
+  double *res;          // [3][stride] (same plane stride as q: 128-B aligned planes for the bulk copies)
   double *rhs;          // [3][nT] scratch (bdg_sw2d_rhs) -- allocated on demand
   double *sflux;        // [3][nF] generic path: Fscale*dFlux
   double *d_Dr, *d_Ds, *d_Lift, *d_Filt, *d_rx, *d_sx, *d_ry, *d_sy, *d_nx, *d_ny, *d_Fscale, *d_aff;
@@ -85,5 +85,5 @@ cudaError_t launch_pack(bdg_sw2d *s, const double *q, int with_H);
 int fused_supported(const bdg_sw2d *s);
 cudaError_t fused_prepare(bdg_sw2d *s);
 cudaError_t launch_fused_stage(bdg_sw2d *s, const double *q_in, double *q_out, double *res, int k0, int k1, double a,
-                               double b, int write_rhs, double *rhs_out);
+                               double b, int write_rhs, double *rhs_out, int slot);
 void fused_release(bdg_sw2d *s);

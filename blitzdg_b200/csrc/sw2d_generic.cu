@@ -220,8 +220,8 @@ __global__ void k_volume(Sw2dView v, double *__restrict__ q, double *__restrict_
   } else {  // A13 (src/advec1d/main.cpp:98,101)
     const double dt = v.scal[S_DT];
     double s1 = dt * r1, s2 = dt * r2, s3 = dt * r3;
-    if (a != 0.0) { s1 = a * res[m] + s1; s2 = a * res[nT + m] + s2; s3 = a * res[2 * nT + m] + s3; }
-    res[m] = s1; res[nT + m] = s2; res[2 * nT + m] = s3;
+    if (a != 0.0) { s1 = a * res[m] + s1; s2 = a * res[v.stride + m] + s2; s3 = a * res[2 * v.stride + m] + s3; }
+    res[m] = s1; res[v.stride + m] = s2; res[2 * v.stride + m] = s3;
     q[m] = h + b * s1; q[v.stride + m] = hu + b * s2; q[2 * v.stride + m] = hv + b * s3;
   }
 }
