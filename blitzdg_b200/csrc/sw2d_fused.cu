@@ -100,17 +100,20 @@ struct Cfg {
   static constexpr int MB = (NP + 7) / 8;     // row blocks
   static constexpr bool A_REGS = (MB * KB <= 36);
   static constexpr int TNP = kTile * NP;      // doubles per field per tile
-  // shared memory carve-up (bytes, every section 16-B aligned)
-  static constexpr size_t oQ = 0;
-  static constexpr size_t oR = oQ + sizeof(double) * 3 * TNP;
-  static constexpr size_t oFl = oR + sizeof(double) * 3 * TNP;
-  static constexpr size_t oAff = oFl + sizeof(double) * 4 * TNP;
-  static constexpr size_t oA = oAff + sizeof(double) * kTile * kAW;
-  static constexpr size_t oVm = oA + (A_REGS ? 0 : sizeof(double) * MB * KB * 32);
-  static constexpr size_t oTag = oVm + sizeof(int32_t) * kTile * NFN;
-  static constexpr size_t oFm = oTag + ((kTile * 3 + 15) / 16) * 16;
-  static constexpr size_t oBar = oFm + ((sizeof(int32_t) * NFN + 15) / 16) * 16;
-  static constexpr size_t bytes = oBar + 32;
+  // one tile buffer (bytes, every section 16-B aligned): q, res, geometry, vmapP, face tags
+  static constexpr size_t bQ = 0;
+  static constexpr size_t bR = bQ + sizeof(double) * 3 * TNP;
+  static constexpr size_t bAff = bR + sizeof(double) * 3 * TNP;
+  static constexpr size_t bVm = bAff + sizeof(double) * kTile * kAW;
+  static constexpr size_t bTag = bVm + sizeof(int32_t) * kTile * NFN;
+  static constexpr size_t BUF = bTag + ((kTile * 3 + 15) / 16) * 16;
+  static constexpr uint32_t txQ = sizeof(double) * TNP;  // one field plane of a tile
+  static constexpr uint32_t txMeta = sizeof(int32_t) * kTile * NFN + sizeof(double) * kTile * kAW + kTile * 3;
+  // CTA-wide sections behind NBUF tile buffers
+  static constexpr size_t sizeFl = sizeof(double) * 4 * TNP;
+  static constexpr size_t sizeA = A_REGS ? 0 : sizeof(double) * MB * KB * 32;
+  static constexpr size_t sizeFm = ((sizeof(int32_t) * NFN + 15) / 16) * 16;
+  static constexpr size_t total(int nbuf) { return nbuf * BUF + sizeFl + sizeA + sizeFm + 64; }
 };
 
 struct StageArgs {
@@ -120,90 +123,90 @@ struct StageArgs {
   double *rhs_out;      // write_rhs mode: [3][nT]
   const double *Afrag;  // [MB][KB][32] operator in DMMA A-fragment order
   int k0, k1;           // active element range
-  int tile0;            // first tile index of this launch
+  int tile0, ntiles;    // tiles [tile0, tile0 + ntiles) of this launch
   int write_rhs;
   int slot;             // scal slot of the global LF speed
   double a, b;          // LSERK4 stage coefficients
 };
 
 template <int NP, int NFP>
-__global__ void __launch_bounds__(kThreads) k_fused_stage(Sw2dView v, StageArgs p) {
+struct Smem {
+  using C = Cfg<NP, NFP>;
+  unsigned char *base;
+  int nbuf;
+  __device__ double *Q(int b) const { return reinterpret_cast<double *>(base + b * C::BUF + C::bQ); }
+  __device__ double *R(int b) const { return reinterpret_cast<double *>(base + b * C::BUF + C::bR); }
+  __device__ double *Aff(int b) const { return reinterpret_cast<double *>(base + b * C::BUF + C::bAff); }
+  __device__ int32_t *Vm(int b) const { return reinterpret_cast<int32_t *>(base + b * C::BUF + C::bVm); }
+  __device__ uint8_t *Tag(int b) const { return base + b * C::BUF + C::bTag; }
+  __device__ double *Fl() const { return reinterpret_cast<double *>(base + nbuf * C::BUF); }
+  __device__ double *A() const { return reinterpret_cast<double *>(base + nbuf * C::BUF + C::sizeFl); }
+  __device__ int32_t *Fm() const { return reinterpret_cast<int32_t *>(base + nbuf * C::BUF + C::sizeFl + C::sizeA); }
+  __device__ uint64_t *Bar() const { return reinterpret_cast<uint64_t *>(base + nbuf * C::BUF + C::sizeFl + C::sizeA + C::sizeFm); }
+};
+
+// thread 0: TMA bulk loads of one full tile into buffer b, completion on bar
+template <int NP, int NFP>
+__device__ __forceinline__ void issue_tile_load(const Sw2dView &v, const StageArgs &p, const Smem<NP, NFP> &S, int b, long long kt0,
+                                                bool need_res, uint64_t *bar) {
+  using C = Cfg<NP, NFP>;
+  const long long base = kt0 * NP;
+  mbar_expect_tx(bar, (need_res ? 6 : 3) * C::txQ + C::txMeta);
+  bulk_g2s(S.Vm(b), v.vmapP + kt0 * C::NFN, sizeof(int32_t) * kTile * C::NFN, bar);
+  bulk_g2s(S.Tag(b), v.facetag + kt0 * 3, kTile * 3, bar);
+  bulk_g2s(S.Aff(b), v.aff + kt0 * kAW, sizeof(double) * kTile * kAW, bar);
+  for (int f = 0; f < 3; ++f) bulk_g2s(S.Q(b) + f * C::TNP, p.q_in + f * v.stride + base, C::txQ, bar);
+  if (need_res)
+    for (int f = 0; f < 3; ++f) bulk_g2s(S.R(b) + f * C::TNP, p.res + f * v.stride + base, C::txQ, bar);
+}
+
+// The arithmetic of one tile that sits in shared memory (A1-A13 of SURVEY.md Appendix A).  On return the
+// tile's q and res planes hold the updated values (stage mode) -- or, in write_rhs mode, rhs_out has been
+// written and the tile is untouched.  Contains two __syncthreads(); the caller makes the tile visible first.
+template <int NP, int NFP>
+__device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs &p, double *__restrict__ sQ, double *__restrict__ sR,
+                                             const double *__restrict__ sAff, const int32_t *__restrict__ sVm,
+                                             const uint8_t *__restrict__ sTag, double *__restrict__ sFl, const double *__restrict__ sA,
+                                             const int32_t *__restrict__ sFm, const double *Areg, long long kt0, int nload,
+                                             bool need_res) {
   using C = Cfg<NP, NFP>;
   constexpr int NFN = C::NFN, NPB = C::NPB, NFB = C::NFB, KB = C::KB, MB = C::MB, TNP = C::TNP;
-  extern __shared__ __align__(128) unsigned char smem[];
-  double *sQ = reinterpret_cast<double *>(smem + C::oQ);
-  double *sR = reinterpret_cast<double *>(smem + C::oR);
-  double *sFl = reinterpret_cast<double *>(smem + C::oFl);
-  double *sAff = reinterpret_cast<double *>(smem + C::oAff);
-  double *sA = reinterpret_cast<double *>(smem + C::oA);
-  int32_t *sVm = reinterpret_cast<int32_t *>(smem + C::oVm);
-  uint8_t *sTag = reinterpret_cast<uint8_t *>(smem + C::oTag);
-  int32_t *sFm = reinterpret_cast<int32_t *>(smem + C::oFm);
-  uint64_t *bar = reinterpret_cast<uint64_t *>(smem + C::oBar);
-
-  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int c = lane >> 2, t = lane & 3;
   const int e = w + 4 * c;  // my element of the tile (B-fragment column c)
-  const long long kt0 = (long long)(p.tile0 + blockIdx.x) * kTile;
-  const int nload = (int)min((long long)kTile, (long long)v.K - kt0);
-  const bool full_tile = nload == kTile;
-  const bool all_active = full_tile && kt0 >= p.k0 && kt0 + kTile <= p.k1;
-  const bool need_res = !p.write_rhs && p.a != 0.0;
+  const int eo = e * NP;
   const long long stride = v.stride;
   const long long base = kt0 * NP;  // first volume node of the tile
+  const int tile_nodes = nload * NP;
+  const double g = v.g, half_g = 0.5 * v.g;
+  const double *af = sAff + e * kAW;
 
-  // ---- stage the tile ------------------------------------------------------------------------------
-  if (full_tile) {
-    if (tid == 0) {
-      mbar_init(&bar[0], 1);
-      mbar_init(&bar[1], 1);
-      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-    if (tid == 0) {
-      constexpr uint32_t bq = sizeof(double) * TNP;
-      constexpr uint32_t b0 = 3 * bq + sizeof(int32_t) * kTile * NFN + sizeof(double) * kTile * kAW + kTile * 3;
-      mbar_expect_tx(&bar[0], b0);
-      for (int f = 0; f < 3; ++f) bulk_g2s(sQ + f * TNP, p.q_in + f * stride + base, bq, &bar[0]);
-      bulk_g2s(sVm, v.vmapP + kt0 * NFN, sizeof(int32_t) * kTile * NFN, &bar[0]);
-      bulk_g2s(sAff, v.aff + kt0 * kAW, sizeof(double) * kTile * kAW, &bar[0]);
-      bulk_g2s(sTag, v.facetag + kt0 * 3, kTile * 3, &bar[0]);
-      if (need_res) {
-        mbar_expect_tx(&bar[1], 3 * bq);
-        for (int f = 0; f < 3; ++f) bulk_g2s(sR + f * TNP, p.res + f * stride + base, bq, &bar[1]);
+  // ---- '+' traces that live outside the tile: issue the L2 gathers now, consume them in phase 2 ---------
+  double gP[NFB][3];
+  int rel[NFB];  // >= 0: tile-local node of the '+' trace; -1: gathered into gP; -2: wall; -3: no slot
+#pragma unroll
+  for (int kb = 0; kb < NFB; ++kb) {
+    const int sl = 4 * kb + t;
+    rel[kb] = -3;
+    gP[kb][0] = gP[kb][1] = gP[kb][2] = 0.0;
+    if (sl < NFN) {
+      const int tag = sTag[e * 3 + sl / NFP];
+      const long long mP = sVm[e * NFN + sl];
+      const long long r = mP - base;
+      if (tag == 3) {
+        rel[kb] = -2;
+      } else if (r >= 0 && r < tile_nodes) {
+        rel[kb] = (int)r;
+      } else {
+        rel[kb] = -1;
+        gP[kb][0] = __ldg(p.q_in + mP);
+        gP[kb][1] = __ldg(p.q_in + stride + mP);
+        gP[kb][2] = __ldg(p.q_in + 2 * stride + mP);
       }
     }
-  } else {  // ragged last tile: plain loads, neutral fill behind the mesh end
-    for (int x = tid; x < 3 * TNP; x += kThreads) {
-      const int f = x / TNP, r = x - f * TNP;
-      const bool in = r < nload * NP;
-      sQ[x] = in ? p.q_in[f * stride + base + r] : (f == 0 ? 1.0 : 0.0);
-      sR[x] = (in && need_res) ? p.res[f * stride + base + r] : 0.0;
-    }
-    for (int x = tid; x < kTile * NFN; x += kThreads) {
-      const int el = x / NFN, sl = x - el * NFN;
-      sVm[x] = el < nload ? v.vmapP[kt0 * NFN + x] : (int32_t)(base + el * NP + v.fmask[sl]);
-    }
-    for (int x = tid; x < kTile * kAW; x += kThreads) sAff[x] = x < nload * kAW ? v.aff[kt0 * kAW + x] : 0.0;
-    for (int x = tid; x < kTile * 3; x += kThreads) sTag[x] = x < nload * 3 ? v.facetag[kt0 * 3 + x] : 0;
   }
-  if (tid < NFN) sFm[tid] = v.fmask[tid];
-
-  // operator fragments: registers (small orders) or shared memory in fragment order
-  double Areg[C::A_REGS ? MB * KB : 1];
-  if (C::A_REGS) {
-#pragma unroll
-    for (int i = 0; i < MB * KB; ++i) Areg[i] = __ldg(p.Afrag + i * 32 + lane);
-  } else {
-    for (int x = tid; x < MB * KB * 32; x += kThreads) sA[x] = __ldg(p.Afrag + x);
-  }
-  const double g = v.g, half_g = 0.5 * v.g;
-
-  if (full_tile) mbar_wait(&bar[0], 0);
-  __syncthreads();
 
   // ---- phase 1: nodal fluxes and wave speed at my volume nodes (A6, A7 '-' side) ----------------------
-  const int eo = e * NP;
 #pragma unroll
   for (int kb = 0; kb < NPB; ++kb) {
     const int n = 4 * kb + t;
@@ -219,10 +222,8 @@ __global__ void __launch_bounds__(kThreads) k_fused_stage(Sw2dView v, StageArgs 
   __syncthreads();
 
   // ---- phase 2: face slots of my element: '+' trace, BC, speed, flux jump (A1-A8) ---------------------
-  const double *af = sAff + e * kAW;
   double fn[NFB][3], dq[NFB][3];  // normal flux differences and jumps per slot
   double lam0 = 0.0, lam1 = 0.0, lam2 = 0.0;  // per-face max speed (scalars: a runtime face index must not spill)
-  const int tile_nodes = nload * NP;
 #pragma unroll
   for (int kb = 0; kb < NFB; ++kb) {
     const int sl = 4 * kb + t;
@@ -234,25 +235,21 @@ __global__ void __launch_bounds__(kThreads) k_fused_stage(Sw2dView v, StageArgs 
       const double nx = af[4 + 3 * f], ny = af[5 + 3 * f];
       const double hM = sQ[eo + n], huM = sQ[TNP + eo + n], hvM = sQ[2 * TNP + eo + n];
       const double F2M = sFl[eo + n], G2M = sFl[TNP + eo + n], G3M = sFl[2 * TNP + eo + n], spdM = sFl[3 * TNP + eo + n];
-      const int tag = sTag[e * 3 + f];
-      const long long mP = sVm[e * NFN + sl];
-      const long long rel = mP - base;
-      const bool in_tile = rel >= 0 && rel < tile_nodes;
       double hP, huP, hvP, F2P, G2P, G3P, spdP;
-      if (in_tile && tag != 3) {  // neighbour inside the tile: everything is already in shared memory
-        const int r = (int)rel;
+      const int r = rel[kb];
+      if (r >= 0) {  // neighbour inside the tile: everything is already in shared memory
         hP = sQ[r]; huP = sQ[TNP + r]; hvP = sQ[2 * TNP + r];
         F2P = sFl[r]; G2P = sFl[TNP + r]; G3P = sFl[2 * TNP + r]; spdP = sFl[3 * TNP + r];
       } else {
-        if (tag == 3) {  // Wall (main.cpp:340-345)
+        if (r == -2) {  // Wall (main.cpp:340-345)
           const double d = huM * nx + hvM * ny;
           hP = hM;
           huP = fma(-2.0 * nx, d, huM);
           hvP = fma(-2.0 * ny, d, hvM);
-        } else {  // neighbour tile or ghost slot: L2 gather
-          hP = __ldg(p.q_in + mP); huP = __ldg(p.q_in + stride + mP); hvP = __ldg(p.q_in + 2 * stride + mP);
+        } else {  // neighbour tile or ghost slot
+          hP = gP[kb][0]; huP = gP[kb][1]; hvP = gP[kb][2];
         }
-        const double r = frcp(hP), u = huP * r, vv = hvP * r, gh2 = (half_g * hP) * hP;
+        const double rr = frcp(hP), u = huP * rr, vv = hvP * rr, gh2 = (half_g * hP) * hP;
         F2P = fma(huP, u, gh2); G2P = huP * vv; G3P = fma(hvP, vv, gh2);
         spdP = fsqrt(fma(u, u, vv * vv)) + fsqrt(g * hP);
       }
@@ -291,12 +288,11 @@ __global__ void __launch_bounds__(kThreads) k_fused_stage(Sw2dView v, StageArgs 
   // ---- phase 3: per field, B fragments -> DMMA -> stage update ------------------------------------------
   const double rx = af[0], sx = af[1], ry = af[2], sy = af[3];
   const double dt = p.write_rhs ? 0.0 : v.scal[S_DT];
-  if (full_tile && need_res) mbar_wait(&bar[1], 0);
   const int gr = lane >> 2;                       // C fragment row within a row block
   const int e0 = w + 4 * (2 * t), e1 = e0 + 4;    // C fragment columns 2t, 2t+1
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
-    const double *X = i == 0 ? sQ + TNP : (i == 1 ? sFl : sFl + TNP);          // F_i: hu, F2, G2
+    const double *X = i == 0 ? sQ + TNP : (i == 1 ? sFl : sFl + TNP);                // F_i: hu, F2, G2
     const double *Y = i == 0 ? sQ + 2 * TNP : (i == 1 ? sFl + TNP : sFl + 2 * TNP);  // G_i: hv, G2, G3
     double acc[MB][2];
 #pragma unroll
@@ -348,17 +344,77 @@ __global__ void __launch_bounds__(kThreads) k_fused_stage(Sw2dView v, StageArgs 
       }
     }
   }
+}
+
+template <int NP, int NFP>
+__device__ __forceinline__ void load_operator(const StageArgs &p, double *Areg, double *sA, int32_t *sFm, const Sw2dView &v) {
+  using C = Cfg<NP, NFP>;
+  const int tid = threadIdx.x, lane = tid & 31;
+  if (C::A_REGS) {
+#pragma unroll
+    for (int i = 0; i < C::MB * C::KB; ++i) Areg[i] = __ldg(p.Afrag + i * 32 + lane);
+  } else {
+    for (int x = tid; x < C::MB * C::KB * 32; x += kThreads) sA[x] = __ldg(p.Afrag + x);
+  }
+  if (tid < C::NFN) sFm[tid] = v.fmask[tid];
+}
+
+// ---- edge kernel: one tile per CTA, any tile (ragged mesh end, partially active range, write_rhs) -------
+template <int NP, int NFP>
+__global__ void __launch_bounds__(kThreads, 3) k_fused_edge(Sw2dView v, StageArgs p) {
+  using C = Cfg<NP, NFP>;
+  constexpr int NFN = C::NFN, TNP = C::TNP;
+  extern __shared__ __align__(128) unsigned char smem[];
+  const Smem<NP, NFP> S{smem, 1};
+  double *sQ = S.Q(0), *sR = S.R(0), *sAff = S.Aff(0);
+  int32_t *sVm = S.Vm(0);
+  uint8_t *sTag = S.Tag(0);
+  uint64_t *bar = S.Bar();
+
+  const int tid = threadIdx.x;
+  const long long kt0 = (long long)(p.tile0 + blockIdx.x) * kTile;
+  const int nload = (int)min((long long)kTile, (long long)v.K - kt0);
+  const bool full_tile = nload == kTile;
+  const bool all_active = full_tile && kt0 >= p.k0 && kt0 + kTile <= p.k1;
+  const bool need_res = !p.write_rhs && p.a != 0.0;
+  const long long stride = v.stride;
+  const long long base = kt0 * NP;
+
+  if (full_tile) {
+    if (tid == 0) {
+      mbar_init(&bar[0], 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      issue_tile_load<NP, NFP>(v, p, S, 0, kt0, need_res, &bar[0]);
+    }
+  } else {  // ragged last tile: plain loads, neutral fill behind the mesh end
+    for (int x = tid; x < 3 * TNP; x += kThreads) {
+      const int f = x / TNP, r = x - f * TNP;
+      const bool in = r < nload * NP;
+      sQ[x] = in ? p.q_in[f * stride + base + r] : (f == 0 ? 1.0 : 0.0);
+      sR[x] = (in && need_res) ? p.res[f * stride + base + r] : 0.0;
+    }
+    for (int x = tid; x < kTile * NFN; x += kThreads) {
+      const int el = x / NFN, sl = x - el * NFN;
+      sVm[x] = el < nload ? v.vmapP[kt0 * NFN + x] : (int32_t)(base + el * NP + v.fmask[sl]);
+    }
+    for (int x = tid; x < kTile * kAW; x += kThreads) sAff[x] = x < nload * kAW ? v.aff[kt0 * kAW + x] : 0.0;
+    for (int x = tid; x < kTile * 3; x += kThreads) sTag[x] = x < nload * 3 ? v.facetag[kt0 * 3 + x] : 0;
+  }
+  double Areg[C::A_REGS ? C::MB * C::KB : 1];
+  load_operator<NP, NFP>(p, Areg, S.A(), S.Fm(), v);
+  __syncthreads();  // mbarrier init + plain stores visible
+  if (full_tile) mbar_wait(&bar[0], 0);
+
+  compute_tile<NP, NFP>(v, p, sQ, sR, sAff, sVm, sTag, S.Fl(), S.A(), S.Fm(), Areg, kt0, nload, need_res);
   if (p.write_rhs) return;
 
-  // ---- write the tile back ----------------------------------------------------------------------------
   if (all_active) {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
     if (tid == 0) {
-      constexpr uint32_t bq = sizeof(double) * TNP;
       for (int f = 0; f < 3; ++f) {
-        bulk_s2g(p.q_out + f * stride + base, sQ + f * TNP, bq);
-        bulk_s2g(p.res + f * stride + base, sR + f * TNP, bq);
+        bulk_s2g(p.q_out + f * stride + base, sQ + f * TNP, C::txQ);
+        bulk_s2g(p.res + f * stride + base, sR + f * TNP, C::txQ);
       }
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
@@ -376,21 +432,99 @@ __global__ void __launch_bounds__(kThreads) k_fused_stage(Sw2dView v, StageArgs 
   }
 }
 
+// ---- persistent kernel: full, fully active tiles; two tile buffers, the next tile's TMA loads fly while
+// the current tile is computed; results leave through TMA bulk stores from the same buffer -----------------
+template <int NP, int NFP>
+__global__ void __launch_bounds__(kThreads, 3) k_fused_persistent(Sw2dView v, StageArgs p) {
+  using C = Cfg<NP, NFP>;
+  constexpr int TNP = C::TNP;
+  extern __shared__ __align__(128) unsigned char smem[];
+  const Smem<NP, NFP> S{smem, 2};
+  uint64_t *bar = S.Bar();
+  const int tid = threadIdx.x;
+  const bool need_res = p.a != 0.0;
+  const long long stride = v.stride;
+  const int nmine = (p.ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // tiles blockIdx.x + it*gridDim.x
+
+  if (tid == 0) {
+    mbar_init(&bar[0], 1);
+    mbar_init(&bar[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    for (int it = 0; it < 2 && it < nmine; ++it)
+      issue_tile_load<NP, NFP>(v, p, S, it, (long long)(p.tile0 + blockIdx.x + it * gridDim.x) * kTile, need_res, &bar[it]);
+  }
+  double Areg[C::A_REGS ? C::MB * C::KB : 1];
+  load_operator<NP, NFP>(p, Areg, S.A(), S.Fm(), v);
+  __syncthreads();
+
+  for (int it = 0; it < nmine; ++it) {
+    const int b = it & 1;
+    const long long kt0 = (long long)(p.tile0 + blockIdx.x + it * gridDim.x) * kTile;
+    mbar_wait(&bar[b], (it >> 1) & 1);
+    compute_tile<NP, NFP>(v, p, S.Q(b), S.R(b), S.Aff(b), S.Vm(b), S.Tag(b), S.Fl(), S.A(), S.Fm(), Areg, kt0, kTile, need_res);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    if (tid == 0) {
+      const long long base = kt0 * NP;
+      for (int f = 0; f < 3; ++f) {
+        bulk_s2g(p.q_out + f * stride + base, S.Q(b) + f * TNP, C::txQ);
+        bulk_s2g(p.res + f * stride + base, S.R(b) + f * TNP, C::txQ);
+      }
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // buffer b drained -> refill it
+      if (it + 2 < nmine)
+        issue_tile_load<NP, NFP>(v, p, S, b, (long long)(p.tile0 + blockIdx.x + (it + 2) * gridDim.x) * kTile, need_res, &bar[b]);
+    }
+  }
+}
+
 struct FusedOps {
   double *Afrag;
   int Np, Nfp;
 };
 
+int g_sm_count[16] = {};
+
 template <int NP, int NFP>
-cudaError_t launch_t(bdg_sw2d *s, const StageArgs &a, int ntiles) {
+cudaError_t launch_t(bdg_sw2d *s, StageArgs a) {
   using C = Cfg<NP, NFP>;
   static bool attr_set[16] = {};
-  if (!attr_set[s->device & 15]) {
-    cudaError_t e = cudaFuncSetAttribute(k_fused_stage<NP, NFP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::bytes);
-    if (e != cudaSuccess) return e;
-    attr_set[s->device & 15] = true;
+  static int ctas_per_sm[16] = {};
+  const int dev = s->device & 15;
+  const size_t smem_edge = C::total(1), smem_pers = C::total(2);
+  cudaError_t e;
+  if (!attr_set[dev]) {
+    if ((e = cudaFuncSetAttribute(k_fused_edge<NP, NFP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_edge)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_fused_persistent<NP, NFP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pers)) != cudaSuccess) return e;
+    cudaFuncSetAttribute(k_fused_edge<NP, NFP>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(k_fused_persistent<NP, NFP>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm[dev], k_fused_persistent<NP, NFP>, kThreads, smem_pers)) != cudaSuccess) return e;
+    if ((e = cudaDeviceGetAttribute(&g_sm_count[dev], cudaDevAttrMultiProcessorCount, s->device)) != cudaSuccess) return e;
+    if (ctas_per_sm[dev] < 1) return cudaErrorLaunchOutOfResources;
+    attr_set[dev] = true;
   }
-  k_fused_stage<NP, NFP><<<ntiles, kThreads, C::bytes, s->stream>>>(s->v, a);
+  // tiles [t0,t1) cover [k0,k1); the fully active ones [p0,p1) go to the persistent kernel (k1 <= K, so
+  // they are also full), ragged / partially active head and tail tiles to the edge kernel
+  const int t0 = a.k0 / kTile, t1 = (a.k1 - 1) / kTile + 1;
+  int p0 = (a.k0 + kTile - 1) / kTile, p1 = a.k1 / kTile;
+  if (a.write_rhs || p1 <= p0) p0 = p1 = t1;
+  auto edge = [&](int first, int last) {
+    if (last <= first) return;
+    StageArgs h = a;
+    h.tile0 = first; h.ntiles = last - first;
+    k_fused_edge<NP, NFP><<<h.ntiles, kThreads, smem_edge, s->stream>>>(s->v, h);
+    s->launches++;
+  };
+  edge(t0, p0);
+  if (p1 > p0) {
+    StageArgs m = a;
+    m.tile0 = p0; m.ntiles = p1 - p0;
+    int grid = g_sm_count[dev] * ctas_per_sm[dev];
+    if (grid > m.ntiles) grid = m.ntiles;
+    k_fused_persistent<NP, NFP><<<grid, kThreads, smem_pers, s->stream>>>(s->v, m);
+    s->launches++;
+  }
+  edge(p1, t1);
   return cudaGetLastError();
 }
 
@@ -474,12 +608,10 @@ cudaError_t launch_fused_stage(bdg_sw2d *s, const double *q_in, double *q_out, d
   if (!ops) return cudaErrorNotSupported;
   StageArgs args;
   args.q_in = q_in; args.q_out = q_out; args.res = res; args.rhs_out = rhs_out; args.Afrag = ops->Afrag;
-  args.k0 = k0; args.k1 = k1; args.tile0 = k0 / kTile;
+  args.k0 = k0; args.k1 = k1; args.tile0 = 0; args.ntiles = 0;
   args.write_rhs = write_rhs; args.slot = slot; args.a = a; args.b = b;
-  const int ntiles = (k1 - 1) / kTile - args.tile0 + 1;
-  s->launches++;
 #define X(np, nfp) \
-  if (ops->Np == np && ops->Nfp == nfp) return launch_t<np, nfp>(s, args, ntiles);
+  if (ops->Np == np && ops->Nfp == nfp) return launch_t<np, nfp>(s, args);
   BDG_FUSED_ORDERS(X)
 #undef X
   return cudaErrorNotSupported;
