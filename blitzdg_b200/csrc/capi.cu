@@ -327,9 +327,9 @@ static int create_impl(bdg_sw2d *s, const bdg_dgcontext2d *c, const bdg_sw2d_par
 
   s->fused_ok = 0;
   if (s->is_affine && face_uniform && !v.use_filter && fused_supported(s)) {
-    cudaError_t e = fused_prepare(s);
+    cudaError_t e = fused_prepare(s, c->Dr, c->Ds, c->Lift, c->vmapP, facetag.data());
     if (e != cudaSuccess) return fail(s, BDG_E_CUDA, "fused_prepare: %s", cudaGetErrorString(e));
-    s->fused_ok = 1;
+    s->fused_ok = s->fused_ops != nullptr;
   }
   CU(cudaStreamSynchronize(s->stream));
   return BDG_OK;

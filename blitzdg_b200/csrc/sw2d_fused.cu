@@ -4,22 +4,33 @@
 //   res = a*res + dt*RHS ; q += b*res                           (src/advec1d/main.cpp:98,101)
 // reading q/res once and writing them once (B_alg of SURVEY.md §8d).
 //
-// Mapping.  A CTA of 4 warps owns a tile of 32 consecutive elements; the tile's h,hu,hv,res,vmapP and
-// per-element geometry arrive in shared memory through 1-D TMA bulk copies (cp.async.bulk + mbarrier) and
-// the results leave the same way.  Because the element is affine,
+// Tiles.  A CTA of 4 warps works on tiles of 32 consecutive elements.  At create time every tile gets
+//   * a LOCAL trace map: for each face node the index of its '+' node inside the tile's node array, either one
+//     of the tile's own 32*Np nodes or one of the tile's GHOST nodes (the distinct '+' nodes that live in other
+//     tiles or in off-rank halo slots), packed with the face's BC tag in one 32-bit word, and
+//   * the ghost source list (global node ids).
+// A tile in shared memory is therefore a closed problem: h,hu,hv of own + ghost nodes, res, 13 geometry doubles
+// per element, the local map.  Own nodes / res / geometry / map arrive through 1-D TMA bulk copies
+// (cp.async.bulk + mbarrier), ghost nodes through 8-byte cp.async gathers from L2 that signal the same mbarrier;
+// results leave through TMA bulk stores.  The persistent kernel double-buffers tiles so the next tile's copies
+// and gathers fly while the current one is computed.
+//
+// Arithmetic.  Because the element is affine,
 //   RHS_i = -( Dr (rx F_i + ry G_i) + Ds (sx F_i + sy G_i) ) + LIFT (Fscale dF_i)
 // is one small GEMM  C[Np x cols] = A[Np x Kp] * B[Kp x cols]  with the constant operator
 //   A = [ -Dr | -Ds | LIFT ]   (each block padded to a multiple of 4 columns, rows to a multiple of 8)
-// and B assembled per (element, field) column from the pointwise fluxes.  The contraction runs on the fp64
-// tensor pipe (mma.sync.m8n8k4.f64 = DMMA), the operator fragments live in registers (N<=5) or in shared
-// memory in fragment order, and every thread computes its B fragment entries DIRECTLY in fragment layout:
-//   lane = 4*c + t  ->  element e = warp + 4*c of the tile (c = 0..7), nodes / face slots j = 4*kb + t.
-// The 4 lanes of a quad therefore hold all face nodes of one element and the per-face max of the wave speed
-// (sw2d-simple main.cpp:305-312) is two xor-shuffles.
+// run on the fp64 tensor pipe (mma.sync.m8n8k4.f64 = DMMA) with A fragments in registers (N<=4) or in shared
+// memory in fragment order.  Phase 1 evaluates nodal fluxes and wave speeds for own AND ghost nodes with a flat,
+// branch-free thread->node mapping; phase 2 builds the LIFT-part B fragments directly in fragment layout
+//   lane = 4*c + t  ->  element E(c) of the tile, face slots j = 4*kb + t
+// so the 4 lanes of a quad hold all face nodes of one element and the per-face max of the wave speed
+// (sw2d-simple main.cpp:305-312) is two xor-shuffles; phase 3 builds the volume B fragments, issues the DMMAs and
+// applies the stage update in place in shared memory.
 //
 // Deviations from the reference's operation order (inside the parity tolerance, SURVEY.md §7 hard part 1):
 // FMA contraction, x/h evaluated as x*(1/h) with a Newton-refined reciprocal, chain-rule factors applied
 // before the contraction (exact for affine elements up to round-off).
+#include <algorithm>
 #include <cstdio>
 #include <vector>
 
@@ -31,6 +42,7 @@ constexpr int kWarps = 4;
 constexpr int kThreads = kWarps * 32;
 constexpr int kTile = kWarps * 8;  // elements per CTA tile
 constexpr int kAW = 13;            // doubles per element in v.aff: rx,sx,ry,sy,(nx,ny,Fscale)x3
+constexpr int kGI = 5;             // ghost indices a thread can carry: Gmax <= kGI*kThreads
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -61,12 +73,21 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
 __device__ __forceinline__ void bulk_s2g(void *dst, const void *src, uint32_t bytes) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)), "r"(bytes) : "memory");
 }
+// 8-byte asynchronous gather global -> shared (LDGSTS); completion through cp_async_arrive on an mbarrier
+__device__ __forceinline__ void cp_async8(void *dst, const void *src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_arrive(uint64_t *bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 
 __device__ __forceinline__ void dmma884(double &d0, double &d1, double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
 
-// 1/x: MUFU seed (20+ bits) + two Newton steps -> <= 1 ulp-ish; no denormal / inf handling (h > 0 here)
+__device__ __forceinline__ double dmax(double a, double b) { return a > b ? a : b; }
+
+// 1/x: MUFU seed (20+ bits) + two Newton steps; no denormal / inf handling (h > 0 here)
 __device__ __forceinline__ double frcp(double x) {
   double r;
   asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
@@ -75,18 +96,16 @@ __device__ __forceinline__ double frcp(double x) {
   e = fma(-x, r, 1.0);
   return fma(r, e, r);
 }
-// sqrt(x), x >= 0 (0 maps to 1e-150): coupled Newton on (sqrt, 1/(2 sqrt)) from the MUFU rsqrt seed
+// sqrt(x), x > 0: coupled Newton on (sqrt, 1/(2 sqrt)) from the MUFU rsqrt seed, two final corrections
 __device__ __forceinline__ double fsqrt(double x) {
-  x = fmax(x, 1e-300);
   double r;
   asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
   double hh = 0.5 * r, s = x * r;
   double e = fma(-hh, s, 0.5);
   s = fma(s, e, s);
   hh = fma(hh, e, hh);
-  e = fma(-hh, s, 0.5);
-  s = fma(s, e, s);
-  hh = fma(hh, e, hh);
+  e = fma(-s, s, x);
+  s = fma(e, hh, s);
   e = fma(-s, s, x);
   return fma(e, hh, s);
 }
@@ -99,124 +118,98 @@ struct Cfg {
   static constexpr int KB = 2 * NPB + NFB;
   static constexpr int MB = (NP + 7) / 8;     // row blocks
   static constexpr bool A_REGS = (MB * KB <= 36);
-  static constexpr int TNP = kTile * NP;      // doubles per field per tile
-  // one tile buffer (bytes, every section 16-B aligned): q, res, geometry, vmapP, face tags
-  static constexpr size_t bQ = 0;
-  static constexpr size_t bR = bQ + sizeof(double) * 3 * TNP;
-  static constexpr size_t bAff = bR + sizeof(double) * 3 * TNP;
-  static constexpr size_t bVm = bAff + sizeof(double) * kTile * kAW;
-  static constexpr size_t bTag = bVm + sizeof(int32_t) * kTile * NFN;
-  static constexpr size_t BUF = bTag + ((kTile * 3 + 15) / 16) * 16;
+  static constexpr int TNP = kTile * NP;      // own nodes per tile
   static constexpr uint32_t txQ = sizeof(double) * TNP;  // one field plane of a tile
-  static constexpr uint32_t txMeta = sizeof(int32_t) * kTile * NFN + sizeof(double) * kTile * kAW + kTile * 3;
-  // CTA-wide sections behind NBUF tile buffers
-  static constexpr size_t sizeFl = sizeof(double) * 4 * TNP;
+  static constexpr uint32_t txMeta = sizeof(uint32_t) * kTile * NFN + sizeof(double) * kTile * kAW;
   static constexpr size_t sizeA = A_REGS ? 0 : sizeof(double) * MB * KB * 32;
-  static constexpr size_t sizeFm = ((sizeof(int32_t) * NFN + 15) / 16) * 16;
-  static constexpr size_t total(int nbuf) { return nbuf * BUF + sizeFl + sizeA + sizeFm + 64; }
+  // per tile buffer: Q[3][PS], Aff[kTile][13], Lm[kTile][NFN]; CTA-wide: R[3][TNP], Fl[4][PS], A, barriers
+  static size_t buf_bytes(int G) { return sizeof(double) * 3 * (TNP + G) + sizeof(double) * kTile * kAW + sizeof(uint32_t) * kTile * NFN; }
+  static size_t total(int nbuf, int G) { return nbuf * buf_bytes(G) + sizeof(double) * 3 * TNP + sizeof(double) * 4 * (TNP + G) + sizeA + 64; }
 };
 
 struct StageArgs {
   const double *q_in;
   double *q_out;
   double *res;
-  double *rhs_out;      // write_rhs mode: [3][nT]
-  const double *Afrag;  // [MB][KB][32] operator in DMMA A-fragment order
-  int k0, k1;           // active element range
-  int tile0, ntiles;    // tiles [tile0, tile0 + ntiles) of this launch
+  double *rhs_out;        // write_rhs mode: [3][nT]
+  const double *Afrag;    // [MB][KB][32] operator in DMMA A-fragment order
+  const uint32_t *lmap;   // [ntiles_all*kTile][NFN]: local '+' node (low 16 bits) | face tag << 16
+  const int32_t *gsrc;    // [ntiles_all][G]: global node ids of the tile's ghost nodes
+  int G;                  // ghost slots per tile (multiple of 8)
+  int k0, k1;             // active element range
+  int tile0, ntiles;      // tiles [tile0, tile0 + ntiles) of this launch
   int write_rhs;
-  int slot;             // scal slot of the global LF speed
-  double a, b;          // LSERK4 stage coefficients
+  int slot;               // scal slot of the global LF speed
+  double a, b;            // LSERK4 stage coefficients
 };
 
 template <int NP, int NFP>
 struct Smem {
   using C = Cfg<NP, NFP>;
   unsigned char *base;
-  int nbuf;
-  __device__ double *Q(int b) const { return reinterpret_cast<double *>(base + b * C::BUF + C::bQ); }
-  __device__ double *R(int b) const { return reinterpret_cast<double *>(base + b * C::BUF + C::bR); }
-  __device__ double *Aff(int b) const { return reinterpret_cast<double *>(base + b * C::BUF + C::bAff); }
-  __device__ int32_t *Vm(int b) const { return reinterpret_cast<int32_t *>(base + b * C::BUF + C::bVm); }
-  __device__ uint8_t *Tag(int b) const { return base + b * C::BUF + C::bTag; }
-  __device__ double *Fl() const { return reinterpret_cast<double *>(base + nbuf * C::BUF); }
-  __device__ double *A() const { return reinterpret_cast<double *>(base + nbuf * C::BUF + C::sizeFl); }
-  __device__ int32_t *Fm() const { return reinterpret_cast<int32_t *>(base + nbuf * C::BUF + C::sizeFl + C::sizeA); }
-  __device__ uint64_t *Bar() const { return reinterpret_cast<uint64_t *>(base + nbuf * C::BUF + C::sizeFl + C::sizeA + C::sizeFm); }
+  int nbuf, G;
+  __device__ int PS() const { return C::TNP + G; }
+  __device__ size_t bufb() const { return sizeof(double) * 3 * PS() + sizeof(double) * kTile * kAW + sizeof(uint32_t) * kTile * C::NFN; }
+  __device__ double *Q(int b) const { return reinterpret_cast<double *>(base + b * bufb()); }
+  __device__ double *Aff(int b) const { return Q(b) + 3 * PS(); }
+  __device__ uint32_t *Lm(int b) const { return reinterpret_cast<uint32_t *>(Aff(b) + kTile * kAW); }
+  __device__ double *R() const { return reinterpret_cast<double *>(base + nbuf * bufb()); }
+  __device__ double *Fl() const { return R() + 3 * C::TNP; }
+  __device__ double *A() const { return Fl() + 4 * PS(); }
+  __device__ uint64_t *Bar() const { return reinterpret_cast<uint64_t *>(reinterpret_cast<unsigned char *>(A()) + C::sizeA); }
 };
 
-// thread 0: TMA bulk loads of one full tile into buffer b, completion on bar
+// thread 0: TMA bulk loads of one full tile's own nodes, geometry and local map into buffer b
 template <int NP, int NFP>
-__device__ __forceinline__ void issue_tile_load(const Sw2dView &v, const StageArgs &p, const Smem<NP, NFP> &S, int b, long long kt0,
-                                                bool need_res, uint64_t *bar) {
+__device__ __forceinline__ void issue_tile_load(const Sw2dView &v, const StageArgs &p, const Smem<NP, NFP> &S, int b, long long tile,
+                                                uint64_t *bar) {
   using C = Cfg<NP, NFP>;
-  const long long base = kt0 * NP;
-  mbar_expect_tx(bar, (need_res ? 6 : 3) * C::txQ + C::txMeta);
-  bulk_g2s(S.Vm(b), v.vmapP + kt0 * C::NFN, sizeof(int32_t) * kTile * C::NFN, bar);
-  bulk_g2s(S.Tag(b), v.facetag + kt0 * 3, kTile * 3, bar);
+  const long long kt0 = tile * kTile, base = kt0 * NP;
+  mbar_expect_tx(bar, 3 * C::txQ + C::txMeta);
+  bulk_g2s(S.Lm(b), p.lmap + kt0 * C::NFN, sizeof(uint32_t) * kTile * C::NFN, bar);
   bulk_g2s(S.Aff(b), v.aff + kt0 * kAW, sizeof(double) * kTile * kAW, bar);
-  for (int f = 0; f < 3; ++f) bulk_g2s(S.Q(b) + f * C::TNP, p.q_in + f * v.stride + base, C::txQ, bar);
-  if (need_res)
-    for (int f = 0; f < 3; ++f) bulk_g2s(S.R(b) + f * C::TNP, p.res + f * v.stride + base, C::txQ, bar);
+  for (int f = 0; f < 3; ++f) bulk_g2s(S.Q(b) + f * S.PS(), p.q_in + f * v.stride + base, C::txQ, bar);
+}
+template <int NP, int NFP>
+__device__ __forceinline__ void issue_res_load(const Sw2dView &v, const StageArgs &p, const Smem<NP, NFP> &S, long long tile, uint64_t *bar) {
+  using C = Cfg<NP, NFP>;
+  const long long base = tile * kTile * NP;
+  mbar_expect_tx(bar, 3 * C::txQ);
+  for (int f = 0; f < 3; ++f) bulk_g2s(S.R() + f * C::TNP, p.res + f * v.stride + base, C::txQ, bar);
 }
 
-// The arithmetic of one tile that sits in shared memory (A1-A13 of SURVEY.md Appendix A).  On return the
-// tile's q and res planes hold the updated values (stage mode) -- or, in write_rhs mode, rhs_out has been
-// written and the tile is untouched.  Contains two __syncthreads(); the caller makes the tile visible first.
+// The arithmetic of one tile that sits in shared memory (A1-A13 of SURVEY.md Appendix A).  sQ: [3][PS] own +
+// ghost nodes, sR: [3][TNP].  On return the tile's q and res planes hold the updated values (stage mode) -- or,
+// in write_rhs mode, rhs_out has been written and the tile is untouched.  Contains two __syncthreads() and an
+// optional wait on the res barrier before phase 3; the caller makes the tile visible first.
 template <int NP, int NFP>
 __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs &p, double *__restrict__ sQ, double *__restrict__ sR,
-                                             const double *__restrict__ sAff, const int32_t *__restrict__ sVm,
-                                             const uint8_t *__restrict__ sTag, double *__restrict__ sFl, const double *__restrict__ sA,
-                                             const int32_t *__restrict__ sFm, const double *Areg, long long kt0, int nload,
-                                             bool need_res) {
+                                             const double *__restrict__ sAff, const uint32_t *__restrict__ sLm, double *__restrict__ sFl,
+                                             const double *__restrict__ sA, const double *Areg, const int *fm, int PS, long long kt0,
+                                             bool need_res, uint64_t *bar_res, uint32_t res_parity) {
   using C = Cfg<NP, NFP>;
   constexpr int NFN = C::NFN, NPB = C::NPB, NFB = C::NFB, KB = C::KB, MB = C::MB, TNP = C::TNP;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int c = lane >> 2, t = lane & 3;
-  const int e = w + 4 * c;  // my element of the tile (B-fragment column c)
+  const int e = w + 4 * (c < 4 ? c : (c ^ 1));  // my element (B-fragment column c); E(c) keeps B and C accesses conflict-free
   const int eo = e * NP;
-  const long long stride = v.stride;
-  const long long base = kt0 * NP;  // first volume node of the tile
-  const int tile_nodes = nload * NP;
   const double g = v.g, half_g = 0.5 * v.g;
   const double *af = sAff + e * kAW;
 
-  // ---- '+' traces that live outside the tile: issue the L2 gathers now, consume them in phase 2 ---------
-  double gP[NFB][3];
-  int rel[NFB];  // >= 0: tile-local node of the '+' trace; -1: gathered into gP; -2: wall; -3: no slot
+  // ---- phase 1: nodal fluxes and wave speed at own and ghost nodes (A6, A7), flat mapping ------------------
+#pragma unroll 1
+  for (int j0 = threadIdx.x; j0 < PS; j0 += 3 * kThreads) {
 #pragma unroll
-  for (int kb = 0; kb < NFB; ++kb) {
-    const int sl = 4 * kb + t;
-    rel[kb] = -3;
-    gP[kb][0] = gP[kb][1] = gP[kb][2] = 0.0;
-    if (sl < NFN) {
-      const int tag = sTag[e * 3 + sl / NFP];
-      const long long mP = sVm[e * NFN + sl];
-      const long long r = mP - base;
-      if (tag == 3) {
-        rel[kb] = -2;
-      } else if (r >= 0 && r < tile_nodes) {
-        rel[kb] = (int)r;
-      } else {
-        rel[kb] = -1;
-        gP[kb][0] = __ldg(p.q_in + mP);
-        gP[kb][1] = __ldg(p.q_in + stride + mP);
-        gP[kb][2] = __ldg(p.q_in + 2 * stride + mP);
+    for (int u3 = 0; u3 < 3; ++u3) {
+      const int j = j0 + u3 * kThreads;
+      if (j < PS) {
+        const double h = sQ[j], hu = sQ[PS + j], hv = sQ[2 * PS + j];
+        const double r = frcp(h), u = hu * r, vv = hv * r, gh2 = (half_g * h) * h;
+        sFl[j] = fma(hu, u, gh2);            // F2
+        sFl[PS + j] = hu * vv;               // G2 = F3
+        sFl[2 * PS + j] = fma(hv, vv, gh2);  // G3
+        sFl[3 * PS + j] = fsqrt(fma(u, u, fma(vv, vv, 1e-300))) + fsqrt(g * h);
       }
-    }
-  }
-
-  // ---- phase 1: nodal fluxes and wave speed at my volume nodes (A6, A7 '-' side) ----------------------
-#pragma unroll
-  for (int kb = 0; kb < NPB; ++kb) {
-    const int n = 4 * kb + t;
-    if (n < NP) {
-      const double h = sQ[eo + n], hu = sQ[TNP + eo + n], hv = sQ[2 * TNP + eo + n];
-      const double r = frcp(h), u = hu * r, vv = hv * r, gh2 = (half_g * h) * h;
-      sFl[eo + n] = fma(hu, u, gh2);            // F2
-      sFl[TNP + eo + n] = hu * vv;              // G2 = F3
-      sFl[2 * TNP + eo + n] = fma(hv, vv, gh2); // G3
-      sFl[3 * TNP + eo + n] = fsqrt(fma(u, u, vv * vv)) + fsqrt(g * h);
     }
   }
   __syncthreads();
@@ -231,47 +224,43 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
     dq[kb][0] = dq[kb][1] = dq[kb][2] = 0.0;
     if (sl < NFN) {
       const int f = sl / NFP;
-      const int n = sFm[sl];
+      const int m = eo + fm[kb];
+      const uint32_t word = sLm[e * NFN + sl];
+      const int r = word & 0xffffu;
       const double nx = af[4 + 3 * f], ny = af[5 + 3 * f];
-      const double hM = sQ[eo + n], huM = sQ[TNP + eo + n], hvM = sQ[2 * TNP + eo + n];
-      const double F2M = sFl[eo + n], G2M = sFl[TNP + eo + n], G3M = sFl[2 * TNP + eo + n], spdM = sFl[3 * TNP + eo + n];
-      double hP, huP, hvP, F2P, G2P, G3P, spdP;
-      const int r = rel[kb];
-      if (r >= 0) {  // neighbour inside the tile: everything is already in shared memory
-        hP = sQ[r]; huP = sQ[TNP + r]; hvP = sQ[2 * TNP + r];
-        F2P = sFl[r]; G2P = sFl[TNP + r]; G3P = sFl[2 * TNP + r]; spdP = sFl[3 * TNP + r];
-      } else {
-        if (r == -2) {  // Wall (main.cpp:340-345)
-          const double d = huM * nx + hvM * ny;
-          hP = hM;
-          huP = fma(-2.0 * nx, d, huM);
-          hvP = fma(-2.0 * ny, d, hvM);
-        } else {  // neighbour tile or ghost slot
-          hP = gP[kb][0]; huP = gP[kb][1]; hvP = gP[kb][2];
-        }
+      const double hM = sQ[m], huM = sQ[PS + m], hvM = sQ[2 * PS + m];
+      const double F2M = sFl[m], G2M = sFl[PS + m], G3M = sFl[2 * PS + m], spdM = sFl[3 * PS + m];
+      double hP = sQ[r], huP = sQ[PS + r], hvP = sQ[2 * PS + r];
+      double F2P = sFl[r], G2P = sFl[PS + r], G3P = sFl[2 * PS + r], spdP = sFl[3 * PS + r];
+      if ((word >> 16) == 3u) {  // Wall (main.cpp:340-345): reflect the normal momentum of the '-' trace
+        const double d = huM * nx + hvM * ny;
+        hP = hM;
+        huP = fma(-2.0 * nx, d, huM);
+        hvP = fma(-2.0 * ny, d, hvM);
         const double rr = frcp(hP), u = huP * rr, vv = hvP * rr, gh2 = (half_g * hP) * hP;
         F2P = fma(huP, u, gh2); G2P = huP * vv; G3P = fma(hvP, vv, gh2);
-        spdP = fsqrt(fma(u, u, vv * vv)) + fsqrt(g * hP);
+        spdP = fsqrt(fma(u, u, fma(vv, vv, 1e-300))) + fsqrt(g * hP);
       }
-      const double sp = fmax(spdM, spdP);
-      lam0 = f == 0 ? fmax(lam0, sp) : lam0;
-      lam1 = f == 1 ? fmax(lam1, sp) : lam1;
-      lam2 = f == 2 ? fmax(lam2, sp) : lam2;
+      const double sp = dmax(spdM, spdP);
+      lam0 = f == 0 ? dmax(lam0, sp) : lam0;
+      lam1 = f == 1 ? dmax(lam1, sp) : lam1;
+      lam2 = f == 2 ? dmax(lam2, sp) : lam2;
       dq[kb][0] = hM - hP; dq[kb][1] = huM - huP; dq[kb][2] = hvM - hvP;
+      const double dG2 = G2M - G2P;
       fn[kb][0] = fma(dq[kb][1], nx, dq[kb][2] * ny);
-      fn[kb][1] = fma(F2M - F2P, nx, (G2M - G2P) * ny);
-      fn[kb][2] = fma(G2M - G2P, nx, (G3M - G3P) * ny);
+      fn[kb][1] = fma(F2M - F2P, nx, dG2 * ny);
+      fn[kb][2] = fma(dG2, nx, (G3M - G3P) * ny);
     }
   }
   if (v.lf_global) {
     lam0 = lam1 = lam2 = v.scal[p.slot];
   } else {  // per-face max over the quad (the 4 lanes of a quad hold all face nodes of element e)
-    lam0 = fmax(lam0, __shfl_xor_sync(0xffffffffu, lam0, 1));
-    lam1 = fmax(lam1, __shfl_xor_sync(0xffffffffu, lam1, 1));
-    lam2 = fmax(lam2, __shfl_xor_sync(0xffffffffu, lam2, 1));
-    lam0 = fmax(lam0, __shfl_xor_sync(0xffffffffu, lam0, 2));
-    lam1 = fmax(lam1, __shfl_xor_sync(0xffffffffu, lam1, 2));
-    lam2 = fmax(lam2, __shfl_xor_sync(0xffffffffu, lam2, 2));
+    lam0 = dmax(lam0, __shfl_xor_sync(0xffffffffu, lam0, 1));
+    lam1 = dmax(lam1, __shfl_xor_sync(0xffffffffu, lam1, 1));
+    lam2 = dmax(lam2, __shfl_xor_sync(0xffffffffu, lam2, 1));
+    lam0 = dmax(lam0, __shfl_xor_sync(0xffffffffu, lam0, 2));
+    lam1 = dmax(lam1, __shfl_xor_sync(0xffffffffu, lam1, 2));
+    lam2 = dmax(lam2, __shfl_xor_sync(0xffffffffu, lam2, 2));
   }
   double sfl[NFB][3];  // Fscale * dFlux_i at my slots = LIFT-part B fragments
 #pragma unroll
@@ -288,15 +277,18 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   // ---- phase 3: per field, B fragments -> DMMA -> stage update ------------------------------------------
   const double rx = af[0], sx = af[1], ry = af[2], sy = af[3];
   const double dt = p.write_rhs ? 0.0 : v.scal[S_DT];
-  const int gr = lane >> 2;                       // C fragment row within a row block
-  const int e0 = w + 4 * (2 * t), e1 = e0 + 4;    // C fragment columns 2t, 2t+1
+  if (bar_res) mbar_wait(bar_res, res_parity);
+  const int gr = lane >> 2;  // C fragment row within a row block
+  const int c0 = 2 * t, c1 = 2 * t + 1;
+  const int e0 = w + 4 * (c0 < 4 ? c0 : (c0 ^ 1));  // C fragment column 2t   -> element E(2t)
+  const int e1 = w + 4 * (c1 < 4 ? c1 : (c1 ^ 1));  // C fragment column 2t+1 -> element E(2t+1)
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
-    const double *X = i == 0 ? sQ + TNP : (i == 1 ? sFl : sFl + TNP);                // F_i: hu, F2, G2
-    const double *Y = i == 0 ? sQ + 2 * TNP : (i == 1 ? sFl + TNP : sFl + 2 * TNP);  // G_i: hv, G2, G3
-    double acc[MB][2];
+    const double *X = i == 0 ? sQ + PS : (i == 1 ? sFl : sFl + PS);               // F_i: hu, F2, G2
+    const double *Y = i == 0 ? sQ + 2 * PS : (i == 1 ? sFl + PS : sFl + 2 * PS);  // G_i: hv, G2, G3
+    double acc[MB][2][2];  // two independent DMMA chains per row block
 #pragma unroll
-    for (int rb = 0; rb < MB; ++rb) acc[rb][0] = acc[rb][1] = 0.0;
+    for (int rb = 0; rb < MB; ++rb) acc[rb][0][0] = acc[rb][0][1] = acc[rb][1][0] = acc[rb][1][1] = 0.0;
 #pragma unroll
     for (int kb = 0; kb < NPB; ++kb) {
       const int n = 4 * kb + t;
@@ -310,8 +302,8 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
       for (int rb = 0; rb < MB; ++rb) {
         const double a1 = C::A_REGS ? Areg[rb * KB + kb] : sA[(rb * KB + kb) * 32 + lane];
         const double a2 = C::A_REGS ? Areg[rb * KB + NPB + kb] : sA[(rb * KB + NPB + kb) * 32 + lane];
-        dmma884(acc[rb][0], acc[rb][1], a1, ba);
-        dmma884(acc[rb][0], acc[rb][1], a2, bb);
+        dmma884(acc[rb][0][0], acc[rb][0][1], a1, ba);
+        dmma884(acc[rb][1][0], acc[rb][1][1], a2, bb);
       }
     }
 #pragma unroll
@@ -319,7 +311,7 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
 #pragma unroll
       for (int rb = 0; rb < MB; ++rb) {
         const double a3 = C::A_REGS ? Areg[rb * KB + 2 * NPB + kb] : sA[(rb * KB + 2 * NPB + kb) * 32 + lane];
-        dmma884(acc[rb][0], acc[rb][1], a3, sfl[kb][i]);
+        dmma884(acc[rb][kb & 1][0], acc[rb][kb & 1][1], a3, sfl[kb][i]);
       }
     }
     // epilogue: rows n = 8*rb + gr of elements e0, e1
@@ -330,7 +322,7 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
 #pragma unroll
         for (int cc = 0; cc < 2; ++cc) {
           const int o = (cc ? e1 : e0) * NP + n;
-          const double rhs = acc[rb][cc];
+          const double rhs = acc[rb][0][cc] + acc[rb][1][cc];
           if (p.write_rhs) {
             const long long k = kt0 + (cc ? e1 : e0);
             if (k >= p.k0 && k < p.k1) p.rhs_out[(long long)i * NP * v.K + k * NP + n] = rhs;
@@ -338,7 +330,7 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
             double rs = dt * rhs;
             if (need_res) rs = fma(p.a, sR[i * TNP + o], rs);
             sR[i * TNP + o] = rs;
-            sQ[i * TNP + o] = fma(p.b, rs, sQ[i * TNP + o]);
+            sQ[i * PS + o] = fma(p.b, rs, sQ[i * PS + o]);
           }
         }
       }
@@ -346,8 +338,9 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   }
 }
 
+// per-thread constants: operator fragments, '-' node offsets of my face slots
 template <int NP, int NFP>
-__device__ __forceinline__ void load_operator(const StageArgs &p, double *Areg, double *sA, int32_t *sFm, const Sw2dView &v) {
+__device__ __forceinline__ void load_constants(const StageArgs &p, const Sw2dView &v, double *Areg, double *sA, int *fm) {
   using C = Cfg<NP, NFP>;
   const int tid = threadIdx.x, lane = tid & 31;
   if (C::A_REGS) {
@@ -356,7 +349,11 @@ __device__ __forceinline__ void load_operator(const StageArgs &p, double *Areg, 
   } else {
     for (int x = tid; x < C::MB * C::KB * 32; x += kThreads) sA[x] = __ldg(p.Afrag + x);
   }
-  if (tid < C::NFN) sFm[tid] = v.fmask[tid];
+#pragma unroll
+  for (int kb = 0; kb < C::NFB; ++kb) {
+    const int sl = 4 * kb + (lane & 3);
+    fm[kb] = sl < C::NFN ? __ldg(v.fmask + sl) : 0;
+  }
 }
 
 // ---- edge kernel: one tile per CTA, any tile (ragged mesh end, partially active range, write_rhs) -------
@@ -365,47 +362,39 @@ __global__ void __launch_bounds__(kThreads, 3) k_fused_edge(Sw2dView v, StageArg
   using C = Cfg<NP, NFP>;
   constexpr int NFN = C::NFN, TNP = C::TNP;
   extern __shared__ __align__(128) unsigned char smem[];
-  const Smem<NP, NFP> S{smem, 1};
-  double *sQ = S.Q(0), *sR = S.R(0), *sAff = S.Aff(0);
-  int32_t *sVm = S.Vm(0);
-  uint8_t *sTag = S.Tag(0);
-  uint64_t *bar = S.Bar();
+  const Smem<NP, NFP> S{smem, 1, p.G};
+  const int PS = S.PS();
+  double *sQ = S.Q(0), *sR = S.R(), *sAff = S.Aff(0);
+  uint32_t *sLm = S.Lm(0);
 
   const int tid = threadIdx.x;
-  const long long kt0 = (long long)(p.tile0 + blockIdx.x) * kTile;
+  const long long tile = p.tile0 + blockIdx.x;
+  const long long kt0 = tile * kTile;
   const int nload = (int)min((long long)kTile, (long long)v.K - kt0);
-  const bool full_tile = nload == kTile;
-  const bool all_active = full_tile && kt0 >= p.k0 && kt0 + kTile <= p.k1;
+  const bool all_active = nload == kTile && kt0 >= p.k0 && kt0 + kTile <= p.k1;
   const bool need_res = !p.write_rhs && p.a != 0.0;
   const long long stride = v.stride;
   const long long base = kt0 * NP;
 
-  if (full_tile) {
-    if (tid == 0) {
-      mbar_init(&bar[0], 1);
-      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-      issue_tile_load<NP, NFP>(v, p, S, 0, kt0, need_res, &bar[0]);
-    }
-  } else {  // ragged last tile: plain loads, neutral fill behind the mesh end
-    for (int x = tid; x < 3 * TNP; x += kThreads) {
-      const int f = x / TNP, r = x - f * TNP;
-      const bool in = r < nload * NP;
-      sQ[x] = in ? p.q_in[f * stride + base + r] : (f == 0 ? 1.0 : 0.0);
-      sR[x] = (in && need_res) ? p.res[f * stride + base + r] : 0.0;
-    }
-    for (int x = tid; x < kTile * NFN; x += kThreads) {
-      const int el = x / NFN, sl = x - el * NFN;
-      sVm[x] = el < nload ? v.vmapP[kt0 * NFN + x] : (int32_t)(base + el * NP + v.fmask[sl]);
-    }
-    for (int x = tid; x < kTile * kAW; x += kThreads) sAff[x] = x < nload * kAW ? v.aff[kt0 * kAW + x] : 0.0;
-    for (int x = tid; x < kTile * 3; x += kThreads) sTag[x] = x < nload * 3 ? v.facetag[kt0 * 3 + x] : 0;
+  // plain loads; neutral fill (h = 1) behind the mesh end; lmap / gsrc are padded to whole tiles at create
+  for (int x = tid; x < 3 * TNP; x += kThreads) {
+    const int f = x / TNP, r = x - f * TNP;
+    const bool in = r < nload * NP;
+    sQ[f * PS + r] = in ? p.q_in[f * stride + base + r] : (f == 0 ? 1.0 : 0.0);
+    sR[x] = (in && need_res) ? p.res[f * stride + base + r] : 0.0;
   }
+  for (int x = tid; x < p.G; x += kThreads) {
+    const long long m = p.gsrc[tile * p.G + x];
+    for (int f = 0; f < 3; ++f) sQ[f * PS + TNP + x] = p.q_in[f * stride + m];
+  }
+  for (int x = tid; x < kTile * NFN; x += kThreads) sLm[x] = p.lmap[kt0 * NFN + x];
+  for (int x = tid; x < kTile * kAW; x += kThreads) sAff[x] = x < nload * kAW ? v.aff[kt0 * kAW + x] : 0.0;
   double Areg[C::A_REGS ? C::MB * C::KB : 1];
-  load_operator<NP, NFP>(p, Areg, S.A(), S.Fm(), v);
-  __syncthreads();  // mbarrier init + plain stores visible
-  if (full_tile) mbar_wait(&bar[0], 0);
+  int fm[C::NFB];
+  load_constants<NP, NFP>(p, v, Areg, S.A(), fm);
+  __syncthreads();
 
-  compute_tile<NP, NFP>(v, p, sQ, sR, sAff, sVm, sTag, S.Fl(), S.A(), S.Fm(), Areg, kt0, nload, need_res);
+  compute_tile<NP, NFP>(v, p, sQ, sR, sAff, sLm, S.Fl(), S.A(), Areg, fm, PS, kt0, need_res, nullptr, 0);
   if (p.write_rhs) return;
 
   if (all_active) {
@@ -413,7 +402,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_fused_edge(Sw2dView v, StageArg
     __syncthreads();
     if (tid == 0) {
       for (int f = 0; f < 3; ++f) {
-        bulk_s2g(p.q_out + f * stride + base, sQ + f * TNP, C::txQ);
+        bulk_s2g(p.q_out + f * stride + base, sQ + f * PS, C::txQ);
         bulk_s2g(p.res + f * stride + base, sR + f * TNP, C::txQ);
       }
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
@@ -425,61 +414,112 @@ __global__ void __launch_bounds__(kThreads, 3) k_fused_edge(Sw2dView v, StageArg
       const int f = x / TNP, r = x - f * TNP;
       const long long k = kt0 + r / NP;
       if (k >= p.k0 && k < p.k1) {
-        p.q_out[f * stride + base + r] = sQ[x];
+        p.q_out[f * stride + base + r] = sQ[f * PS + r];
         p.res[f * stride + base + r] = sR[x];
       }
     }
   }
 }
 
-// ---- persistent kernel: full, fully active tiles; two tile buffers, the next tile's TMA loads fly while
-// the current tile is computed; results leave through TMA bulk stores from the same buffer -----------------
+// ---- persistent kernel: full, fully active tiles; two tile buffers.  While tile `it` is computed, the TMA
+// copies of tile it+1 (issued at the end of iteration it-1) and its ghost gathers (issued at the top of
+// iteration it) are in flight; results leave through TMA bulk stores from the same buffer. -------------------
 template <int NP, int NFP>
 __global__ void __launch_bounds__(kThreads, 3) k_fused_persistent(Sw2dView v, StageArgs p) {
   using C = Cfg<NP, NFP>;
   constexpr int TNP = C::TNP;
   extern __shared__ __align__(128) unsigned char smem[];
-  const Smem<NP, NFP> S{smem, 2};
-  uint64_t *bar = S.Bar();
+  const Smem<NP, NFP> S{smem, 2, p.G};
+  const int PS = S.PS(), G = p.G;
+  uint64_t *bar = S.Bar();  // [0],[1]: tile buffers (1 expect_tx arrival + kThreads cp.async arrivals); [2]: res
   const int tid = threadIdx.x;
   const bool need_res = p.a != 0.0;
   const long long stride = v.stride;
   const int nmine = (p.ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // tiles blockIdx.x + it*gridDim.x
+  auto tile_of = [&](int it) { return (long long)p.tile0 + blockIdx.x + (long long)it * gridDim.x; };
 
   if (tid == 0) {
-    mbar_init(&bar[0], 1);
-    mbar_init(&bar[1], 1);
+    mbar_init(&bar[0], 1 + kThreads);
+    mbar_init(&bar[1], 1 + kThreads);
+    mbar_init(&bar[2], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    for (int it = 0; it < 2 && it < nmine; ++it)
-      issue_tile_load<NP, NFP>(v, p, S, it, (long long)(p.tile0 + blockIdx.x + it * gridDim.x) * kTile, need_res, &bar[it]);
+  }
+  __syncthreads();
+  if (tid == 0) {
+    issue_tile_load<NP, NFP>(v, p, S, 0, tile_of(0), &bar[0]);
+    if (nmine > 1) issue_tile_load<NP, NFP>(v, p, S, 1, tile_of(1), &bar[1]);
+    if (need_res) issue_res_load<NP, NFP>(v, p, S, tile_of(0), &bar[2]);
+  }
+  // ghost gathers of my first tile; ghost ids of my second tile into registers
+  int gi[kGI];
+  {
+    const int32_t *gs = p.gsrc + tile_of(0) * G;
+    double *dst = S.Q(0) + TNP;
+#pragma unroll
+    for (int u = 0; u < kGI; ++u) {
+      const int x = tid + u * kThreads;
+      gi[u] = 0;
+      if (x < G) {
+        const long long m = __ldg(gs + x);
+        for (int f = 0; f < 3; ++f) cp_async8(dst + f * PS + x, p.q_in + f * stride + m);
+      }
+    }
+    cp_async_arrive(&bar[0]);
+    if (nmine > 1) {
+      const int32_t *gs1 = p.gsrc + tile_of(1) * G;
+#pragma unroll
+      for (int u = 0; u < kGI; ++u)
+        if (tid + u * kThreads < G) gi[u] = __ldg(gs1 + tid + u * kThreads);
+    }
   }
   double Areg[C::A_REGS ? C::MB * C::KB : 1];
-  load_operator<NP, NFP>(p, Areg, S.A(), S.Fm(), v);
+  int fm[C::NFB];
+  load_constants<NP, NFP>(p, v, Areg, S.A(), fm);
   __syncthreads();
 
   for (int it = 0; it < nmine; ++it) {
     const int b = it & 1;
-    const long long kt0 = (long long)(p.tile0 + blockIdx.x + it * gridDim.x) * kTile;
+    const long long kt0 = tile_of(it) * kTile;
+    if (it + 1 < nmine) {  // ghost gathers of the next tile into the other buffer, ids of the one after into registers
+      double *dst = S.Q(b ^ 1) + TNP;
+#pragma unroll
+      for (int u = 0; u < kGI; ++u) {
+        const int x = tid + u * kThreads;
+        if (x < G)
+          for (int f = 0; f < 3; ++f) cp_async8(dst + f * PS + x, p.q_in + f * stride + gi[u]);
+      }
+      cp_async_arrive(&bar[b ^ 1]);
+      if (it + 2 < nmine) {
+        const int32_t *gs2 = p.gsrc + tile_of(it + 2) * G;
+#pragma unroll
+        for (int u = 0; u < kGI; ++u)
+          if (tid + u * kThreads < G) gi[u] = __ldg(gs2 + tid + u * kThreads);
+      }
+    }
     mbar_wait(&bar[b], (it >> 1) & 1);
-    compute_tile<NP, NFP>(v, p, S.Q(b), S.R(b), S.Aff(b), S.Vm(b), S.Tag(b), S.Fl(), S.A(), S.Fm(), Areg, kt0, kTile, need_res);
+    compute_tile<NP, NFP>(v, p, S.Q(b), S.R(), S.Aff(b), S.Lm(b), S.Fl(), S.A(), Areg, fm, PS, kt0, need_res, need_res ? &bar[2] : nullptr,
+                          it & 1);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
     if (tid == 0) {
       const long long base = kt0 * NP;
       for (int f = 0; f < 3; ++f) {
-        bulk_s2g(p.q_out + f * stride + base, S.Q(b) + f * TNP, C::txQ);
-        bulk_s2g(p.res + f * stride + base, S.R(b) + f * TNP, C::txQ);
+        bulk_s2g(p.q_out + f * stride + base, S.Q(b) + f * PS, C::txQ);
+        bulk_s2g(p.res + f * stride + base, S.R() + f * TNP, C::txQ);
       }
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-      asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // buffer b drained -> refill it
-      if (it + 2 < nmine)
-        issue_tile_load<NP, NFP>(v, p, S, b, (long long)(p.tile0 + blockIdx.x + (it + 2) * gridDim.x) * kTile, need_res, &bar[b]);
+      asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // buffer b and R drained -> refill them
+      if (it + 2 < nmine) issue_tile_load<NP, NFP>(v, p, S, b, tile_of(it + 2), &bar[b]);
+      if (need_res && it + 1 < nmine) issue_res_load<NP, NFP>(v, p, S, tile_of(it + 1), &bar[2]);
     }
   }
 }
 
 struct FusedOps {
   double *Afrag;
+  uint32_t *lmap;
+  int32_t *gsrc;
+  int G;
   int Np, Nfp;
 };
 
@@ -488,12 +528,12 @@ int g_sm_count[16] = {};
 template <int NP, int NFP>
 cudaError_t launch_t(bdg_sw2d *s, StageArgs a) {
   using C = Cfg<NP, NFP>;
-  static bool attr_set[16] = {};
   static int ctas_per_sm[16] = {};
+  static int attr_G[16] = {};
   const int dev = s->device & 15;
-  const size_t smem_edge = C::total(1), smem_pers = C::total(2);
+  const size_t smem_edge = C::total(1, a.G), smem_pers = C::total(2, a.G);
   cudaError_t e;
-  if (!attr_set[dev]) {
+  if (attr_G[dev] != a.G + 1) {
     if ((e = cudaFuncSetAttribute(k_fused_edge<NP, NFP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_edge)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_fused_persistent<NP, NFP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pers)) != cudaSuccess) return e;
     cudaFuncSetAttribute(k_fused_edge<NP, NFP>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -501,7 +541,7 @@ cudaError_t launch_t(bdg_sw2d *s, StageArgs a) {
     if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm[dev], k_fused_persistent<NP, NFP>, kThreads, smem_pers)) != cudaSuccess) return e;
     if ((e = cudaDeviceGetAttribute(&g_sm_count[dev], cudaDevAttrMultiProcessorCount, s->device)) != cudaSuccess) return e;
     if (ctas_per_sm[dev] < 1) return cudaErrorLaunchOutOfResources;
-    attr_set[dev] = true;
+    attr_G[dev] = a.G + 1;
   }
   // tiles [t0,t1) cover [k0,k1); the fully active ones [p0,p1) go to the persistent kernel (k1 <= K, so
   // they are also full), ragged / partially active head and tail tiles to the edge kernel
@@ -567,25 +607,78 @@ int fused_supported(const bdg_sw2d *s) {
   return 0;
 }
 
-cudaError_t fused_prepare(bdg_sw2d *s) {
-  const int Np = s->v.Np, Nfn = s->v.Nfn;
-  std::vector<double> Dr((size_t)Np * Np), Ds((size_t)Np * Np), Lift((size_t)Np * Nfn), frag;
-  cudaError_t e;
-  if ((e = cudaStreamSynchronize(s->stream)) != cudaSuccess) return e;
-  if ((e = cudaMemcpy(Dr.data(), s->d_Dr, sizeof(double) * Dr.size(), cudaMemcpyDeviceToHost)) != cudaSuccess) return e;
-  if ((e = cudaMemcpy(Ds.data(), s->d_Ds, sizeof(double) * Ds.size(), cudaMemcpyDeviceToHost)) != cudaSuccess) return e;
-  if ((e = cudaMemcpy(Lift.data(), s->d_Lift, sizeof(double) * Lift.size(), cudaMemcpyDeviceToHost)) != cudaSuccess) return e;
+// Builds the operator fragments and the per-tile local trace maps / ghost lists.  vmapP and facetag are the
+// host arrays of create (vmapP entries >= Np*K address halo slots and are always ghosts).  Sets fused_ops on
+// success; leaves it NULL (generic path) when a tile needs more ghost slots than the kernel can carry.
+cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const double *Lift, const int32_t *vmapP,
+                          const uint8_t *facetag) {
+  const int Np = s->v.Np, Nfp = s->v.Nfp, Nfn = s->v.Nfn, K = s->v.K;
+  std::vector<double> frag;
 #define X(np, nfp) \
-  if (Np == np && s->v.Nfp == nfp) build_afrag<np, nfp>(Dr.data(), Ds.data(), Lift.data(), frag);
+  if (Np == np && Nfp == nfp) build_afrag<np, nfp>(Dr, Ds, Lift, frag);
   BDG_FUSED_ORDERS(X)
 #undef X
   if (frag.empty()) return cudaErrorNotSupported;
+
+  const int ntiles = (K + kTile - 1) / kTile;
+  const int tnp = kTile * Np;
+  std::vector<uint32_t> lmap((size_t)ntiles * kTile * Nfn);
+  std::vector<int32_t> gflat;           // ghosts of all tiles back to back
+  std::vector<size_t> goff(ntiles + 1, 0);
+  int Gmax = 0;
+  std::vector<int32_t> ext;
+  for (int T = 0; T < ntiles; ++T) {
+    const long long kt0 = (long long)T * kTile, base = kt0 * Np;
+    ext.clear();
+    for (int el = 0; el < kTile && kt0 + el < K; ++el)
+      for (int sl = 0; sl < Nfn; ++sl) {
+        const int32_t mP = vmapP[(kt0 + el) * Nfn + sl];
+        const long long r = (long long)mP - base;
+        if (r < 0 || r >= tnp) ext.push_back(mP);
+      }
+    std::sort(ext.begin(), ext.end());
+    ext.erase(std::unique(ext.begin(), ext.end()), ext.end());
+    gflat.insert(gflat.end(), ext.begin(), ext.end());
+    goff[T + 1] = gflat.size();
+    Gmax = std::max(Gmax, (int)ext.size());
+    for (int el = 0; el < kTile; ++el)
+      for (int sl = 0; sl < Nfn; ++sl) {
+        uint32_t word;
+        if (kt0 + el >= K) {
+          word = (uint32_t)(el * Np);  // padding element behind the mesh end: any valid own node
+        } else {
+          const int32_t mP = vmapP[(kt0 + el) * Nfn + sl];
+          const long long r = (long long)mP - base;
+          uint32_t loc;
+          if (r >= 0 && r < tnp)
+            loc = (uint32_t)r;
+          else
+            loc = (uint32_t)(tnp + (std::lower_bound(ext.begin(), ext.end(), mP) - ext.begin()));
+          word = loc | ((uint32_t)facetag[(kt0 + el) * 3 + sl / Nfp] << 16);
+        }
+        lmap[((size_t)kt0 + el) * Nfn + sl] = word;
+      }
+  }
+  const int G = std::max(8, (Gmax + 7) / 8 * 8);
+  if (G > kGI * kThreads || tnp + G > 65535) return cudaSuccess;  // not representable: stay on the generic path
+  std::vector<int32_t> gsrc((size_t)ntiles * G);
+  for (int T = 0; T < ntiles; ++T) {
+    const size_t n = goff[T + 1] - goff[T];
+    for (int x = 0; x < G; ++x)
+      gsrc[(size_t)T * G + x] = (size_t)x < n ? gflat[goff[T] + x] : (int32_t)((long long)T * kTile * Np);  // pad: own first node
+  }
+
   FusedOps *ops = new FusedOps();
-  ops->Np = Np;
-  ops->Nfp = s->v.Nfp;
-  if ((e = cudaMalloc(&ops->Afrag, sizeof(double) * frag.size())) != cudaSuccess) { delete ops; return e; }
-  if ((e = cudaMemcpy(ops->Afrag, frag.data(), sizeof(double) * frag.size(), cudaMemcpyHostToDevice)) != cudaSuccess) {
-    cudaFree(ops->Afrag);
+  ops->Np = Np; ops->Nfp = Nfp; ops->G = G;
+  ops->Afrag = nullptr; ops->lmap = nullptr; ops->gsrc = nullptr;
+  cudaError_t e;
+  if ((e = cudaMalloc(&ops->Afrag, sizeof(double) * frag.size())) != cudaSuccess ||
+      (e = cudaMalloc(&ops->lmap, sizeof(uint32_t) * lmap.size())) != cudaSuccess ||
+      (e = cudaMalloc(&ops->gsrc, sizeof(int32_t) * gsrc.size())) != cudaSuccess ||
+      (e = cudaMemcpy(ops->Afrag, frag.data(), sizeof(double) * frag.size(), cudaMemcpyHostToDevice)) != cudaSuccess ||
+      (e = cudaMemcpy(ops->lmap, lmap.data(), sizeof(uint32_t) * lmap.size(), cudaMemcpyHostToDevice)) != cudaSuccess ||
+      (e = cudaMemcpy(ops->gsrc, gsrc.data(), sizeof(int32_t) * gsrc.size(), cudaMemcpyHostToDevice)) != cudaSuccess) {
+    cudaFree(ops->Afrag); cudaFree(ops->lmap); cudaFree(ops->gsrc);
     delete ops;
     return e;
   }
@@ -596,7 +689,7 @@ cudaError_t fused_prepare(bdg_sw2d *s) {
 void fused_release(bdg_sw2d *s) {
   if (!s->fused_ops) return;
   FusedOps *ops = static_cast<FusedOps *>(s->fused_ops);
-  cudaFree(ops->Afrag);
+  cudaFree(ops->Afrag); cudaFree(ops->lmap); cudaFree(ops->gsrc);
   delete ops;
   s->fused_ops = nullptr;
 }
@@ -608,6 +701,7 @@ cudaError_t launch_fused_stage(bdg_sw2d *s, const double *q_in, double *q_out, d
   if (!ops) return cudaErrorNotSupported;
   StageArgs args;
   args.q_in = q_in; args.q_out = q_out; args.res = res; args.rhs_out = rhs_out; args.Afrag = ops->Afrag;
+  args.lmap = ops->lmap; args.gsrc = ops->gsrc; args.G = ops->G;
   args.k0 = k0; args.k1 = k1; args.tile0 = 0; args.ntiles = 0;
   args.write_rhs = write_rhs; args.slot = slot; args.a = a; args.b = b;
 #define X(np, nfp) \
