@@ -204,7 +204,11 @@ static int create_impl(bdg_sw2d *s, const bdg_dgcontext2d *c, const bdg_sw2d_par
   }
 
   CU(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
-  CU(cudaStreamCreateWithFlags(&s->comm_stream, cudaStreamNonBlocking));
+  {  // the halo exchange must win the race for SM slots against the interior-element kernel it overlaps with
+    int lo = 0, hi = 0;
+    CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CU(cudaStreamCreateWithPriority(&s->comm_stream, cudaStreamNonBlocking, hi));
+  }
   CU(cudaEventCreateWithFlags(&s->ev_pack, cudaEventDisableTiming));
   CU(cudaEventCreateWithFlags(&s->ev_recv, cudaEventDisableTiming));
 

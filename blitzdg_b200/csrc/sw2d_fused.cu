@@ -32,6 +32,7 @@
 // before the contraction (exact for affine elements up to round-off).
 #include <algorithm>
 #include <cstdio>
+#include <type_traits>
 #include <vector>
 
 #include "sw2d_common.cuh"
@@ -134,8 +135,12 @@ struct StageArgs {
   double *rhs_out;        // write_rhs mode: [3][nT]
   const double *Afrag;    // [MB][KB][32] operator in DMMA A-fragment order
   const uint32_t *lmap;   // [ntiles_all*kTile][NFN]: local '+' node (low 16 bits) | face tag << 16
-  const int32_t *gsrc;    // [ntiles_all][G]: global node ids of the tile's ghost nodes
-  int G;                  // ghost slots per tile (multiple of 8)
+  const int32_t *gflat;   // ghost node sources (global node ids) of all tiles back to back
+  const long long *goff;  // [ntiles_all + 1]: tile T owns gflat[goff[T] .. goff[T+1])
+  const int4 *rec;        // persistent kernel: regular tiles {tile id, ghost count, goff low / high 32 bits}
+  const int32_t *biglist; // edge kernel in list mode: tile ids with more than Gcap ghosts
+  int G;                  // ghost slots per tile in shared memory (Gcap: persistent kernel, Gmax: edge kernel), multiple of 8
+  int list_first, use_list;  // first list position of this launch (rec / biglist); edge kernel: 0 = tiles tile0 + blockIdx.x
   int k0, k1;             // active element range
   int tile0, ntiles;      // tiles [tile0, tile0 + ntiles) of this launch
   int write_rhs;
@@ -185,7 +190,7 @@ __device__ __forceinline__ void issue_res_load(const Sw2dView &v, const StageArg
 template <int NP, int NFP>
 __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs &p, double *__restrict__ sQ, double *__restrict__ sR,
                                              const double *__restrict__ sAff, const uint32_t *__restrict__ sLm, double *__restrict__ sFl,
-                                             const double *__restrict__ sA, const double *Areg, const int *fm, int PS, long long kt0,
+                                             const double *__restrict__ sA, const double *Areg, const int *fm, int PS, int nnodes, long long kt0,
                                              bool need_res, uint64_t *bar_res, uint32_t res_parity) {
   using C = Cfg<NP, NFP>;
   constexpr int NFN = C::NFN, NPB = C::NPB, NFB = C::NFB, KB = C::KB, MB = C::MB, TNP = C::TNP;
@@ -198,11 +203,11 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
 
   // ---- phase 1: nodal fluxes and wave speed at own and ghost nodes (A6, A7), flat mapping ------------------
 #pragma unroll 1
-  for (int j0 = threadIdx.x; j0 < PS; j0 += 3 * kThreads) {
+  for (int j0 = threadIdx.x; j0 < nnodes; j0 += 3 * kThreads) {  // nnodes = own + this tile's ghost nodes
 #pragma unroll
     for (int u3 = 0; u3 < 3; ++u3) {
       const int j = j0 + u3 * kThreads;
-      if (j < PS) {
+      if (j < nnodes) {
         const double h = sQ[j], hu = sQ[PS + j], hv = sQ[2 * PS + j];
         const double r = frcp(h), u = hu * r, vv = hv * r, gh2 = (half_g * h) * h;
         sFl[j] = fma(hu, u, gh2);            // F2
@@ -356,7 +361,8 @@ __device__ __forceinline__ void load_constants(const StageArgs &p, const Sw2dVie
   }
 }
 
-// ---- edge kernel: one tile per CTA, any tile (ragged mesh end, partially active range, write_rhs) -------
+// ---- edge kernel: one tile per CTA, any tile (ragged mesh end, partially active range, write_rhs, tiles with
+// more ghost nodes than the persistent kernel's buffers hold) --------------------------------------------------
 template <int NP, int NFP>
 __global__ void __launch_bounds__(kThreads, 3) k_fused_edge(Sw2dView v, StageArgs p) {
   using C = Cfg<NP, NFP>;
@@ -368,23 +374,25 @@ __global__ void __launch_bounds__(kThreads, 3) k_fused_edge(Sw2dView v, StageArg
   uint32_t *sLm = S.Lm(0);
 
   const int tid = threadIdx.x;
-  const long long tile = p.tile0 + blockIdx.x;
+  const long long tile = p.use_list ? p.biglist[p.list_first + blockIdx.x] : p.tile0 + blockIdx.x;
   const long long kt0 = tile * kTile;
   const int nload = (int)min((long long)kTile, (long long)v.K - kt0);
   const bool all_active = nload == kTile && kt0 >= p.k0 && kt0 + kTile <= p.k1;
   const bool need_res = !p.write_rhs && p.a != 0.0;
   const long long stride = v.stride;
   const long long base = kt0 * NP;
+  const long long g0 = p.goff[tile];
+  const int gc = (int)(p.goff[tile + 1] - g0);
 
-  // plain loads; neutral fill (h = 1) behind the mesh end; lmap / gsrc are padded to whole tiles at create
+  // plain loads; neutral fill (h = 1) behind the mesh end; lmap is padded to whole tiles at create
   for (int x = tid; x < 3 * TNP; x += kThreads) {
     const int f = x / TNP, r = x - f * TNP;
     const bool in = r < nload * NP;
     sQ[f * PS + r] = in ? p.q_in[f * stride + base + r] : (f == 0 ? 1.0 : 0.0);
     sR[x] = (in && need_res) ? p.res[f * stride + base + r] : 0.0;
   }
-  for (int x = tid; x < p.G; x += kThreads) {
-    const long long m = p.gsrc[tile * p.G + x];
+  for (int x = tid; x < gc; x += kThreads) {
+    const long long m = p.gflat[g0 + x];
     for (int f = 0; f < 3; ++f) sQ[f * PS + TNP + x] = p.q_in[f * stride + m];
   }
   for (int x = tid; x < kTile * NFN; x += kThreads) sLm[x] = p.lmap[kt0 * NFN + x];
@@ -394,7 +402,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_fused_edge(Sw2dView v, StageArg
   load_constants<NP, NFP>(p, v, Areg, S.A(), fm);
   __syncthreads();
 
-  compute_tile<NP, NFP>(v, p, sQ, sR, sAff, sLm, S.Fl(), S.A(), Areg, fm, PS, kt0, need_res, nullptr, 0);
+  compute_tile<NP, NFP>(v, p, sQ, sR, sAff, sLm, S.Fl(), S.A(), Areg, fm, PS, TNP + gc, kt0, need_res, nullptr, 0);
   if (p.write_rhs) return;
 
   if (all_active) {
@@ -421,22 +429,39 @@ __global__ void __launch_bounds__(kThreads, 3) k_fused_edge(Sw2dView v, StageArg
   }
 }
 
-// ---- persistent kernel: full, fully active tiles; two tile buffers.  While tile `it` is computed, the TMA
-// copies of tile it+1 (issued at the end of iteration it-1) and its ghost gathers (issued at the top of
-// iteration it) are in flight; results leave through TMA bulk stores from the same buffer. -------------------
+// ---- persistent kernel: full, fully active tiles with at most Gcap ghosts, addressed through the record list
+// rec[] = {tile id, ghost count, ghost offset}.  Two tile buffers: while tile `it` is computed, the TMA copies of
+// tile it+1 (issued at the end of iteration it-1) and its ghost gathers (issued at the top of iteration it) are in
+// flight; results leave through TMA bulk stores from the same buffer. ---------------------------------------------
 template <int NP, int NFP>
 __global__ void __launch_bounds__(kThreads, 3) k_fused_persistent(Sw2dView v, StageArgs p) {
   using C = Cfg<NP, NFP>;
   constexpr int TNP = C::TNP;
   extern __shared__ __align__(128) unsigned char smem[];
   const Smem<NP, NFP> S{smem, 2, p.G};
-  const int PS = S.PS(), G = p.G;
+  const int PS = S.PS();
   uint64_t *bar = S.Bar();  // [0],[1]: tile buffers (1 expect_tx arrival + kThreads cp.async arrivals); [2]: res
   const int tid = threadIdx.x;
   const bool need_res = p.a != 0.0;
   const long long stride = v.stride;
-  const int nmine = (p.ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // tiles blockIdx.x + it*gridDim.x
-  auto tile_of = [&](int it) { return (long long)p.tile0 + blockIdx.x + (long long)it * gridDim.x; };
+  const int nmine = (p.ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // list positions blockIdx.x + it*gridDim.x
+  auto rec_of = [&](int it) { return __ldg(p.rec + p.list_first + blockIdx.x + (long long)it * gridDim.x); };
+  // all threads: 8-byte gathers of a tile's ghost nodes into buffer b, then one arrival on its barrier
+  auto gather = [&](int b, int gcount, const int *ids) {
+    double *dst = S.Q(b) + TNP;
+#pragma unroll
+    for (int u = 0; u < kGI; ++u) {
+      const int x = tid + u * kThreads;
+      if (x < gcount)
+        for (int f = 0; f < 3; ++f) cp_async8(dst + f * PS + x, p.q_in + f * stride + ids[u]);
+    }
+    cp_async_arrive(&bar[b]);
+  };
+  auto load_ids = [&](const int4 &r, int *ids) {
+    const int32_t *gs = p.gflat + (((long long)r.w << 32) | (unsigned)r.z);
+#pragma unroll
+    for (int u = 0; u < kGI; ++u) ids[u] = (tid + u * kThreads < r.y) ? __ldg(gs + tid + u * kThreads) : 0;
+  };
 
   if (tid == 0) {
     mbar_init(&bar[0], 1 + kThreads);
@@ -445,33 +470,18 @@ __global__ void __launch_bounds__(kThreads, 3) k_fused_persistent(Sw2dView v, St
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
+  int4 rcur = rec_of(0);                              // tile being computed
+  int4 rnext = nmine > 1 ? rec_of(1) : rcur;          // tile whose copies are in flight
+  int4 rnext2 = nmine > 2 ? rec_of(2) : rcur;         // tile after that
   if (tid == 0) {
-    issue_tile_load<NP, NFP>(v, p, S, 0, tile_of(0), &bar[0]);
-    if (nmine > 1) issue_tile_load<NP, NFP>(v, p, S, 1, tile_of(1), &bar[1]);
-    if (need_res) issue_res_load<NP, NFP>(v, p, S, tile_of(0), &bar[2]);
+    issue_tile_load<NP, NFP>(v, p, S, 0, rcur.x, &bar[0]);
+    if (nmine > 1) issue_tile_load<NP, NFP>(v, p, S, 1, rnext.x, &bar[1]);
+    if (need_res) issue_res_load<NP, NFP>(v, p, S, rcur.x, &bar[2]);
   }
-  // ghost gathers of my first tile; ghost ids of my second tile into registers
-  int gi[kGI];
-  {
-    const int32_t *gs = p.gsrc + tile_of(0) * G;
-    double *dst = S.Q(0) + TNP;
-#pragma unroll
-    for (int u = 0; u < kGI; ++u) {
-      const int x = tid + u * kThreads;
-      gi[u] = 0;
-      if (x < G) {
-        const long long m = __ldg(gs + x);
-        for (int f = 0; f < 3; ++f) cp_async8(dst + f * PS + x, p.q_in + f * stride + m);
-      }
-    }
-    cp_async_arrive(&bar[0]);
-    if (nmine > 1) {
-      const int32_t *gs1 = p.gsrc + tile_of(1) * G;
-#pragma unroll
-      for (int u = 0; u < kGI; ++u)
-        if (tid + u * kThreads < G) gi[u] = __ldg(gs1 + tid + u * kThreads);
-    }
-  }
+  int gi[kGI];  // ghost ids of tile `rnext`
+  load_ids(rcur, gi);
+  gather(0, rcur.y, gi);
+  if (nmine > 1) load_ids(rnext, gi);
   double Areg[C::A_REGS ? C::MB * C::KB : 1];
   int fm[C::NFB];
   load_constants<NP, NFP>(p, v, Areg, S.A(), fm);
@@ -479,26 +489,14 @@ __global__ void __launch_bounds__(kThreads, 3) k_fused_persistent(Sw2dView v, St
 
   for (int it = 0; it < nmine; ++it) {
     const int b = it & 1;
-    const long long kt0 = tile_of(it) * kTile;
+    const long long kt0 = (long long)rcur.x * kTile;
     if (it + 1 < nmine) {  // ghost gathers of the next tile into the other buffer, ids of the one after into registers
-      double *dst = S.Q(b ^ 1) + TNP;
-#pragma unroll
-      for (int u = 0; u < kGI; ++u) {
-        const int x = tid + u * kThreads;
-        if (x < G)
-          for (int f = 0; f < 3; ++f) cp_async8(dst + f * PS + x, p.q_in + f * stride + gi[u]);
-      }
-      cp_async_arrive(&bar[b ^ 1]);
-      if (it + 2 < nmine) {
-        const int32_t *gs2 = p.gsrc + tile_of(it + 2) * G;
-#pragma unroll
-        for (int u = 0; u < kGI; ++u)
-          if (tid + u * kThreads < G) gi[u] = __ldg(gs2 + tid + u * kThreads);
-      }
+      gather(b ^ 1, rnext.y, gi);
+      if (it + 2 < nmine) load_ids(rnext2, gi);
     }
     mbar_wait(&bar[b], (it >> 1) & 1);
-    compute_tile<NP, NFP>(v, p, S.Q(b), S.R(), S.Aff(b), S.Lm(b), S.Fl(), S.A(), Areg, fm, PS, kt0, need_res, need_res ? &bar[2] : nullptr,
-                          it & 1);
+    compute_tile<NP, NFP>(v, p, S.Q(b), S.R(), S.Aff(b), S.Lm(b), S.Fl(), S.A(), Areg, fm, PS, TNP + rcur.y, kt0, need_res,
+                          need_res ? &bar[2] : nullptr, it & 1);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
     if (tid == 0) {
@@ -509,31 +507,38 @@ __global__ void __launch_bounds__(kThreads, 3) k_fused_persistent(Sw2dView v, St
       }
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // buffer b and R drained -> refill them
-      if (it + 2 < nmine) issue_tile_load<NP, NFP>(v, p, S, b, tile_of(it + 2), &bar[b]);
-      if (need_res && it + 1 < nmine) issue_res_load<NP, NFP>(v, p, S, tile_of(it + 1), &bar[2]);
+      if (it + 2 < nmine) issue_tile_load<NP, NFP>(v, p, S, b, rnext2.x, &bar[b]);
+      if (need_res && it + 1 < nmine) issue_res_load<NP, NFP>(v, p, S, rnext.x, &bar[2]);
     }
+    rcur = rnext;
+    rnext = rnext2;
+    if (it + 3 < nmine) rnext2 = rec_of(it + 3);
   }
 }
 
 struct FusedOps {
   double *Afrag;
   uint32_t *lmap;
-  int32_t *gsrc;
-  int G;
+  int32_t *gflat;
+  long long *goff;
+  int4 *rec;
+  int32_t *biglist;
+  std::vector<int> reg_tiles, big_tiles;  // host copies (sorted tile ids) to cut launch ranges
+  int Gcap, Gmax;                         // ghost slots of the persistent / edge kernel buffers (multiples of 8)
   int Np, Nfp;
 };
 
 int g_sm_count[16] = {};
 
 template <int NP, int NFP>
-cudaError_t launch_t(bdg_sw2d *s, StageArgs a) {
+cudaError_t launch_t(bdg_sw2d *s, StageArgs a, const FusedOps *ops) {
   using C = Cfg<NP, NFP>;
   static int ctas_per_sm[16] = {};
-  static int attr_G[16] = {};
+  static int attr_key[16] = {};
   const int dev = s->device & 15;
-  const size_t smem_edge = C::total(1, a.G), smem_pers = C::total(2, a.G);
+  const size_t smem_edge = C::total(1, ops->Gmax), smem_pers = C::total(2, ops->Gcap);
   cudaError_t e;
-  if (attr_G[dev] != a.G + 1) {
+  if (attr_key[dev] != ops->Gmax * 4096 + ops->Gcap + 1) {
     if ((e = cudaFuncSetAttribute(k_fused_edge<NP, NFP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_edge)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_fused_persistent<NP, NFP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pers)) != cudaSuccess) return e;
     cudaFuncSetAttribute(k_fused_edge<NP, NFP>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -541,30 +546,45 @@ cudaError_t launch_t(bdg_sw2d *s, StageArgs a) {
     if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm[dev], k_fused_persistent<NP, NFP>, kThreads, smem_pers)) != cudaSuccess) return e;
     if ((e = cudaDeviceGetAttribute(&g_sm_count[dev], cudaDevAttrMultiProcessorCount, s->device)) != cudaSuccess) return e;
     if (ctas_per_sm[dev] < 1) return cudaErrorLaunchOutOfResources;
-    attr_G[dev] = a.G + 1;
+    attr_key[dev] = ops->Gmax * 4096 + ops->Gcap + 1;
   }
-  // tiles [t0,t1) cover [k0,k1); the fully active ones [p0,p1) go to the persistent kernel (k1 <= K, so
-  // they are also full), ragged / partially active head and tail tiles to the edge kernel
+  // tiles [t0,t1) cover [k0,k1); the fully active ones [p0,p1) (k1 <= K, so they are also full) go to the
+  // persistent kernel when they are regular (<= Gcap ghosts); ragged / partially active head and tail tiles and
+  // the big tiles inside [p0,p1) go to the edge kernel
   const int t0 = a.k0 / kTile, t1 = (a.k1 - 1) / kTile + 1;
   int p0 = (a.k0 + kTile - 1) / kTile, p1 = a.k1 / kTile;
   if (a.write_rhs || p1 <= p0) p0 = p1 = t1;
-  auto edge = [&](int first, int last) {
-    if (last <= first) return;
+  auto edge = [&](int first, int count, int use_list) {
+    if (count <= 0) return;
     StageArgs h = a;
-    h.tile0 = first; h.ntiles = last - first;
-    k_fused_edge<NP, NFP><<<h.ntiles, kThreads, smem_edge, s->stream>>>(s->v, h);
+    h.G = ops->Gmax;
+    h.use_list = use_list;
+    h.tile0 = use_list ? 0 : first;
+    h.list_first = use_list ? first : 0;
+    h.ntiles = count;
+    k_fused_edge<NP, NFP><<<count, kThreads, smem_edge, s->stream>>>(s->v, h);
     s->launches++;
   };
-  edge(t0, p0);
+  edge(t0, p0 - t0, 0);
   if (p1 > p0) {
-    StageArgs m = a;
-    m.tile0 = p0; m.ntiles = p1 - p0;
-    int grid = g_sm_count[dev] * ctas_per_sm[dev];
-    if (grid > m.ntiles) grid = m.ntiles;
-    k_fused_persistent<NP, NFP><<<grid, kThreads, smem_pers, s->stream>>>(s->v, m);
-    s->launches++;
+    const int jr0 = (int)(std::lower_bound(ops->reg_tiles.begin(), ops->reg_tiles.end(), p0) - ops->reg_tiles.begin());
+    const int jr1 = (int)(std::lower_bound(ops->reg_tiles.begin(), ops->reg_tiles.end(), p1) - ops->reg_tiles.begin());
+    if (jr1 > jr0) {
+      StageArgs m = a;
+      m.G = ops->Gcap;
+      m.list_first = jr0; m.ntiles = jr1 - jr0; m.use_list = 1; m.tile0 = 0;
+      int grid = g_sm_count[dev] * ctas_per_sm[dev];
+      // while a halo exchange is in flight leave a few SMs one CTA short, so the NCCL send/recv kernel finds room
+      if (s->comm && s->n_nbr > 0 && a.k0 == 0 && a.k1 < s->v.K) grid -= 16;
+      if (grid > m.ntiles) grid = m.ntiles;
+      k_fused_persistent<NP, NFP><<<grid, kThreads, smem_pers, s->stream>>>(s->v, m);
+      s->launches++;
+    }
+    const int jb0 = (int)(std::lower_bound(ops->big_tiles.begin(), ops->big_tiles.end(), p0) - ops->big_tiles.begin());
+    const int jb1 = (int)(std::lower_bound(ops->big_tiles.begin(), ops->big_tiles.end(), p1) - ops->big_tiles.begin());
+    edge(jb0, jb1 - jb0, 1);
   }
-  edge(p1, t1);
+  edge(p1, t1 - p1, 0);
   return cudaGetLastError();
 }
 
@@ -659,27 +679,47 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
         lmap[((size_t)kt0 + el) * Nfn + sl] = word;
       }
   }
-  const int G = std::max(8, (Gmax + 7) / 8 * 8);
-  if (G > kGI * kThreads || tnp + G > 65535) return cudaSuccess;  // not representable: stay on the generic path
-  std::vector<int32_t> gsrc((size_t)ntiles * G);
-  for (int T = 0; T < ntiles; ++T) {
-    const size_t n = goff[T + 1] - goff[T];
-    for (int x = 0; x < G; ++x)
-      gsrc[(size_t)T * G + x] = (size_t)x < n ? gflat[goff[T] + x] : (int32_t)((long long)T * kTile * Np);  // pad: own first node
-  }
-
+  // Buffer sizing: the persistent kernel's tile buffers hold Gcap ghosts, chosen so that (almost) every tile
+  // fits -- a few outliers (e.g. tiles whose elements are not neighbours of each other after a partition's
+  // interior-first renumbering) must not dictate the shared memory and phase-1 work of all tiles.
+  std::vector<int> cnt(ntiles);
+  for (int T = 0; T < ntiles; ++T) cnt[T] = (int)(goff[T + 1] - goff[T]);
+  std::vector<int> sorted = cnt;
+  std::sort(sorted.begin(), sorted.end());
+  int cap = sorted[(size_t)((ntiles - 1) * 0.97)];
+  if (Gmax - cap <= 16) cap = Gmax;
+  const int Gcap = std::max(8, (cap + 7) / 8 * 8), Gmax8 = std::max(8, (Gmax + 7) / 8 * 8);
+  if (Gmax8 > kGI * kThreads || tnp + Gmax8 > 65535) return cudaSuccess;  // not representable: stay on the generic path
+  std::vector<int4> rec;
   FusedOps *ops = new FusedOps();
-  ops->Np = Np; ops->Nfp = Nfp; ops->G = G;
-  ops->Afrag = nullptr; ops->lmap = nullptr; ops->gsrc = nullptr;
+  for (int T = 0; T < ntiles; ++T) {
+    if (cnt[T] <= Gcap) {
+      ops->reg_tiles.push_back(T);
+      rec.push_back(make_int4(T, cnt[T], (int)(goff[T] & 0xffffffffLL), (int)(goff[T] >> 32)));
+    } else {
+      ops->big_tiles.push_back(T);
+    }
+  }
+  std::vector<long long> goff64(goff.begin(), goff.end());
+  if (gflat.empty()) gflat.push_back(0);
+  std::vector<int32_t> big(ops->big_tiles.begin(), ops->big_tiles.end());
+  if (big.empty()) big.push_back(0);
+  if (rec.empty()) rec.push_back(make_int4(0, 0, 0, 0));
+
+  ops->Np = Np; ops->Nfp = Nfp; ops->Gcap = Gcap; ops->Gmax = Gmax8;
+  ops->Afrag = nullptr; ops->lmap = nullptr; ops->gflat = nullptr; ops->goff = nullptr; ops->rec = nullptr; ops->biglist = nullptr;
   cudaError_t e;
-  if ((e = cudaMalloc(&ops->Afrag, sizeof(double) * frag.size())) != cudaSuccess ||
-      (e = cudaMalloc(&ops->lmap, sizeof(uint32_t) * lmap.size())) != cudaSuccess ||
-      (e = cudaMalloc(&ops->gsrc, sizeof(int32_t) * gsrc.size())) != cudaSuccess ||
-      (e = cudaMemcpy(ops->Afrag, frag.data(), sizeof(double) * frag.size(), cudaMemcpyHostToDevice)) != cudaSuccess ||
-      (e = cudaMemcpy(ops->lmap, lmap.data(), sizeof(uint32_t) * lmap.size(), cudaMemcpyHostToDevice)) != cudaSuccess ||
-      (e = cudaMemcpy(ops->gsrc, gsrc.data(), sizeof(int32_t) * gsrc.size(), cudaMemcpyHostToDevice)) != cudaSuccess) {
-    cudaFree(ops->Afrag); cudaFree(ops->lmap); cudaFree(ops->gsrc);
-    delete ops;
+  auto up = [&](auto **dst, const auto &vec) -> cudaError_t {
+    using T = typename std::remove_reference<decltype(vec[0])>::type;
+    cudaError_t r = cudaMalloc((void **)dst, sizeof(T) * vec.size());
+    if (r != cudaSuccess) return r;
+    return cudaMemcpy((void *)*dst, vec.data(), sizeof(T) * vec.size(), cudaMemcpyHostToDevice);
+  };
+  if ((e = up(&ops->Afrag, frag)) != cudaSuccess || (e = up(&ops->lmap, lmap)) != cudaSuccess ||
+      (e = up(&ops->gflat, gflat)) != cudaSuccess || (e = up(&ops->goff, goff64)) != cudaSuccess ||
+      (e = up(&ops->rec, rec)) != cudaSuccess || (e = up(&ops->biglist, big)) != cudaSuccess) {
+    s->fused_ops = ops;
+    fused_release(s);
     return e;
   }
   s->fused_ops = ops;
@@ -689,7 +729,7 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
 void fused_release(bdg_sw2d *s) {
   if (!s->fused_ops) return;
   FusedOps *ops = static_cast<FusedOps *>(s->fused_ops);
-  cudaFree(ops->Afrag); cudaFree(ops->lmap); cudaFree(ops->gsrc);
+  cudaFree(ops->Afrag); cudaFree(ops->lmap); cudaFree(ops->gflat); cudaFree(ops->goff); cudaFree(ops->rec); cudaFree(ops->biglist);
   delete ops;
   s->fused_ops = nullptr;
 }
@@ -701,11 +741,12 @@ cudaError_t launch_fused_stage(bdg_sw2d *s, const double *q_in, double *q_out, d
   if (!ops) return cudaErrorNotSupported;
   StageArgs args;
   args.q_in = q_in; args.q_out = q_out; args.res = res; args.rhs_out = rhs_out; args.Afrag = ops->Afrag;
-  args.lmap = ops->lmap; args.gsrc = ops->gsrc; args.G = ops->G;
+  args.lmap = ops->lmap; args.gflat = ops->gflat; args.goff = ops->goff; args.rec = ops->rec; args.biglist = ops->biglist;
+  args.G = ops->Gmax; args.list_first = 0; args.use_list = 0;
   args.k0 = k0; args.k1 = k1; args.tile0 = 0; args.ntiles = 0;
   args.write_rhs = write_rhs; args.slot = slot; args.a = a; args.b = b;
 #define X(np, nfp) \
-  if (ops->Np == np && ops->Nfp == nfp) return launch_t<np, nfp>(s, args);
+  if (ops->Np == np && ops->Nfp == nfp) return launch_t<np, nfp>(s, args, ops);
   BDG_FUSED_ORDERS(X)
 #undef X
   return cudaErrorNotSupported;
