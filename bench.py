@@ -201,7 +201,7 @@ def workload_config(args, world, variant):
                     % (fam, Kper, args.nx, args.ny, args.order) if args.mode == "simple" else
                     "sw2d full physics (global LF, star states, sources) on synthetic %s mesh, %d elements per GPU, N=%d" % (fam, Kper, args.order),
         "elements_per_gpu": Kper, "order": args.order, "lserk_steps_per_step": OUTPUT_INTERVAL, "stages_per_step": 5 * OUTPUT_INTERVAL,
-        "partition": "single GPU" if world == 1 else "%d horizontal strips, NCCL send/recv face-trace halo per stage" % world,
+        "partition": "single GPU" if world == 1 else "%d horizontal strips; face-trace halo per stage by direct NVLink peer stores from the sender's kernel + epoch flags (NCCL send/recv fallback)" % world,
         "l2": "working set (>=1 GB of state per GPU) exceeds the 126 MB L2; no explicit flush",
         "kernel_variant": variant,
     }

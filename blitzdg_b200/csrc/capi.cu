@@ -144,7 +144,13 @@ extern "C" void bdg_sw2d_destroy(bdg_sw2d *s) {
   if (!s) return;
   cudaSetDevice(s->device);
   cudaStreamSynchronize(s->stream);
+  for (int k = 0; k < 3; ++k)
+    for (int i = 0; i < kMaxNbr; ++i)
+      if (s->peer_base[k][i]) cudaIpcCloseMemHandle(s->peer_base[k][i]);
   if (s->comm) ncclCommDestroy((ncclComm_t)s->comm);
+  if (s->d_flags) cudaFree(s->d_flags);
+  if (s->d_put_counter) cudaFree(s->d_put_counter);
+  if (s->d_put_dst) cudaFree(s->d_put_dst);
   fused_release(s);
   void *ptrs[] = {s->q[0], s->q[1], s->res, s->rhs, s->sflux, s->d_Dr, s->d_Ds, s->d_Lift, s->d_Filt, s->d_rx, s->d_sx,
                   s->d_ry, s->d_sy, s->d_nx, s->d_ny, s->d_Fscale, s->d_aff, s->d_H, s->d_Hx, s->d_Hy, s->d_vmapP,
@@ -389,6 +395,10 @@ extern "C" int bdg_sw2d_set_bathymetry(bdg_sw2d *s, const double *H, const doubl
 extern "C" int bdg_sw2d_set_state(bdg_sw2d *s, const double *h, const double *hu, const double *hv, double t) {
   if (!s || !h || !hu || !hv) return BDG_E_INVALID;
   CU(cudaSetDevice(s->device));
+  if (s->put_pending) {
+    CU(cudaStreamSynchronize(s->comm_stream));
+    s->put_pending = 0;
+  }
   double *q = s->q[s->cur];
   const double *src[3] = {h, hu, hv};
   for (int c = 0; c < 3; ++c) {
@@ -397,6 +407,7 @@ extern "C" int bdg_sw2d_set_state(bdg_sw2d *s, const double *h, const double *hu
   }
   CU(cudaMemsetAsync(s->res, 0, sizeof(double) * 3 * s->v.stride, s->stream));  // reference src/sw2d/main.cpp:117-119
   s->t = t;
+  s->ghost_valid = 0;
   CU(cudaMemcpyAsync(s->d_scal + S_T, &s->t, sizeof(double), cudaMemcpyHostToDevice, s->stream));
   CU(cudaStreamSynchronize(s->stream));
   return BDG_OK;
@@ -471,6 +482,94 @@ extern "C" int bdg_nccl_unique_id(void *id_out) {
   return BDG_OK;
 }
 
+// Peer-memory halo setup (sw2d_halo.cu): all-gather CUDA IPC handles of the two state buffers and the flag
+// array, plus each rank's ghost base per sender, over the communicator; open the neighbours' handles.
+// Any failure leaves peer_ok = 0 and the NCCL send/recv path in charge.
+struct PeerRecord {
+  cudaIpcMemHandle_t q[2], flags;
+  long long stride;
+};
+static int peer_setup(bdg_sw2d *s) {
+  s->peer_ok = 0;
+  const char *env = getenv("BDG_HALO");
+  if (env && !strcmp(env, "nccl")) return BDG_OK;
+  if (!s->fused_ok || s->v.lf_global || s->nranks < 2 || s->n_nbr > kMaxNbr) return BDG_OK;
+  ncclComm_t comm = (ncclComm_t)s->comm;
+  const int P = s->nranks;
+  int rc;
+  if ((rc = dev_alloc(s, &s->d_flags, (size_t)P))) return rc;
+  CU(cudaMemsetAsync(s->d_flags, 0, sizeof(unsigned long long) * P, s->stream));
+  if ((rc = dev_alloc(s, &s->d_put_counter, 1))) return rc;
+  CU(cudaMemsetAsync(s->d_put_counter, 0, sizeof(unsigned int), s->stream));
+  // my record and my ghost bases: gbase[r] = first ghost slot (plane index) that sender r fills, or -1
+  PeerRecord mine;
+  memset(&mine, 0, sizeof(mine));
+  bool ok = cudaIpcGetMemHandle(&mine.q[0], s->q[0]) == cudaSuccess && cudaIpcGetMemHandle(&mine.q[1], s->q[1]) == cudaSuccess &&
+            cudaIpcGetMemHandle(&mine.flags, s->d_flags) == cudaSuccess;
+  if (!ok) cudaGetLastError();
+  mine.stride = ok ? s->v.stride : -1;
+  std::vector<long long> gbase(P, -1);
+  for (int i = 0; i < s->n_nbr; ++i) gbase[s->h_nbr[i]] = (long long)s->nT + s->h_recv_off[i];
+  std::vector<PeerRecord> all(P);
+  std::vector<long long> gall((size_t)P * P);
+  unsigned char *d_rec = nullptr;
+  long long *d_g = nullptr;
+  if ((rc = dev_alloc(s, &d_rec, sizeof(PeerRecord) * (P + 1)))) return rc;
+  if ((rc = dev_alloc(s, &d_g, (size_t)P * (P + 1)))) return rc;
+  CU(cudaMemcpyAsync(d_rec + sizeof(PeerRecord) * P, &mine, sizeof(mine), cudaMemcpyHostToDevice, s->stream));
+  CU(cudaMemcpyAsync(d_g + (size_t)P * P, gbase.data(), sizeof(long long) * P, cudaMemcpyHostToDevice, s->stream));
+  NC(ncclAllGather(d_rec + sizeof(PeerRecord) * P, d_rec, sizeof(PeerRecord), ncclChar, comm, s->stream));
+  NC(ncclAllGather(d_g + (size_t)P * P, d_g, P, ncclInt64, comm, s->stream));
+  CU(cudaMemcpyAsync(all.data(), d_rec, sizeof(PeerRecord) * P, cudaMemcpyDeviceToHost, s->stream));
+  CU(cudaMemcpyAsync(gall.data(), d_g, sizeof(long long) * P * P, cudaMemcpyDeviceToHost, s->stream));
+  CU(cudaStreamSynchronize(s->stream));
+  cudaFree(d_rec);
+  cudaFree(d_g);
+  for (int r = 0; r < P; ++r)
+    if (all[r].stride < 0) ok = false;  // every rank must take the same decision
+  PeerTable pt;
+  memset(&pt, 0, sizeof(pt));
+  pt.n = s->n_nbr;
+  for (int i = 0; i < s->n_nbr && ok; ++i) {
+    const int r = s->h_nbr[i];
+    void *p0 = nullptr, *p1 = nullptr, *pf = nullptr;
+    if (cudaIpcOpenMemHandle(&p0, all[r].q[0], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess ||
+        cudaIpcOpenMemHandle(&p1, all[r].q[1], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess ||
+        cudaIpcOpenMemHandle(&pf, all[r].flags, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+      cudaGetLastError();
+      ok = false;
+    }
+    s->peer_base[0][i] = p0; s->peer_base[1][i] = p1; s->peer_base[2][i] = pf;
+    pt.rank[i] = r;
+    pt.q[0][i] = (double *)p0; pt.q[1][i] = (double *)p1;
+    pt.stride[i] = all[r].stride;
+    pt.flags[i] = (unsigned long long *)pf;
+    if (gall[(size_t)r * P + s->rank] < 0) ok = false;
+  }
+  // the decision must be unanimous: a rank that could not map a peer forces everyone back to NCCL
+  int *d_ok = nullptr;
+  if ((rc = dev_alloc(s, &d_ok, 1))) return rc;
+  int h_ok = ok ? 1 : 0;
+  CU(cudaMemcpyAsync(d_ok, &h_ok, sizeof(int), cudaMemcpyHostToDevice, s->stream));
+  NC(ncclAllReduce(d_ok, d_ok, 1, ncclInt, ncclMin, comm, s->stream));
+  CU(cudaMemcpyAsync(&h_ok, d_ok, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+  CU(cudaStreamSynchronize(s->stream));
+  cudaFree(d_ok);
+  if (!h_ok) return BDG_OK;
+  std::vector<long long> dst((size_t)(s->n_send ? s->n_send : 1));
+  for (int i = 0; i < s->n_nbr; ++i) {
+    const long long base = gall[(size_t)s->h_nbr[i] * P + s->rank];
+    for (int j = s->h_send_off[i]; j < s->h_send_off[i + 1]; ++j) dst[j] = base + (j - s->h_send_off[i]);
+  }
+  if ((rc = dev_upload(s, &s->d_put_dst, dst.data(), dst.size()))) return rc;
+  CU(cudaStreamSynchronize(s->stream));
+  s->peer = pt;
+  s->epoch = 0;
+  s->ghost_valid = 0;
+  s->peer_ok = 1;
+  return BDG_OK;
+}
+
 extern "C" int bdg_sw2d_comm_init(bdg_sw2d *s, const void *idp) {
   if (!s || !idp) return BDG_E_INVALID;
   CU(cudaSetDevice(s->device));
@@ -479,7 +578,7 @@ extern "C" int bdg_sw2d_comm_init(bdg_sw2d *s, const void *idp) {
   ncclComm_t comm;
   NC(ncclCommInitRank(&comm, s->nranks, id, s->rank));
   s->comm = (ncclComm *)comm;
-  return BDG_OK;
+  return peer_setup(s);
 }
 
 extern "C" int bdg_sw2d_halo_pack_to_host(bdg_sw2d *s, double *send_buf) {
@@ -525,9 +624,57 @@ static int enqueue_stage(bdg_sw2d *s, int write_rhs, double *rhs_out, double a, 
   double *q = s->q[s->cur];
   const int K = s->v.K;
   const bool halo = s->comm && s->n_nbr > 0;
-  const int ksplit = halo ? s->n_interior : K;
+  // interior/cut split rounded down to a whole 32-element tile of the fused kernel: computing a few interior
+  // elements with the cut launch is harmless and keeps both launches free of partially active tiles
+  const int ksplit = halo ? (use_fused(s) ? s->n_interior / 32 * 32 : s->n_interior) : K;
   int rc;
   cudaError_t e;
+  if (halo && s->peer_ok && use_fused(s)) {
+    // Peer-memory halo (sw2d_halo.cu): ghosts of the live buffer were stored by the neighbours during the
+    // previous stage.  Cut elements first, then publish their new traces into the neighbours' next buffer,
+    // then the interior elements -- the NVLink transfer hides behind the interior launch.
+    double *qo = s->q[s->cur ^ 1];
+    static int prof_on = getenv("BDG_PROF") ? 1 : 0;
+    static cudaEvent_t pev[6];
+    static long pcount = 0;
+    const bool prof = prof_on && (++pcount == 700);
+    if (prof) for (auto &x : pev) cudaEventCreate(&x);
+#define PREC(i) if (prof) cudaEventRecord(pev[i], s->stream)
+    PREC(0);
+    if (s->put_pending) {  // join the previous stage's put before its source buffer can be written again
+      CU(cudaStreamWaitEvent(s->stream, s->ev_recv, 0));
+      s->put_pending = 0;
+    }
+    if (!s->ghost_valid) {  // first evaluation after set_state: exchange the traces of the live buffer itself
+      if ((e = launch_put(s, q, s->cur, ++s->epoch, 0)) != cudaSuccess) return fail(s, BDG_E_CUDA, "put: %s", cudaGetErrorString(e));
+      s->ghost_valid = 1;
+    }
+    if ((e = launch_wait_epoch(s, s->epoch)) != cudaSuccess) return fail(s, BDG_E_CUDA, "wait: %s", cudaGetErrorString(e));
+    PREC(1);
+    if ((e = launch_fused_stage(s, q, qo, s->res, ksplit, K, a, b, write_rhs, rhs_out, slot)) != cudaSuccess)
+      return fail(s, BDG_E_CUDA, "fused(cut): %s", cudaGetErrorString(e));
+    PREC(2);
+    if (!write_rhs && (e = launch_put(s, qo, s->cur ^ 1, ++s->epoch, 1)) != cudaSuccess)
+      return fail(s, BDG_E_CUDA, "put: %s", cudaGetErrorString(e));
+    PREC(3);
+    if ((e = launch_fused_stage(s, q, qo, s->res, 0, ksplit, a, b, write_rhs, rhs_out, slot)) != cudaSuccess)
+      return fail(s, BDG_E_CUDA, "fused(interior): %s", cudaGetErrorString(e));
+    PREC(4);
+    if (prof) {
+      cudaStreamSynchronize(s->stream);
+      float t[4];
+      for (int i = 0; i < 4; ++i) cudaEventElapsedTime(&t[i], pev[i], pev[i + 1]);
+      fprintf(stderr, "[BDG_PROF rank %d] wait %.1f us, cut %.1f us, put %.1f us, interior %.1f us (launches so far %lld)\n", s->rank,
+              1e3 * t[0], 1e3 * t[1], 1e3 * t[2], 1e3 * t[3], (long long)s->launches);
+    }
+    if (!write_rhs) s->cur ^= 1;
+    return BDG_OK;
+  }
+  if (s->put_pending) {
+    CU(cudaStreamWaitEvent(s->stream, s->ev_recv, 0));
+    s->put_pending = 0;
+  }
+  s->ghost_valid = 0;  // this path refreshes the ghosts itself (NCCL) and may update q in place
   if ((rc = halo_begin(s, q))) return rc;
   if (s->v.lf_global) {  // needs every trace, ghosts included: no overlap in this mode
     if ((rc = halo_wait(s))) return rc;
@@ -650,6 +797,7 @@ extern "C" int bdg_sw2d_set_variant(bdg_sw2d *s, int32_t variant) {
   if (!s || variant < 0 || variant > 2) return BDG_E_INVALID;
   if (variant == 2 && !s->fused_ok) return fail(s, BDG_E_UNSUPPORTED, "fused path unavailable for this context (needs affine triangles, uniform face tags, no filter, supported order)");
   s->variant = variant;
+  s->ghost_valid = 0;
   return BDG_OK;
 }
 extern "C" int bdg_sw2d_get_variant(const bdg_sw2d *s) { return s ? (use_fused(s) ? 2 : 1) : -1; }

@@ -36,6 +36,16 @@ struct Sw2dView {
   double *scal;                          // S_COUNT device scalars
 };
 
+// peer-memory halo (sw2d_halo.cu): per neighbour i, the peer's two state buffers, plane stride, flag words
+constexpr int kMaxNbr = 8;
+struct PeerTable {
+  int n;
+  int rank[kMaxNbr];
+  double *q[2][kMaxNbr];
+  long long stride[kMaxNbr];
+  unsigned long long *flags[kMaxNbr];  // the peer's flag array [nranks]; I write entry [my rank]
+};
+
 struct bdg_sw2d {
   int device;
   cudaStream_t stream, comm_stream;
@@ -66,6 +76,16 @@ struct bdg_sw2d {
   int32_t *d_send_nodes;
   double *d_sendbuf;    // [n_nbr segments][3 (or 4)][count]
   ncclComm *comm;
+  // peer-memory halo
+  int peer_ok;                    // IPC mappings established: the fused per-face path exchanges halos by direct stores
+  PeerTable peer;
+  void *peer_base[3][kMaxNbr];    // opened IPC mappings (q0, q1, flags) to close at destroy
+  unsigned long long *d_flags;    // [nranks] epochs published by my neighbours
+  unsigned int *d_put_counter;
+  long long *d_put_dst;           // [n_send] ghost slot index in the receiver's plane
+  unsigned long long epoch;       // number of puts issued (identical on all ranks: same call sequence)
+  int put_pending;                // a put on the communication stream has not been joined by the main stream yet
+  int ghost_valid;                // the live buffer's ghost slots hold its neighbours' traces
   int64_t launches;
   char err[512];
 };
@@ -81,6 +101,8 @@ cudaError_t launch_dt_finalize(bdg_sw2d *s);
 cudaError_t launch_advance_time(bdg_sw2d *s);
 cudaError_t launch_check(bdg_sw2d *s, const double *q);
 cudaError_t launch_pack(bdg_sw2d *s, const double *q, int with_H);
+cudaError_t launch_put(bdg_sw2d *s, const double *q, int buf, unsigned long long epoch, int side);
+cudaError_t launch_wait_epoch(bdg_sw2d *s, unsigned long long epoch);
 // fused DMMA path (affine triangles): q_in -> q_out, res in place, elements [k0,k1)
 int fused_supported(const bdg_sw2d *s);
 cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const double *Lift, const int32_t *vmapP,

@@ -575,7 +575,7 @@ cudaError_t launch_t(bdg_sw2d *s, StageArgs a, const FusedOps *ops) {
       m.list_first = jr0; m.ntiles = jr1 - jr0; m.use_list = 1; m.tile0 = 0;
       int grid = g_sm_count[dev] * ctas_per_sm[dev];
       // while a halo exchange is in flight leave a few SMs one CTA short, so the NCCL send/recv kernel finds room
-      if (s->comm && s->n_nbr > 0 && a.k0 == 0 && a.k1 < s->v.K) grid -= 16;
+      if (s->comm && !s->peer_ok && s->n_nbr > 0 && a.k0 == 0 && a.k1 < s->v.K) grid -= 16;
       if (grid > m.ntiles) grid = m.ntiles;
       k_fused_persistent<NP, NFP><<<grid, kThreads, smem_pers, s->stream>>>(s->v, m);
       s->launches++;

@@ -55,10 +55,18 @@ def build_local(mesh, epart, rank, N):
     mine = np.nonzero(epart == rank)[0]
     nb_part = epart[e2e[mine]]  # [Kloc][Nf]
     is_cut = (nb_part != rank).any(axis=1)
+    n_touch = int(is_cut.sum())
+    # Elements wedged between cut elements (>= 2 of their neighbours are cut, e.g. the upper triangles of a
+    # structured boundary row) join the cut group: left among the interior elements they would form tiles whose
+    # members are not neighbours of each other.  "Interior touches no ghost slot" still holds.
+    cut_glob = np.zeros(K, dtype=bool)
+    cut_glob[mine[is_cut]] = True
+    nb_cut = (cut_glob[e2e[mine]] & (e2e[mine] != mine[:, None])).sum(axis=1)
+    is_cut = is_cut | (nb_cut >= 2)
     local = np.concatenate([mine[~is_cut], mine[is_cut]])
     n_interior = int((~is_cut).sum())
     Kloc = len(local)
-    ring = np.unique(e2e[mine[is_cut]][nb_part[is_cut] != rank])
+    ring = np.unique(e2e[mine][nb_part != rank])
     sub = np.concatenate([local, ring])
     uv, inv = np.unique(etov[sub].reshape(-1), return_inverse=True)
     m = MeshManager()
