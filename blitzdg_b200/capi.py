@@ -11,7 +11,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libblitzdg_b200.so")
+# BDG_B200_LIB selects another build of the SAME sources (tools/build_variant.sh: kernel experiments, the phase profiler)
+LIB_PATH = os.environ.get("BDG_B200_LIB") or os.path.join(_HERE, "csrc", "libblitzdg_b200.so")
 
 BDG_OK, BDG_E_INVALID, BDG_E_CUDA, BDG_E_UNSTABLE, BDG_E_NCCL, BDG_E_UNSUPPORTED = range(6)
 BDG_NCCL_ID_BYTES = 128

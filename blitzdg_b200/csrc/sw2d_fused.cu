@@ -78,6 +78,12 @@ __device__ __forceinline__ void bulk_s2g(void *dst, const void *src, uint32_t by
 __device__ __forceinline__ void cp_async8(void *dst, const void *src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
 }
+__device__ __forceinline__ void cp_async16(void *dst, const void *src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void prefetch_l2(const void *src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void cp_async_arrive(uint64_t *bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -111,6 +117,19 @@ __device__ __forceinline__ double fsqrt(double x) {
   return fma(e, hh, s);
 }
 
+#ifdef BDG_PHASEPROF
+// phase profiler (debug builds only): lane 0 of every warp accumulates clock64() deltas per code section
+#define PROF_DECL long long pacc[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; long long plast = clock64();
+#define PROF_T(i) do { long long now_ = clock64(); pacc[i] += now_ - plast; plast = now_; } while (0)
+#define PROF_ARGS , long long *pacc, long long &plast
+#define PROF_PASS , pacc, plast
+#else
+#define PROF_DECL
+#define PROF_T(i) do { } while (0)
+#define PROF_ARGS
+#define PROF_PASS
+#endif
+
 template <int NP, int NFP>
 struct Cfg {
   static constexpr int NFN = 3 * NFP;
@@ -118,14 +137,17 @@ struct Cfg {
   static constexpr int NFB = (NFN + 3) / 4;   // k-blocks of the LIFT part
   static constexpr int KB = 2 * NPB + NFB;
   static constexpr int MB = (NP + 7) / 8;     // row blocks
-  static constexpr bool A_REGS = (MB * KB <= 36);
+#ifndef BDG_AREGS_MAX
+#define BDG_AREGS_MAX 36
+#endif
+  static constexpr bool A_REGS = (MB * KB <= BDG_AREGS_MAX);
   static constexpr int TNP = kTile * NP;      // own nodes per tile
   static constexpr uint32_t txQ = sizeof(double) * TNP;  // one field plane of a tile
   static constexpr uint32_t txMeta = sizeof(uint32_t) * kTile * NFN + sizeof(double) * kTile * kAW;
   static constexpr size_t sizeA = A_REGS ? 0 : sizeof(double) * MB * KB * 32;
   // per tile buffer: Q[3][PS], Aff[kTile][13], Lm[kTile][NFN]; CTA-wide: R[3][TNP], Fl[4][PS], A, barriers
   static size_t buf_bytes(int G) { return sizeof(double) * 3 * (TNP + G) + sizeof(double) * kTile * kAW + sizeof(uint32_t) * kTile * NFN; }
-  static size_t total(int nbuf, int G) { return nbuf * buf_bytes(G) + sizeof(double) * 3 * TNP + sizeof(double) * 4 * (TNP + G) + sizeA + 64; }
+  static size_t total(int nbuf, int G) { return nbuf * buf_bytes(G) + sizeof(double) * 3 * TNP + sizeof(double) * 4 * (TNP + G) + sizeA + 64 + 128 + (nbuf > 1 ? nbuf * sizeof(int32_t) * G : 0); }
 };
 
 struct StageArgs {
@@ -145,6 +167,7 @@ struct StageArgs {
   int tile0, ntiles;      // tiles [tile0, tile0 + ntiles) of this launch
   int write_rhs;
   int slot;               // scal slot of the global LF speed
+  long long *prof;        // BDG_PHASEPROF builds: [kWarps][12] cycle sums
   double a, b;            // LSERK4 stage coefficients
 };
 
@@ -162,36 +185,48 @@ struct Smem {
   __device__ double *Fl() const { return R() + 3 * C::TNP; }
   __device__ double *A() const { return Fl() + 4 * PS(); }
   __device__ uint64_t *Bar() const { return reinterpret_cast<uint64_t *>(reinterpret_cast<unsigned char *>(A()) + C::sizeA); }
+  __device__ int4 *Ring() const { return reinterpret_cast<int4 *>(Bar() + 8); }  // 8 tile records (persistent kernel)
+  __device__ int32_t *Ids(int b) const { return reinterpret_cast<int32_t *>(Ring() + 8) + b * G; }  // ghost sources of the tile after buffer b's
 };
 
-// thread 0: TMA bulk loads of one full tile's own nodes, geometry and local map into buffer b
-template <int NP, int NFP>
-__device__ __forceinline__ void issue_tile_load(const Sw2dView &v, const StageArgs &p, const Smem<NP, NFP> &S, int b, long long tile,
-                                                uint64_t *bar) {
-  using C = Cfg<NP, NFP>;
-  const long long kt0 = tile * kTile, base = kt0 * NP;
-  mbar_expect_tx(bar, 3 * C::txQ + C::txMeta);
-  bulk_g2s(S.Lm(b), p.lmap + kt0 * C::NFN, sizeof(uint32_t) * kTile * C::NFN, bar);
-  bulk_g2s(S.Aff(b), v.aff + kt0 * kAW, sizeof(double) * kTile * kAW, bar);
-  for (int f = 0; f < 3; ++f) bulk_g2s(S.Q(b) + f * S.PS(), p.q_in + f * v.stride + base, C::txQ, bar);
-}
-template <int NP, int NFP>
-__device__ __forceinline__ void issue_res_load(const Sw2dView &v, const StageArgs &p, const Smem<NP, NFP> &S, long long tile, uint64_t *bar) {
-  using C = Cfg<NP, NFP>;
-  const long long base = tile * kTile * NP;
-  mbar_expect_tx(bar, 3 * C::txQ);
-  for (int f = 0; f < 3; ++f) bulk_g2s(S.R() + f * C::TNP, p.res + f * v.stride + base, C::txQ, bar);
+// Phase 1 for U nodes of one thread at once (j, j + kThreads, ...): the U dependency chains (reciprocal, two
+// square roots) are independent straight-line code, so the scheduler interleaves them.  Indices behind the
+// tile's last node are clamped: such lanes recompute (and re-store) the last node's values.
+template <int U>
+__device__ __forceinline__ void phase1_nodes(const double *__restrict__ sQ, double *__restrict__ sFl, int PS, int j0, int last, double g,
+                                             double half_g) {
+  int j[U];
+  double h[U], hu[U], hv[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    j[u] = min(j0 + u * kThreads, last);
+    h[u] = sQ[j[u]];
+    hu[u] = sQ[PS + j[u]];
+    hv[u] = sQ[2 * PS + j[u]];
+  }
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const double r = frcp(h[u]), uu = hu[u] * r, vv = hv[u] * r, gh2 = (half_g * h[u]) * h[u];
+    sFl[j[u]] = fma(hu[u], uu, gh2);            // F2
+    sFl[PS + j[u]] = hu[u] * vv;                // G2 = F3
+    sFl[2 * PS + j[u]] = fma(hv[u], vv, gh2);   // G3
+    sFl[3 * PS + j[u]] = fsqrt(fma(uu, uu, fma(vv, vv, 1e-300))) + fsqrt(g * h[u]);
+  }
 }
 
 // The arithmetic of one tile that sits in shared memory (A1-A13 of SURVEY.md Appendix A).  sQ: [3][PS] own +
 // ghost nodes, sR: [3][TNP].  On return the tile's q and res planes hold the updated values (stage mode) -- or,
 // in write_rhs mode, rhs_out has been written and the tile is untouched.  Contains two __syncthreads() and an
 // optional wait on the res barrier before phase 3; the caller makes the tile visible first.
-template <int NP, int NFP>
+// The operator fragments (Areg / sA) arrive pre-multiplied by dt (by 1 in write_rhs mode), so the accumulators,
+// started from a*res, end as the new res.  All three phases are branch-free on their hot path: padding slots are
+// clamped to a valid neighbour (their operator columns are zero), the wall reflection is a rare warp-level
+// fix-up pass, and every thread keeps several independent dependency chains in flight.
+template <int NP, int NFP, class Mid>
 __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs &p, double *__restrict__ sQ, double *__restrict__ sR,
                                              const double *__restrict__ sAff, const uint32_t *__restrict__ sLm, double *__restrict__ sFl,
                                              const double *__restrict__ sA, const double *Areg, const int *fm, int PS, int nnodes, long long kt0,
-                                             bool need_res, uint64_t *bar_res, uint32_t res_parity) {
+                                             bool need_res, uint64_t *bar_res, uint32_t res_parity, Mid mid PROF_ARGS) {
   using C = Cfg<NP, NFP>;
   constexpr int NFN = C::NFN, NPB = C::NPB, NFB = C::NFB, KB = C::KB, MB = C::MB, TNP = C::TNP;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -202,64 +237,65 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   const double *af = sAff + e * kAW;
 
   // ---- phase 1: nodal fluxes and wave speed at own and ghost nodes (A6, A7), flat mapping ------------------
-#pragma unroll 1
-  for (int j0 = threadIdx.x; j0 < nnodes; j0 += 3 * kThreads) {  // nnodes = own + this tile's ghost nodes
-#pragma unroll
-    for (int u3 = 0; u3 < 3; ++u3) {
-      const int j = j0 + u3 * kThreads;
-      if (j < nnodes) {
-        const double h = sQ[j], hu = sQ[PS + j], hv = sQ[2 * PS + j];
-        const double r = frcp(h), u = hu * r, vv = hv * r, gh2 = (half_g * h) * h;
-        sFl[j] = fma(hu, u, gh2);            // F2
-        sFl[PS + j] = hu * vv;               // G2 = F3
-        sFl[2 * PS + j] = fma(hv, vv, gh2);  // G3
-        sFl[3 * PS + j] = fsqrt(fma(u, u, fma(vv, vv, 1e-300))) + fsqrt(g * h);
-      }
-    }
+  {
+    const int wbase = w * 32, last = nnodes - 1;
+    int i = 0;
+    for (; wbase + (i + 2) * kThreads < nnodes; i += 3) phase1_nodes<3>(sQ, sFl, PS, threadIdx.x + i * kThreads, last, g, half_g);
+    if (wbase + (i + 1) * kThreads < nnodes)
+      phase1_nodes<2>(sQ, sFl, PS, threadIdx.x + i * kThreads, last, g, half_g);
+    else if (wbase + i * kThreads < nnodes)
+      phase1_nodes<1>(sQ, sFl, PS, threadIdx.x + i * kThreads, last, g, half_g);
   }
+  PROF_T(2);
   __syncthreads();
+  mid();  // the caller's copy duties that had to wait for the previous tile's last reader (persistent kernel)
+  PROF_T(3);
 
   // ---- phase 2: face slots of my element: '+' trace, BC, speed, flux jump (A1-A8) ---------------------
-  double fn[NFB][3], dq[NFB][3];  // normal flux differences and jumps per slot
-  double lam0 = 0.0, lam1 = 0.0, lam2 = 0.0;  // per-face max speed (scalars: a runtime face index must not spill)
+  // fm[kb] = local '-' node | face << 16 of slot min(4*kb+t, NFN-1).  Pass A finds the per-face maximum wave speed
+  // (two loads per slot), pass B evaluates the flux jump straight into the LIFT-part B fragments, so only those
+  // 3*NFB doubles stay live.  Wall faces (main.cpp:340-345: hP = hM, normal momentum reflected) are rare: a warp
+  // that holds one runs the second variant of each pass.
+  auto wall_trace = [&](double nx, double ny, double hM, double huM, double hvM, double &huP, double &hvP, double &F2P, double &G2P,
+                        double &G3P, double &spdP) {
+    const double d = huM * nx + hvM * ny;
+    huP = fma(-2.0 * nx, d, huM);
+    hvP = fma(-2.0 * ny, d, hvM);
+    const double rr = frcp(hM), u = huP * rr, vv = hvP * rr, gh2 = (half_g * hM) * hM;
+    F2P = fma(huP, u, gh2); G2P = huP * vv; G3P = fma(hvP, vv, gh2);
+    spdP = fsqrt(fma(u, u, fma(vv, vv, 1e-300))) + fsqrt(g * hM);
+  };
+  uint32_t word[NFB];
+  uint32_t wallmask = 0;
 #pragma unroll
   for (int kb = 0; kb < NFB; ++kb) {
-    const int sl = 4 * kb + t;
-    fn[kb][0] = fn[kb][1] = fn[kb][2] = 0.0;
-    dq[kb][0] = dq[kb][1] = dq[kb][2] = 0.0;
-    if (sl < NFN) {
-      const int f = sl / NFP;
-      const int m = eo + fm[kb];
-      const uint32_t word = sLm[e * NFN + sl];
-      const int r = word & 0xffffu;
-      const double nx = af[4 + 3 * f], ny = af[5 + 3 * f];
-      const double hM = sQ[m], huM = sQ[PS + m], hvM = sQ[2 * PS + m];
-      const double F2M = sFl[m], G2M = sFl[PS + m], G3M = sFl[2 * PS + m], spdM = sFl[3 * PS + m];
-      double hP = sQ[r], huP = sQ[PS + r], hvP = sQ[2 * PS + r];
-      double F2P = sFl[r], G2P = sFl[PS + r], G3P = sFl[2 * PS + r], spdP = sFl[3 * PS + r];
-      if ((word >> 16) == 3u) {  // Wall (main.cpp:340-345): reflect the normal momentum of the '-' trace
-        const double d = huM * nx + hvM * ny;
-        hP = hM;
-        huP = fma(-2.0 * nx, d, huM);
-        hvP = fma(-2.0 * ny, d, hvM);
-        const double rr = frcp(hP), u = huP * rr, vv = hvP * rr, gh2 = (half_g * hP) * hP;
-        F2P = fma(huP, u, gh2); G2P = huP * vv; G3P = fma(hvP, vv, gh2);
-        spdP = fsqrt(fma(u, u, fma(vv, vv, 1e-300))) + fsqrt(g * hP);
-      }
-      const double sp = dmax(spdM, spdP);
-      lam0 = f == 0 ? dmax(lam0, sp) : lam0;
-      lam1 = f == 1 ? dmax(lam1, sp) : lam1;
-      lam2 = f == 2 ? dmax(lam2, sp) : lam2;
-      dq[kb][0] = hM - hP; dq[kb][1] = huM - huP; dq[kb][2] = hvM - hvP;
-      const double dG2 = G2M - G2P;
-      fn[kb][0] = fma(dq[kb][1], nx, dq[kb][2] * ny);
-      fn[kb][1] = fma(F2M - F2P, nx, dG2 * ny);
-      fn[kb][2] = fma(dG2, nx, (G3M - G3P) * ny);
-    }
+    word[kb] = sLm[e * NFN + min(4 * kb + t, NFN - 1)];
+    wallmask |= ((word[kb] >> 16) == 3u ? 1u : 0u) << kb;
   }
+  const bool any_wall = __any_sync(0xffffffffu, wallmask != 0u);
+  double lam0 = 0.0, lam1 = 0.0, lam2 = 0.0;  // per-face max speed (scalars: a runtime face index must not spill)
   if (v.lf_global) {
     lam0 = lam1 = lam2 = v.scal[p.slot];
-  } else {  // per-face max over the quad (the 4 lanes of a quad hold all face nodes of element e)
+  } else {
+    auto pass_a = [&](auto with_wall) {
+#pragma unroll
+      for (int kb = 0; kb < NFB; ++kb) {
+        const int f = fm[kb] >> 16;
+        const int m = eo + (fm[kb] & 0xffff), r = word[kb] & 0xffffu;
+        double spdP = sFl[3 * PS + r];
+        const double spdM = sFl[3 * PS + m];
+        if (decltype(with_wall)::value && ((wallmask >> kb) & 1u)) {
+          double a0, a1, a2, a3, a4;
+          wall_trace(af[4 + 3 * f], af[5 + 3 * f], sQ[m], sQ[PS + m], sQ[2 * PS + m], a0, a1, a2, a3, a4, spdP);
+        }
+        const double sp = dmax(spdM, spdP);
+        lam0 = f == 0 ? dmax(lam0, sp) : lam0;
+        lam1 = f == 1 ? dmax(lam1, sp) : lam1;
+        lam2 = f == 2 ? dmax(lam2, sp) : lam2;
+      }
+    };
+    if (any_wall) pass_a(std::true_type{}); else pass_a(std::false_type{});
+    // per-face max over the quad (the 4 lanes of a quad hold all face nodes of element e)
     lam0 = dmax(lam0, __shfl_xor_sync(0xffffffffu, lam0, 1));
     lam1 = dmax(lam1, __shfl_xor_sync(0xffffffffu, lam1, 1));
     lam2 = dmax(lam2, __shfl_xor_sync(0xffffffffu, lam2, 1));
@@ -268,72 +304,103 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
     lam2 = dmax(lam2, __shfl_xor_sync(0xffffffffu, lam2, 2));
   }
   double sfl[NFB][3];  // Fscale * dFlux_i at my slots = LIFT-part B fragments
+  auto pass_b = [&](auto with_wall) {
 #pragma unroll
   for (int kb = 0; kb < NFB; ++kb) {
-    const int sl = 4 * kb + t;
-    const int f = sl < NFN ? sl / NFP : 0;
+    const int f = fm[kb] >> 16;
+    const int m = eo + (fm[kb] & 0xffff), r = word[kb] & 0xffffu;
+    const double nx = af[4 + 3 * f], ny = af[5 + 3 * f], hfs = 0.5 * af[6 + 3 * f];
     const double l = f == 0 ? lam0 : (f == 1 ? lam1 : lam2);
-    const double hfs = 0.5 * af[6 + 3 * f];
-#pragma unroll
-    for (int i = 0; i < 3; ++i) sfl[kb][i] = hfs * fma(-l, dq[kb][i], fn[kb][i]);
+    const double hM = sQ[m], huM = sQ[PS + m], hvM = sQ[2 * PS + m];
+    const double F2M = sFl[m], G2M = sFl[PS + m], G3M = sFl[2 * PS + m];
+    double hP = sQ[r], huP = sQ[PS + r], hvP = sQ[2 * PS + r];
+    double F2P = sFl[r], G2P = sFl[PS + r], G3P = sFl[2 * PS + r];
+    if (decltype(with_wall)::value && ((wallmask >> kb) & 1u)) {
+      double spd_unused;
+      hP = hM;
+      wall_trace(nx, ny, hM, huM, hvM, huP, hvP, F2P, G2P, G3P, spd_unused);
+    }
+    const double dh = hM - hP, dhu = huM - huP, dhv = hvM - hvP, dG2 = G2M - G2P;
+    sfl[kb][0] = hfs * fma(-l, dh, fma(dhu, nx, dhv * ny));
+    sfl[kb][1] = hfs * fma(-l, dhu, fma(F2M - F2P, nx, dG2 * ny));
+    sfl[kb][2] = hfs * fma(-l, dhv, fma(dG2, nx, (G3M - G3P) * ny));
   }
+  };
+  if (any_wall) pass_b(std::true_type{}); else pass_b(std::false_type{});
+  PROF_T(4);
   __syncthreads();  // all '+' lookups into sQ/sFl are done: the tile may now be updated in place
-
-  // ---- phase 3: per field, B fragments -> DMMA -> stage update ------------------------------------------
+  PROF_T(5);
+  // ---- phase 3: B fragments -> DMMA (six independent accumulator chains: 3 fields x MB row blocks) -> stage update
   const double rx = af[0], sx = af[1], ry = af[2], sy = af[3];
-  const double dt = p.write_rhs ? 0.0 : v.scal[S_DT];
   if (bar_res) mbar_wait(bar_res, res_parity);
+  PROF_T(6);
   const int gr = lane >> 2;  // C fragment row within a row block
   const int c0 = 2 * t, c1 = 2 * t + 1;
   const int e0 = w + 4 * (c0 < 4 ? c0 : (c0 ^ 1));  // C fragment column 2t   -> element E(2t)
   const int e1 = w + 4 * (c1 < 4 ? c1 : (c1 ^ 1));  // C fragment column 2t+1 -> element E(2t+1)
+  double acc[3][MB][2];
 #pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    const double *X = i == 0 ? sQ + PS : (i == 1 ? sFl : sFl + PS);               // F_i: hu, F2, G2
-    const double *Y = i == 0 ? sQ + 2 * PS : (i == 1 ? sFl + PS : sFl + 2 * PS);  // G_i: hv, G2, G3
-    double acc[MB][2][2];  // two independent DMMA chains per row block
+  for (int rb = 0; rb < MB; ++rb) {
+    const int n = min(8 * rb + gr, NP - 1);
 #pragma unroll
-    for (int rb = 0; rb < MB; ++rb) acc[rb][0][0] = acc[rb][0][1] = acc[rb][1][0] = acc[rb][1][1] = 0.0;
+    for (int i = 0; i < 3; ++i) {
+      acc[i][rb][0] = need_res ? p.a * sR[i * TNP + e0 * NP + n] : 0.0;
+      acc[i][rb][1] = need_res ? p.a * sR[i * TNP + e1 * NP + n] : 0.0;
+    }
+  }
 #pragma unroll
-    for (int kb = 0; kb < NPB; ++kb) {
-      const int n = 4 * kb + t;
-      double ba = 0.0, bb = 0.0;
-      if (n < NP) {
-        const double xx = X[eo + n], yy = Y[eo + n];
-        ba = fma(rx, xx, ry * yy);
-        bb = fma(sx, xx, sy * yy);
-      }
+  for (int kb = 0; kb < NPB; ++kb) {
+    const int n = eo + min(4 * kb + t, NP - 1);  // padding rows of B meet zero columns of A
+    const double hu = sQ[PS + n], hv = sQ[2 * PS + n], F2 = sFl[n], G2 = sFl[PS + n], G3 = sFl[2 * PS + n];
+    double ba[3], bb[3];
+    ba[0] = fma(rx, hu, ry * hv); bb[0] = fma(sx, hu, sy * hv);
+    ba[1] = fma(rx, F2, ry * G2); bb[1] = fma(sx, F2, sy * G2);
+    ba[2] = fma(rx, G2, ry * G3); bb[2] = fma(sx, G2, sy * G3);
 #pragma unroll
-      for (int rb = 0; rb < MB; ++rb) {
-        const double a1 = C::A_REGS ? Areg[rb * KB + kb] : sA[(rb * KB + kb) * 32 + lane];
-        const double a2 = C::A_REGS ? Areg[rb * KB + NPB + kb] : sA[(rb * KB + NPB + kb) * 32 + lane];
-        dmma884(acc[rb][0][0], acc[rb][0][1], a1, ba);
-        dmma884(acc[rb][1][0], acc[rb][1][1], a2, bb);
+    for (int rb = 0; rb < MB; ++rb) {
+      const double a1 = C::A_REGS ? Areg[rb * KB + kb] : sA[(rb * KB + kb) * 32 + lane];
+      const double a2 = C::A_REGS ? Areg[rb * KB + NPB + kb] : sA[(rb * KB + NPB + kb) * 32 + lane];
+#pragma unroll
+      for (int i = 0; i < 3; ++i) dmma884(acc[i][rb][0], acc[i][rb][1], a1, ba[i]);
+#pragma unroll
+      for (int i = 0; i < 3; ++i) dmma884(acc[i][rb][0], acc[i][rb][1], a2, bb[i]);
+    }
+  }
+#pragma unroll
+  for (int kb = 0; kb < NFB; ++kb) {
+#pragma unroll
+    for (int rb = 0; rb < MB; ++rb) {
+      const double a3 = C::A_REGS ? Areg[rb * KB + 2 * NPB + kb] : sA[(rb * KB + 2 * NPB + kb) * 32 + lane];
+#pragma unroll
+      for (int i = 0; i < 3; ++i) dmma884(acc[i][rb][0], acc[i][rb][1], a3, sfl[kb][i]);
+    }
+  }
+  __syncwarp();  // every lane's B-fragment reads of this warp's elements precede the in-place update below
+  // epilogue: rows n = 8*rb + gr of elements e0, e1; acc = a*res + dt*rhs (stage mode) or rhs (write_rhs mode)
+  if (p.write_rhs) {
+#pragma unroll
+    for (int rb = 0; rb < MB; ++rb) {
+      const int n = 8 * rb + gr;
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        const long long k = kt0 + (cc ? e1 : e0);
+        if (n < NP && k >= p.k0 && k < p.k1) {
+#pragma unroll
+          for (int i = 0; i < 3; ++i) p.rhs_out[(long long)i * NP * v.K + k * NP + n] = acc[i][rb][cc];
+        }
       }
     }
-#pragma unroll
-    for (int kb = 0; kb < NFB; ++kb) {
-#pragma unroll
-      for (int rb = 0; rb < MB; ++rb) {
-        const double a3 = C::A_REGS ? Areg[rb * KB + 2 * NPB + kb] : sA[(rb * KB + 2 * NPB + kb) * 32 + lane];
-        dmma884(acc[rb][kb & 1][0], acc[rb][kb & 1][1], a3, sfl[kb][i]);
-      }
-    }
-    // epilogue: rows n = 8*rb + gr of elements e0, e1
+  } else {
 #pragma unroll
     for (int rb = 0; rb < MB; ++rb) {
       const int n = 8 * rb + gr;
       if (n < NP) {
 #pragma unroll
-        for (int cc = 0; cc < 2; ++cc) {
-          const int o = (cc ? e1 : e0) * NP + n;
-          const double rhs = acc[rb][0][cc] + acc[rb][1][cc];
-          if (p.write_rhs) {
-            const long long k = kt0 + (cc ? e1 : e0);
-            if (k >= p.k0 && k < p.k1) p.rhs_out[(long long)i * NP * v.K + k * NP + n] = rhs;
-          } else {
-            double rs = dt * rhs;
-            if (need_res) rs = fma(p.a, sR[i * TNP + o], rs);
+        for (int i = 0; i < 3; ++i) {
+#pragma unroll
+          for (int cc = 0; cc < 2; ++cc) {
+            const int o = (cc ? e1 : e0) * NP + n;
+            const double rs = acc[i][rb][cc];
             sR[i * TNP + o] = rs;
             sQ[i * PS + o] = fma(p.b, rs, sQ[i * PS + o]);
           }
@@ -343,23 +410,25 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   }
 }
 
-// per-thread constants: operator fragments, '-' node offsets of my face slots
+// per-thread constants: operator fragments scaled by `scale` (dt, or 1 in write_rhs mode), and for each of my
+// face slots min(4*kb+t, NFN-1) the '-' node offset | face << 16
 template <int NP, int NFP>
-__device__ __forceinline__ void load_constants(const StageArgs &p, const Sw2dView &v, double *Areg, double *sA, int *fm) {
+__device__ __forceinline__ void load_constants(const StageArgs &p, const Sw2dView &v, double *Areg, double *sA, int *fm, double scale) {
   using C = Cfg<NP, NFP>;
   const int tid = threadIdx.x, lane = tid & 31;
   if (C::A_REGS) {
 #pragma unroll
-    for (int i = 0; i < C::MB * C::KB; ++i) Areg[i] = __ldg(p.Afrag + i * 32 + lane);
+    for (int i = 0; i < C::MB * C::KB; ++i) Areg[i] = scale * __ldg(p.Afrag + i * 32 + lane);
   } else {
-    for (int x = tid; x < C::MB * C::KB * 32; x += kThreads) sA[x] = __ldg(p.Afrag + x);
+    for (int x = tid; x < C::MB * C::KB * 32; x += kThreads) sA[x] = scale * __ldg(p.Afrag + x);
   }
 #pragma unroll
   for (int kb = 0; kb < C::NFB; ++kb) {
-    const int sl = 4 * kb + (lane & 3);
-    fm[kb] = sl < C::NFN ? __ldg(v.fmask + sl) : 0;
+    const int sl = min(4 * kb + (lane & 3), C::NFN - 1);
+    fm[kb] = __ldg(v.fmask + sl) | ((sl / NFP) << 16);
   }
 }
+
 
 // ---- edge kernel: one tile per CTA, any tile (ragged mesh end, partially active range, write_rhs, tiles with
 // more ghost nodes than the persistent kernel's buffers hold) --------------------------------------------------
@@ -399,10 +468,11 @@ __global__ void __launch_bounds__(kThreads, 3) k_fused_edge(Sw2dView v, StageArg
   for (int x = tid; x < kTile * kAW; x += kThreads) sAff[x] = x < nload * kAW ? v.aff[kt0 * kAW + x] : 0.0;
   double Areg[C::A_REGS ? C::MB * C::KB : 1];
   int fm[C::NFB];
-  load_constants<NP, NFP>(p, v, Areg, S.A(), fm);
+  load_constants<NP, NFP>(p, v, Areg, S.A(), fm, p.write_rhs ? 1.0 : v.scal[S_DT]);
   __syncthreads();
 
-  compute_tile<NP, NFP>(v, p, sQ, sR, sAff, sLm, S.Fl(), S.A(), Areg, fm, PS, TNP + gc, kt0, need_res, nullptr, 0);
+  PROF_DECL
+  compute_tile<NP, NFP>(v, p, sQ, sR, sAff, sLm, S.Fl(), S.A(), Areg, fm, PS, TNP + gc, kt0, need_res, nullptr, 0, [] {} PROF_PASS);
   if (p.write_rhs) return;
 
   if (all_active) {
@@ -430,9 +500,15 @@ __global__ void __launch_bounds__(kThreads, 3) k_fused_edge(Sw2dView v, StageArg
 }
 
 // ---- persistent kernel: full, fully active tiles with at most Gcap ghosts, addressed through the record list
-// rec[] = {tile id, ghost count, ghost offset}.  Two tile buffers: while tile `it` is computed, the TMA copies of
-// tile it+1 (issued at the end of iteration it-1) and its ghost gathers (issued at the top of iteration it) are in
-// flight; results leave through TMA bulk stores from the same buffer. ---------------------------------------------
+// rec[] = {tile id, ghost count, ghost offset}.  Two tile buffers.  The bulk load of tile j (own nodes of q,
+// geometry, trace map) also carries record j+3 into a ring and the ghost source list of tile j+1 into the id
+// buffer paired with j's tile buffer, so the loop holds no prefetched values in registers: at the top of
+// iteration it the tile barrier says tile it, its ghosts, record it+3 and the ids of tile it+1 are in shared
+// memory; the ghost gathers of tile it+1 (8-byte cp.async from L2) are issued from those ids and fly during the
+// computation of tile it.  Results leave through bulk stores; the buffers they read are refilled after the first
+// barrier of the NEXT tile (the `mid` hook), when the stores have long drained, so no warp stalls on the drain.
+// The copy duties are spread over the warps: lane 0 of warp f < 3 moves field plane f of q and res, lane 0 of
+// warp 3 the geometry, trace map, record and ids.
 template <int NP, int NFP>
 __global__ void __launch_bounds__(kThreads, 3) k_fused_persistent(Sw2dView v, StageArgs p) {
   using C = Cfg<NP, NFP>;
@@ -440,80 +516,110 @@ __global__ void __launch_bounds__(kThreads, 3) k_fused_persistent(Sw2dView v, St
   extern __shared__ __align__(128) unsigned char smem[];
   const Smem<NP, NFP> S{smem, 2, p.G};
   const int PS = S.PS();
-  uint64_t *bar = S.Bar();  // [0],[1]: tile buffers (1 expect_tx arrival + kThreads cp.async arrivals); [2]: res
-  const int tid = threadIdx.x;
+  uint64_t *bar = S.Bar();  // [0],[1]: tile buffers (kWarps expect_tx arrivals + kThreads cp.async arrivals); [2]: res (3 arrivals)
+  int4 *ring = S.Ring();
+  const int tid = threadIdx.x, w = tid >> 5;
+  const bool leader = (tid & 31) == 0;
   const bool need_res = p.a != 0.0;
   const long long stride = v.stride;
-  const int nmine = (p.ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // list positions blockIdx.x + it*gridDim.x
-  auto rec_of = [&](int it) { return __ldg(p.rec + p.list_first + blockIdx.x + (long long)it * gridDim.x); };
+  const int nmine = (p.ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // list positions blockIdx.x + i*gridDim.x
+  const int4 *myrec = p.rec + p.list_first + blockIdx.x;
   // all threads: 8-byte gathers of a tile's ghost nodes into buffer b, then one arrival on its barrier
-  auto gather = [&](int b, int gcount, const int *ids) {
+  auto gather = [&](int b, int gcount, const int32_t *ids) {
     double *dst = S.Q(b) + TNP;
 #pragma unroll
     for (int u = 0; u < kGI; ++u) {
       const int x = tid + u * kThreads;
-      if (x < gcount)
-        for (int f = 0; f < 3; ++f) cp_async8(dst + f * PS + x, p.q_in + f * stride + ids[u]);
+      if (x < gcount) {
+        const int id = ids[x];
+        for (int f = 0; f < 3; ++f) cp_async8(dst + f * PS + x, p.q_in + f * stride + id);
+      }
     }
     cp_async_arrive(&bar[b]);
   };
-  auto load_ids = [&](const int4 &r, int *ids) {
-    const int32_t *gs = p.gflat + (((long long)r.w << 32) | (unsigned)r.z);
-#pragma unroll
-    for (int u = 0; u < kGI; ++u) ids[u] = (tid + u * kThreads < r.y) ? __ldg(gs + tid + u * kThreads) : 0;
+  // warp leaders: my share of the bulk loads of list position j into buffer b (rj = its record, rj1 = the next one)
+  auto tile_load = [&](int b, int j, const int4 &rj, const int4 &rj1) {
+    const long long kt0 = (long long)rj.x * kTile;
+    if (w < 3) {
+      mbar_expect_tx(&bar[b], C::txQ);
+      bulk_g2s(S.Q(b) + w * PS, p.q_in + w * stride + kt0 * NP, C::txQ, &bar[b]);
+    } else {
+      const bool has_rec = j + 3 < nmine, has_ids = j + 1 < nmine && rj1.y > 0;
+      const uint32_t idb = has_ids ? sizeof(int32_t) * rj1.y : 0;
+      mbar_expect_tx(&bar[b], C::txMeta + (has_rec ? 16u : 0u) + idb);
+      bulk_g2s(S.Lm(b), p.lmap + kt0 * C::NFN, sizeof(uint32_t) * kTile * C::NFN, &bar[b]);
+      bulk_g2s(S.Aff(b), v.aff + kt0 * kAW, sizeof(double) * kTile * kAW, &bar[b]);
+      if (has_rec) bulk_g2s(&ring[(j + 3) & 7], myrec + (long long)(j + 3) * gridDim.x, 16, &bar[b]);
+      if (has_ids) bulk_g2s(S.Ids(b), p.gflat + (((long long)rj1.w << 32) | (unsigned)rj1.z), idb, &bar[b]);
+    }
+  };
+  auto res_load = [&](int tile) {
+    if (w < 3) {
+      mbar_expect_tx(&bar[2], C::txQ);
+      bulk_g2s(S.R() + w * TNP, p.res + w * stride + (long long)tile * kTile * NP, C::txQ, &bar[2]);
+    }
   };
 
   if (tid == 0) {
-    mbar_init(&bar[0], 1 + kThreads);
-    mbar_init(&bar[1], 1 + kThreads);
-    mbar_init(&bar[2], 1);
+    mbar_init(&bar[0], kWarps + kThreads);
+    mbar_init(&bar[1], kWarps + kThreads);
+    mbar_init(&bar[2], 3);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  if (tid < 3 && tid < nmine) ring[tid] = __ldg(myrec + (long long)tid * gridDim.x);
   __syncthreads();
-  int4 rcur = rec_of(0);                              // tile being computed
-  int4 rnext = nmine > 1 ? rec_of(1) : rcur;          // tile whose copies are in flight
-  int4 rnext2 = nmine > 2 ? rec_of(2) : rcur;         // tile after that
-  if (tid == 0) {
-    issue_tile_load<NP, NFP>(v, p, S, 0, rcur.x, &bar[0]);
-    if (nmine > 1) issue_tile_load<NP, NFP>(v, p, S, 1, rnext.x, &bar[1]);
-    if (need_res) issue_res_load<NP, NFP>(v, p, S, rcur.x, &bar[2]);
+  {
+    const int4 r0 = ring[0], r1 = ring[nmine > 1 ? 1 : 0], r2 = ring[nmine > 2 ? 2 : 0];
+    if (leader) {
+      tile_load(0, 0, r0, r1);
+      if (nmine > 1) tile_load(1, 1, r1, r2);
+      if (need_res) res_load(r0.x);
+    }
+    gather(0, r0.y, p.gflat + (((long long)r0.w << 32) | (unsigned)r0.z));  // first tile: ids straight from global memory
   }
-  int gi[kGI];  // ghost ids of tile `rnext`
-  load_ids(rcur, gi);
-  gather(0, rcur.y, gi);
-  if (nmine > 1) load_ids(rnext, gi);
   double Areg[C::A_REGS ? C::MB * C::KB : 1];
   int fm[C::NFB];
-  load_constants<NP, NFP>(p, v, Areg, S.A(), fm);
+  load_constants<NP, NFP>(p, v, Areg, S.A(), fm, v.scal[S_DT]);
   __syncthreads();
 
+  PROF_DECL
   for (int it = 0; it < nmine; ++it) {
     const int b = it & 1;
-    const long long kt0 = (long long)rcur.x * kTile;
-    if (it + 1 < nmine) {  // ghost gathers of the next tile into the other buffer, ids of the one after into registers
-      gather(b ^ 1, rnext.y, gi);
-      if (it + 2 < nmine) load_ids(rnext2, gi);
-    }
+    PROF_T(0);
     mbar_wait(&bar[b], (it >> 1) & 1);
-    compute_tile<NP, NFP>(v, p, S.Q(b), S.R(), S.Aff(b), S.Lm(b), S.Fl(), S.A(), Areg, fm, PS, TNP + rcur.y, kt0, need_res,
-                          need_res ? &bar[2] : nullptr, it & 1);
+    PROF_T(1);
+    const int4 rc = ring[it & 7];
+    const int4 rn = ring[(it + 1 < nmine ? it + 1 : it) & 7];
+    if (it + 1 < nmine) gather(b ^ 1, rn.y, S.Ids(b));
+    const long long kt0 = (long long)rc.x * kTile;
+    // After the first barrier of this tile nobody reads the previous tile's buffers any more and its bulk stores
+    // (issued ~2000 cycles ago) have read them out: the leaders refill them without having stalled their warps.
+    auto mid = [&] {
+      if (leader && it > 0) {
+        if (w < 3) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        if (it + 1 < nmine) tile_load(b ^ 1, it + 1, rn, ring[(it + 2 < nmine ? it + 2 : it) & 7]);
+        if (need_res) res_load(rc.x);
+      }
+    };
+    compute_tile<NP, NFP>(v, p, S.Q(b), S.R(), S.Aff(b), S.Lm(b), S.Fl(), S.A(), Areg, fm, PS, TNP + rc.y, kt0, need_res,
+                          need_res ? &bar[2] : nullptr, it & 1, mid PROF_PASS);
+    PROF_T(7);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
-    if (tid == 0) {
+    PROF_T(8);
+    if (leader && w < 3) {
       const long long base = kt0 * NP;
-      for (int f = 0; f < 3; ++f) {
-        bulk_s2g(p.q_out + f * stride + base, S.Q(b) + f * PS, C::txQ);
-        bulk_s2g(p.res + f * stride + base, S.R() + f * TNP, C::txQ);
-      }
+      bulk_s2g(p.q_out + w * stride + base, S.Q(b) + w * PS, C::txQ);
+      bulk_s2g(p.res + w * stride + base, S.R() + w * TNP, C::txQ);
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-      asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // buffer b and R drained -> refill them
-      if (it + 2 < nmine) issue_tile_load<NP, NFP>(v, p, S, b, rnext2.x, &bar[b]);
-      if (need_res && it + 1 < nmine) issue_res_load<NP, NFP>(v, p, S, rnext.x, &bar[2]);
     }
-    rcur = rnext;
-    rnext = rnext2;
-    if (it + 3 < nmine) rnext2 = rec_of(it + 3);
+    PROF_T(9);
   }
+  if (leader && w < 3) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+#ifdef BDG_PHASEPROF
+  if ((tid & 31) == 0 && p.prof)
+    for (int i = 0; i < 12; ++i) atomicAdd((unsigned long long *)p.prof + (tid >> 5) * 12 + i, (unsigned long long)pacc[i]);
+#endif
 }
 
 struct FusedOps {
@@ -526,6 +632,7 @@ struct FusedOps {
   std::vector<int> reg_tiles, big_tiles;  // host copies (sorted tile ids) to cut launch ranges
   int Gcap, Gmax;                         // ghost slots of the persistent / edge kernel buffers (multiples of 8)
   int Np, Nfp;
+  long long *prof = nullptr;
 };
 
 int g_sm_count[16] = {};
@@ -659,8 +766,9 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
     std::sort(ext.begin(), ext.end());
     ext.erase(std::unique(ext.begin(), ext.end()), ext.end());
     gflat.insert(gflat.end(), ext.begin(), ext.end());
+    while (gflat.size() % 4) gflat.push_back(ext.empty() ? 0 : ext.back());  // 16-byte granules: the lists travel by bulk copy
     goff[T + 1] = gflat.size();
-    Gmax = std::max(Gmax, (int)ext.size());
+    Gmax = std::max(Gmax, (int)(goff[T + 1] - goff[T]));
     for (int el = 0; el < kTile; ++el)
       for (int sl = 0; sl < Nfn; ++sl) {
         uint32_t word;
@@ -722,6 +830,10 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
     fused_release(s);
     return e;
   }
+#ifdef BDG_PHASEPROF
+  cudaMalloc((void **)&ops->prof, sizeof(long long) * kWarps * 12);
+  cudaMemset(ops->prof, 0, sizeof(long long) * kWarps * 12);
+#endif
   s->fused_ops = ops;
   return cudaSuccess;
 }
@@ -729,6 +841,21 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
 void fused_release(bdg_sw2d *s) {
   if (!s->fused_ops) return;
   FusedOps *ops = static_cast<FusedOps *>(s->fused_ops);
+#ifdef BDG_PHASEPROF
+  if (ops->prof) {
+    long long h[kWarps * 12];
+    cudaMemcpy(h, ops->prof, sizeof(h), cudaMemcpyDeviceToHost);
+    static const char *nm[12] = {"top+gather", "wait tile", "phase1", "sync1", "phase2", "sync2", "wait res", "phase3", "fence+sync3", "store+reissue", "", ""};
+    for (int w = 0; w < kWarps; ++w) {
+      long long tot = 0;
+      for (int i = 0; i < 10; ++i) tot += h[w * 12 + i];
+      fprintf(stderr, "[PHASEPROF warp %d]", w);
+      for (int i = 0; i < 10; ++i) fprintf(stderr, " %s %.1f%%", nm[i], 100.0 * h[w * 12 + i] / (tot ? tot : 1));
+      fprintf(stderr, " | total cycles %lld\n", tot);
+    }
+    cudaFree(ops->prof);
+  }
+#endif
   cudaFree(ops->Afrag); cudaFree(ops->lmap); cudaFree(ops->gflat); cudaFree(ops->goff); cudaFree(ops->rec); cudaFree(ops->biglist);
   delete ops;
   s->fused_ops = nullptr;
@@ -744,7 +871,7 @@ cudaError_t launch_fused_stage(bdg_sw2d *s, const double *q_in, double *q_out, d
   args.lmap = ops->lmap; args.gflat = ops->gflat; args.goff = ops->goff; args.rec = ops->rec; args.biglist = ops->biglist;
   args.G = ops->Gmax; args.list_first = 0; args.use_list = 0;
   args.k0 = k0; args.k1 = k1; args.tile0 = 0; args.ntiles = 0;
-  args.write_rhs = write_rhs; args.slot = slot; args.a = a; args.b = b;
+  args.write_rhs = write_rhs; args.slot = slot; args.a = a; args.b = b; args.prof = ops->prof;
 #define X(np, nfp) \
   if (ops->Np == np && ops->Nfp == nfp) return launch_t<np, nfp>(s, args, ops);
   BDG_FUSED_ORDERS(X)
