@@ -40,6 +40,7 @@ def parse():
     ap.add_argument("--ny", type=int, default=500, help="cells in y PER GPU")
     ap.add_argument("--variant", type=int, default=0, help="0 auto, 1 generic, 2 fused")
     ap.add_argument("--mode", default="simple", choices=["simple", "full"])
+    ap.add_argument("--block", default="", help="element order: '' = cell-major, 'BXxBY' = blocks of BX x BY cells (locality study)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -110,7 +111,8 @@ def build_problem(args, rank, world):
     from blitzdg_b200.partition import build_local, strip_partition
     from blitzdg_b200.synthetic import provision, structured_mesh
 
-    mesh = structured_mesh(args.shape, args.nx, args.ny * world)
+    block = tuple(int(x) for x in args.block.split("x")) if args.block else None
+    mesh = structured_mesh(args.shape, args.nx, args.ny * world, block=block)
     if world == 1:
         ctx = provision(mesh, args.order).get_DGContext()
         halo = None

@@ -44,13 +44,15 @@ int fail(bdg_sw2d *s, int code, const char *fmt, ...) {
 
 // ---- layout conversion on the device -------------------------------------------------------------
 // in: row-major [R][K] (k fastest, the reference's blitz storage) -> out: element-major [K][R]
-__global__ void k_rowmajor_to_elem(const double *__restrict__ in, double *__restrict__ out, int R, long long K, int KB) {
+// perm (optional): device element k holds the caller's element perm[k] (sw2d_order.cu)
+__global__ void k_rowmajor_to_elem(const double *__restrict__ in, double *__restrict__ out, int R, long long K, int KB,
+                                   const int32_t *__restrict__ perm) {
   extern __shared__ double tile[];  // [R][KB+1]
   const long long k0 = (long long)blockIdx.x * KB;
   const int nk = (int)min((long long)KB, K - k0);
   for (int x = threadIdx.x; x < R * KB; x += blockDim.x) {
     const int n = x / KB, tk = x - n * KB;
-    if (tk < nk) tile[n * (KB + 1) + tk] = in[(long long)n * K + k0 + tk];
+    if (tk < nk) tile[n * (KB + 1) + tk] = in[(long long)n * K + (perm ? (long long)perm[k0 + tk] : k0 + tk)];
   }
   __syncthreads();
   for (int x = threadIdx.x; x < nk * R; x += blockDim.x) {
@@ -58,7 +60,8 @@ __global__ void k_rowmajor_to_elem(const double *__restrict__ in, double *__rest
     out[k0 * R + x] = tile[n * (KB + 1) + tk];
   }
 }
-__global__ void k_elem_to_rowmajor(const double *__restrict__ in, double *__restrict__ out, int R, long long K, int KB) {
+__global__ void k_elem_to_rowmajor(const double *__restrict__ in, double *__restrict__ out, int R, long long K, int KB,
+                                   const int32_t *__restrict__ perm) {
   extern __shared__ double tile[];
   const long long k0 = (long long)blockIdx.x * KB;
   const int nk = (int)min((long long)KB, K - k0);
@@ -69,7 +72,7 @@ __global__ void k_elem_to_rowmajor(const double *__restrict__ in, double *__rest
   __syncthreads();
   for (int x = threadIdx.x; x < R * KB; x += blockDim.x) {
     const int n = x / KB, tk = x - n * KB;
-    if (tk < nk) out[(long long)n * K + k0 + tk] = tile[n * (KB + 1) + tk];
+    if (tk < nk) out[(long long)n * K + (perm ? (long long)perm[k0 + tk] : k0 + tk)] = tile[n * (KB + 1) + tk];
   }
 }
 
@@ -104,7 +107,7 @@ int upload_transposed(bdg_sw2d *s, const double *host, double *dev, int R, long 
   if (!tmp) return fail(s, BDG_E_CUDA, "staging allocation of %zu doubles failed", (size_t)R * K);
   CU(cudaMemcpyAsync(tmp, host, sizeof(double) * (size_t)R * K, cudaMemcpyHostToDevice, s->stream));
   const int KB = tile_kb(R);
-  k_rowmajor_to_elem<<<(unsigned)((K + KB - 1) / KB), 256, sizeof(double) * R * (KB + 1), s->stream>>>(tmp, dev, R, K, KB);
+  k_rowmajor_to_elem<<<(unsigned)((K + KB - 1) / KB), 256, sizeof(double) * R * (KB + 1), s->stream>>>(tmp, dev, R, K, KB, s->d_perm);
   s->launches++;
   CU(cudaGetLastError());
   return BDG_OK;
@@ -113,7 +116,7 @@ int download_transposed(bdg_sw2d *s, const double *dev, double *host, int R, lon
   double *tmp = staging(s, (size_t)R * K);
   if (!tmp) return fail(s, BDG_E_CUDA, "staging allocation failed");
   const int KB = tile_kb(R);
-  k_elem_to_rowmajor<<<(unsigned)((K + KB - 1) / KB), 256, sizeof(double) * R * (KB + 1), s->stream>>>(dev, tmp, R, K, KB);
+  k_elem_to_rowmajor<<<(unsigned)((K + KB - 1) / KB), 256, sizeof(double) * R * (KB + 1), s->stream>>>(dev, tmp, R, K, KB, s->d_perm);
   s->launches++;
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(host, tmp, sizeof(double) * (size_t)R * K, cudaMemcpyDeviceToHost, s->stream));
@@ -154,7 +157,7 @@ extern "C" void bdg_sw2d_destroy(bdg_sw2d *s) {
   fused_release(s);
   void *ptrs[] = {s->q[0], s->q[1], s->res, s->rhs, s->sflux, s->d_Dr, s->d_Ds, s->d_Lift, s->d_Filt, s->d_rx, s->d_sx,
                   s->d_ry, s->d_sy, s->d_nx, s->d_ny, s->d_Fscale, s->d_aff, s->d_H, s->d_Hx, s->d_Hy, s->d_vmapP,
-                  s->d_fmask, s->d_bctag, s->d_facetag, s->d_scal, s->d_send_nodes, s->d_sendbuf};
+                  s->d_fmask, s->d_bctag, s->d_facetag, s->d_scal, s->d_send_nodes, s->d_sendbuf, s->d_perm};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   free(s->h_nbr); free(s->h_send_off); free(s->h_recv_off);
@@ -209,7 +212,40 @@ static int create_impl(bdg_sw2d *s, const bdg_dgcontext2d *c, const bdg_sw2d_par
       if (bctag[fc * Nfp + j] != t0) { facetag[fc] = 255; face_uniform = false; }
   }
 
+  // Device element order (sw2d_order.cu): compact 32-element patches for the fused kernel's tiles.  From here on
+  // every per-element table is built in device order; perm[k_dev] = caller's element.
+  const int n_interior_in = (halo && halo->n_interior > 0 && halo->n_interior <= K) ? halo->n_interior : (halo && halo->n_neighbors > 0 ? 0 : K);
+  std::vector<int32_t> perm, inv, vmapP_dev;
+  build_element_order(c->vmapP, Np, Nfp, Nf, K, n_interior_in, 32, perm);
+  const bool renum = !perm.empty();
+  const int32_t *vmapP_h = c->vmapP;
+  auto node_dev = [&](int32_t m) -> int32_t {  // volume node id: caller's numbering -> device numbering (ghost slots unchanged)
+    if (!renum || (size_t)m >= s->nT) return m;
+    return (int32_t)(m % Np + (long long)Np * inv[m / Np]);
+  };
+  if (renum) {
+    inv.resize(K);
+    for (int k = 0; k < K; ++k) inv[perm[k]] = k;
+    vmapP_dev.resize(s->nF);
+    std::vector<uint8_t> bt(s->nF), ft((size_t)K * Nf);
+    for (long long k = 0; k < K; ++k) {
+      const long long ko = perm[k];
+      for (int sl = 0; sl < Nfn; ++sl) {
+        vmapP_dev[k * Nfn + sl] = node_dev(c->vmapP[ko * Nfn + sl]);
+        bt[k * Nfn + sl] = bctag[ko * Nfn + sl];
+      }
+      for (int f = 0; f < Nf; ++f) ft[k * Nf + f] = facetag[ko * Nf + f];
+    }
+    bctag.swap(bt);
+    facetag.swap(ft);
+    vmapP_h = vmapP_dev.data();
+  }
+
   CU(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+  if (renum) {
+    int rcp = dev_upload(s, &s->d_perm, perm.data(), (size_t)K);
+    if (rcp) return rcp;
+  }
   {  // the halo exchange must win the race for SM slots against the interior-element kernel it overlaps with
     int lo = 0, hi = 0;
     CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
@@ -232,7 +268,7 @@ static int create_impl(bdg_sw2d *s, const bdg_dgcontext2d *c, const bdg_sw2d_par
   if ((rc = dev_upload(s, &s->d_Ds, c->Ds, (size_t)Np * Np))) return rc;
   if ((rc = dev_upload(s, &s->d_Lift, c->Lift, (size_t)Np * Nfn))) return rc;
   if (c->Filt && (rc = dev_upload(s, &s->d_Filt, c->Filt, (size_t)Np * Np))) return rc;
-  if ((rc = dev_upload(s, &s->d_vmapP, c->vmapP, s->nF))) return rc;
+  if ((rc = dev_upload(s, &s->d_vmapP, vmapP_h, s->nF))) return rc;
   if ((rc = dev_upload(s, &s->d_fmask, fmask.data(), (size_t)Nfn))) return rc;
   if ((rc = dev_upload(s, &s->d_bctag, bctag.data(), s->nF))) return rc;
   if ((rc = dev_upload(s, &s->d_facetag, facetag.data(), (size_t)K * Nf))) return rc;
@@ -288,6 +324,11 @@ static int create_impl(bdg_sw2d *s, const bdg_dgcontext2d *c, const bdg_sw2d_par
       }
     if (ok) {
       s->is_affine = 1;
+      if (renum) {
+        std::vector<double> a2(aff.size());
+        for (long long k = 0; k < K; ++k) memcpy(&a2[k * W], &aff[(size_t)perm[k] * W], sizeof(double) * W);
+        aff.swap(a2);
+      }
       if ((rc = dev_upload(s, &s->d_aff, aff.data(), aff.size()))) return rc;
       CU(cudaStreamSynchronize(s->stream));
     }
@@ -297,7 +338,7 @@ static int create_impl(bdg_sw2d *s, const bdg_dgcontext2d *c, const bdg_sw2d_par
   s->rank = halo ? halo->rank : 0;
   s->nranks = halo ? halo->nranks : 1;
   s->n_nbr = halo ? halo->n_neighbors : 0;
-  s->n_interior = (halo && halo->n_interior > 0 && halo->n_interior <= K) ? halo->n_interior : (halo && s->n_nbr > 0 ? 0 : K);
+  s->n_interior = n_interior_in;
   if (s->n_nbr > 0) {
     const int nn = s->n_nbr;
     s->h_nbr = (int32_t *)malloc(sizeof(int32_t) * nn);
@@ -313,7 +354,7 @@ static int create_impl(bdg_sw2d *s, const bdg_dgcontext2d *c, const bdg_sw2d_par
       for (int j = s->h_send_off[i]; j < s->h_send_off[i + 1]; ++j) {
         const int32_t m = halo->send_nodes[j];
         if (m < 0 || (size_t)m >= s->nT) return fail(s, BDG_E_INVALID, "send_nodes[%d]=%d out of range", j, m);
-        pk[j] = m;
+        pk[j] = node_dev(m);
         pk[s->n_send + j] = i;
       }
     memcpy(pk.data() + 2 * (size_t)s->n_send, s->h_send_off, sizeof(int32_t) * (nn + 1));
@@ -337,7 +378,7 @@ static int create_impl(bdg_sw2d *s, const bdg_dgcontext2d *c, const bdg_sw2d_par
 
   s->fused_ok = 0;
   if (s->is_affine && face_uniform && !v.use_filter && fused_supported(s)) {
-    cudaError_t e = fused_prepare(s, c->Dr, c->Ds, c->Lift, c->vmapP, facetag.data());
+    cudaError_t e = fused_prepare(s, c->Dr, c->Ds, c->Lift, vmapP_h, facetag.data());
     if (e != cudaSuccess) return fail(s, BDG_E_CUDA, "fused_prepare: %s", cudaGetErrorString(e));
     s->fused_ok = s->fused_ops != nullptr;
   }

@@ -64,6 +64,7 @@ struct bdg_sw2d {
   double *d_Dr, *d_Ds, *d_Lift, *d_Filt, *d_rx, *d_sx, *d_ry, *d_sy, *d_nx, *d_ny, *d_Fscale, *d_aff;
   double *d_H, *d_Hx, *d_Hy;
   int32_t *d_vmapP, *d_fmask;
+  int32_t *d_perm;      // device element k = caller's element d_perm[k] (sw2d_order.cu); NULL = identity
   uint8_t *d_bctag, *d_facetag;
   double *d_scal;
   void *fused_ops;      // operator fragments of the fused path (device), NULL if unsupported
@@ -110,3 +111,6 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
 cudaError_t launch_fused_stage(bdg_sw2d *s, const double *q_in, double *q_out, double *res, int k0, int k1, double a,
                                double b, int write_rhs, double *rhs_out, int slot);
 void fused_release(bdg_sw2d *s);
+// device element order (sw2d_order.cu): perm[new] = old, empty = identity
+#include <vector>
+void build_element_order(const int32_t *vmapP, int Np, int Nfp, int Nf, int K, int n_interior, int tile, std::vector<int32_t> &perm);

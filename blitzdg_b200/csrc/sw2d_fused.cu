@@ -32,6 +32,7 @@
 // before the contraction (exact for affine elements up to round-off).
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <type_traits>
 #include <vector>
 
@@ -39,6 +40,9 @@
 
 namespace {
 
+#ifndef BDG_MINBLOCKS
+#define BDG_MINBLOCKS 3
+#endif
 constexpr int kWarps = 4;
 constexpr int kThreads = kWarps * 32;
 constexpr int kTile = kWarps * 8;  // elements per CTA tile
@@ -510,7 +514,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_fused_edge(Sw2dView v, StageArg
 // The copy duties are spread over the warps: lane 0 of warp f < 3 moves field plane f of q and res, lane 0 of
 // warp 3 the geometry, trace map, record and ids.
 template <int NP, int NFP>
-__global__ void __launch_bounds__(kThreads, 3) k_fused_persistent(Sw2dView v, StageArgs p) {
+__global__ void __launch_bounds__(kThreads, BDG_MINBLOCKS) k_fused_persistent(Sw2dView v, StageArgs p) {
   using C = Cfg<NP, NFP>;
   constexpr int TNP = C::TNP;
   extern __shared__ __align__(128) unsigned char smem[];
@@ -795,8 +799,23 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
   std::vector<int> sorted = cnt;
   std::sort(sorted.begin(), sorted.end());
   int cap = sorted[(size_t)((ntiles - 1) * 0.97)];
+  {  // as long as the persistent kernel keeps its CTAs per SM, every tile is a regular tile (phase-1 work follows the
+     // tile's own ghost count, only the buffer size follows the cap)
+    size_t per_g = 0, fixed = 0;
+#define X(np, nfp) \
+    if (Np == np && Nfp == nfp) { fixed = Cfg<np, nfp>::total(2, 0); per_g = Cfg<np, nfp>::total(2, 8) - fixed; }
+    BDG_FUSED_ORDERS(X)
+#undef X
+    const size_t budget = (233472 / BDG_MINBLOCKS) - 1024;  // 228 KB per SM, 1 KB reserved per CTA
+    const int gfit = fixed < budget ? (int)((budget - fixed) / per_g) * 8 : 0;
+    if (Gmax <= gfit) cap = Gmax;
+    else if (cap < gfit) cap = gfit;
+  }
   if (Gmax - cap <= 16) cap = Gmax;
   const int Gcap = std::max(8, (cap + 7) / 8 * 8), Gmax8 = std::max(8, (Gmax + 7) / 8 * 8);
+  if (getenv("BDG_VERBOSE"))
+    fprintf(stderr, "[blitzdg_b200] fused tiles %d, ghosts per tile: mean %.1f median %d cap %d max %d\n", ntiles,
+            (double)gflat.size() / ntiles, sorted[ntiles / 2], Gcap, Gmax);
   if (Gmax8 > kGI * kThreads || tnp + Gmax8 > 65535) return cudaSuccess;  // not representable: stay on the generic path
   std::vector<int4> rec;
   FusedOps *ops = new FusedOps();

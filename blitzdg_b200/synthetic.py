@@ -18,8 +18,10 @@ CONFIG_GRIDS = {
 }
 
 
-def structured_arrays(shape, nx, ny, jitter=0.0, x0=-1.0, x1=1.0, y0=-1.0, y1=1.0):
-    """Returns (EToV [K][Nf] int64, Vert [Nv][3])."""
+def structured_arrays(shape, nx, ny, jitter=0.0, x0=-1.0, x1=1.0, y0=-1.0, y1=1.0, block=None):
+    """Returns (EToV [K][Nf] int64, Vert [Nv][3]).  block=(bx, by): elements ordered by blocks of bx x by cells
+    (cell-major inside a block, blocks row-major) instead of plain cell-major -- the locality study of SURVEY.md §8d;
+    the mesh is the same up to an element permutation."""
     xs = np.linspace(x0, x1, nx + 1)
     ys = np.linspace(y0, y1, ny + 1)
     X, Y = np.meshgrid(xs, ys)  # [ny+1][nx+1], vertex id = j*(nx+1)+i
@@ -32,6 +34,13 @@ def structured_arrays(shape, nx, ny, jitter=0.0, x0=-1.0, x1=1.0, y0=-1.0, y1=1.
         Y[1:-1, 1:-1] += jitter * hy * rng.uniform(-1, 1, size=(ny - 1, nx - 1))
     vert = np.stack([X.reshape(-1), Y.reshape(-1), np.zeros(X.size)], axis=1)
     i, j = np.meshgrid(np.arange(nx, dtype=np.int64), np.arange(ny, dtype=np.int64))
+    if block:
+        bx, by = block
+        if nx % bx or ny % by:
+            raise ValueError("block %s does not divide the %dx%d grid" % (block, nx, ny))
+        # [ny/by][by][nx/bx][bx] -> [ny/by][nx/bx][by][bx]
+        i = i.reshape(ny // by, by, nx // bx, bx).transpose(0, 2, 1, 3)
+        j = j.reshape(ny // by, by, nx // bx, bx).transpose(0, 2, 1, 3)
     v00 = (j * (nx + 1) + i).reshape(-1)
     v10, v01, v11 = v00 + 1, v00 + nx + 1, v00 + nx + 2
     if shape == "tri":
@@ -45,8 +54,8 @@ def structured_arrays(shape, nx, ny, jitter=0.0, x0=-1.0, x1=1.0, y0=-1.0, y1=1.
     return etov, vert
 
 
-def structured_mesh(shape, nx, ny, jitter=0.0):
-    etov, vert = structured_arrays(shape, nx, ny, jitter)
+def structured_mesh(shape, nx, ny, jitter=0.0, block=None):
+    etov, vert = structured_arrays(shape, nx, ny, jitter, block=block)
     m = MeshManager()
     m.buildMesh(etov, vert)
     return m
