@@ -378,7 +378,7 @@ static int create_impl(bdg_sw2d *s, const bdg_dgcontext2d *c, const bdg_sw2d_par
 
   s->fused_ok = 0;
   if (s->is_affine && face_uniform && !v.use_filter && fused_supported(s)) {
-    cudaError_t e = fused_prepare(s, c->Dr, c->Ds, c->Lift, vmapP_h, facetag.data());
+    cudaError_t e = fused_prepare(s, c->Dr, c->Ds, c->Lift, vmapP_h, facetag.data(), fmask.data());
     if (e != cudaSuccess) return fail(s, BDG_E_CUDA, "fused_prepare: %s", cudaGetErrorString(e));
     s->fused_ok = s->fused_ops != nullptr;
   }

@@ -107,7 +107,7 @@ cudaError_t launch_wait_epoch(bdg_sw2d *s, unsigned long long epoch);
 // fused DMMA path (affine triangles): q_in -> q_out, res in place, elements [k0,k1)
 int fused_supported(const bdg_sw2d *s);
 cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const double *Lift, const int32_t *vmapP,
-                          const uint8_t *facetag);  // host arrays of create; sets s->fused_ops when the path applies
+                          const uint8_t *facetag, const int32_t *fmask);  // host arrays of create; sets s->fused_ops when the path applies
 cudaError_t launch_fused_stage(bdg_sw2d *s, const double *q_in, double *q_out, double *res, int k0, int k1, double a,
                                double b, int write_rhs, double *rhs_out, int slot);
 void fused_release(bdg_sw2d *s);

@@ -107,7 +107,7 @@ __device__ __forceinline__ double frcp(double x) {
   e = fma(-x, r, 1.0);
   return fma(r, e, r);
 }
-// sqrt(x), x > 0: coupled Newton on (sqrt, 1/(2 sqrt)) from the MUFU rsqrt seed, two final corrections
+// sqrt(x), x > 0: coupled Newton on (sqrt, 1/(2 sqrt)) from the MUFU rsqrt seed, one final correction
 __device__ __forceinline__ double fsqrt(double x) {
   double r;
   asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
@@ -115,9 +115,7 @@ __device__ __forceinline__ double fsqrt(double x) {
   double e = fma(-hh, s, 0.5);
   s = fma(s, e, s);
   hh = fma(hh, e, hh);
-  e = fma(-s, s, x);
-  s = fma(e, hh, s);
-  e = fma(-s, s, x);
+  e = fma(-s, s, x);  // seed error d -> ~1.5 d^2 after the coupled step -> O(d^4) after this correction (d <= 2^-20)
   return fma(e, hh, s);
 }
 
@@ -171,6 +169,7 @@ struct StageArgs {
   int tile0, ntiles;      // tiles [tile0, tile0 + ntiles) of this launch
   int write_rhs;
   int slot;               // scal slot of the global LF speed
+  const int32_t *slotinfo;  // [4*NFB]: face-slot arrangement: local '-' node | face << 16 | slot << 20 per B-fragment position
   long long *prof;        // BDG_PHASEPROF builds: [kWarps][12] cycle sums
   double a, b;            // LSERK4 stage coefficients
 };
@@ -256,7 +255,7 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   PROF_T(3);
 
   // ---- phase 2: face slots of my element: '+' trace, BC, speed, flux jump (A1-A8) ---------------------
-  // fm[kb] = local '-' node | face << 16 of slot min(4*kb+t, NFN-1).  Pass A finds the per-face maximum wave speed
+  // fm[kb] = local '-' node | face << 16 | slot << 20 of the face slot at my position 4*kb+t (arrange_slots).  Pass A finds the per-face maximum wave speed
   // (two loads per slot), pass B evaluates the flux jump straight into the LIFT-part B fragments, so only those
   // 3*NFB doubles stay live.  Wall faces (main.cpp:340-345: hP = hM, normal momentum reflected) are rare: a warp
   // that holds one runs the second variant of each pass.
@@ -273,7 +272,7 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   uint32_t wallmask = 0;
 #pragma unroll
   for (int kb = 0; kb < NFB; ++kb) {
-    word[kb] = sLm[e * NFN + min(4 * kb + t, NFN - 1)];
+    word[kb] = sLm[e * NFN + (fm[kb] >> 20)];
     wallmask |= ((word[kb] >> 16) == 3u ? 1u : 0u) << kb;
   }
   const bool any_wall = __any_sync(0xffffffffu, wallmask != 0u);
@@ -284,7 +283,7 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
     auto pass_a = [&](auto with_wall) {
 #pragma unroll
       for (int kb = 0; kb < NFB; ++kb) {
-        const int f = fm[kb] >> 16;
+        const int f = (fm[kb] >> 16) & 15;
         const int m = eo + (fm[kb] & 0xffff), r = word[kb] & 0xffffu;
         double spdP = sFl[3 * PS + r];
         const double spdM = sFl[3 * PS + m];
@@ -311,7 +310,7 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   auto pass_b = [&](auto with_wall) {
 #pragma unroll
   for (int kb = 0; kb < NFB; ++kb) {
-    const int f = fm[kb] >> 16;
+    const int f = (fm[kb] >> 16) & 15;
     const int m = eo + (fm[kb] & 0xffff), r = word[kb] & 0xffffu;
     const double nx = af[4 + 3 * f], ny = af[5 + 3 * f], hfs = 0.5 * af[6 + 3 * f];
     const double l = f == 0 ? lam0 : (f == 1 ? lam1 : lam2);
@@ -415,7 +414,7 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
 }
 
 // per-thread constants: operator fragments scaled by `scale` (dt, or 1 in write_rhs mode), and for each of my
-// face slots min(4*kb+t, NFN-1) the '-' node offset | face << 16
+// B-fragment positions 4*kb+t the face slot that sits there: '-' node offset | face << 16 | slot << 20
 template <int NP, int NFP>
 __device__ __forceinline__ void load_constants(const StageArgs &p, const Sw2dView &v, double *Areg, double *sA, int *fm, double scale) {
   using C = Cfg<NP, NFP>;
@@ -427,10 +426,7 @@ __device__ __forceinline__ void load_constants(const StageArgs &p, const Sw2dVie
     for (int x = tid; x < C::MB * C::KB * 32; x += kThreads) sA[x] = scale * __ldg(p.Afrag + x);
   }
 #pragma unroll
-  for (int kb = 0; kb < C::NFB; ++kb) {
-    const int sl = min(4 * kb + (lane & 3), C::NFN - 1);
-    fm[kb] = __ldg(v.fmask + sl) | ((sl / NFP) << 16);
-  }
+  for (int kb = 0; kb < C::NFB; ++kb) fm[kb] = __ldg(p.slotinfo + 4 * kb + (lane & 3));
 }
 
 
@@ -530,13 +526,18 @@ __global__ void __launch_bounds__(kThreads, BDG_MINBLOCKS) k_fused_persistent(Sw
   const int4 *myrec = p.rec + p.list_first + blockIdx.x;
   // all threads: 8-byte gathers of a tile's ghost nodes into buffer b, then one arrival on its barrier
   auto gather = [&](int b, int gcount, const int32_t *ids) {
-    double *dst = S.Q(b) + TNP;
+    double *dst = S.Q(b) + TNP + tid;
+    const double *q0 = p.q_in;
+    int id[kGI];
+#pragma unroll
+    for (int u = 0; u < kGI; ++u) id[u] = tid + u * kThreads < gcount ? ids[tid + u * kThreads] : -1;
 #pragma unroll
     for (int u = 0; u < kGI; ++u) {
-      const int x = tid + u * kThreads;
-      if (x < gcount) {
-        const int id = ids[x];
-        for (int f = 0; f < 3; ++f) cp_async8(dst + f * PS + x, p.q_in + f * stride + id);
+      if (id[u] >= 0) {
+        const double *src = q0 + id[u];
+        cp_async8(dst + u * kThreads, src);
+        cp_async8(dst + u * kThreads + PS, src + stride);
+        cp_async8(dst + u * kThreads + 2 * PS, src + 2 * stride);
       }
     }
     cp_async_arrive(&bar[b]);
@@ -628,6 +629,7 @@ __global__ void __launch_bounds__(kThreads, BDG_MINBLOCKS) k_fused_persistent(Sw
 
 struct FusedOps {
   double *Afrag;
+  int32_t *slotinfo;
   uint32_t *lmap;
   int32_t *gflat;
   long long *goff;
@@ -700,7 +702,7 @@ cudaError_t launch_t(bdg_sw2d *s, StageArgs a, const FusedOps *ops) {
 }
 
 template <int NP, int NFP>
-void build_afrag(const double *Dr, const double *Ds, const double *Lift, std::vector<double> &out) {
+void build_afrag(const double *Dr, const double *Ds, const double *Lift, const std::vector<int> &pos2slot, std::vector<double> &out) {
   using C = Cfg<NP, NFP>;
   constexpr int NPB = C::NPB, KB = C::KB, MB = C::MB, NFN = C::NFN;
   out.assign((size_t)MB * KB * 32, 0.0);
@@ -717,12 +719,80 @@ void build_afrag(const double *Dr, const double *Ds, const double *Lift, std::ve
             const int j = 4 * (kb - NPB) + lane % 4;
             if (j < NP) val = -Ds[row * NP + j];
           } else {
-            const int j = 4 * (kb - 2 * NPB) + lane % 4;
-            if (j < NFN) val = Lift[row * NFN + j];
+            const int sl = pos2slot[4 * (kb - 2 * NPB) + lane % 4];  // -1: padding position (its B entry duplicates a neighbour)
+            if (sl >= 0) val = Lift[row * NFN + sl];
           }
         }
         out[((size_t)rb * KB + kb) * 32 + lane] = val;
       }
+}
+
+// Face-slot arrangement.  The LIFT part of the contraction may take the Nfn face slots in any order (a column
+// permutation of LIFT); the order decides which shared-memory banks the 16 lanes of a half warp hit when they
+// read the '-' traces (element stride Np, 4 elements x 4 positions per k-block) and the '+' traces (wherever the
+// mesh puts the neighbours).  A short local search over position swaps minimises the wavefronts of those loads,
+// the '+' side counted on a sample of the mesh's own tiles.  pos2slot[j] = slot at B-fragment position j, -1 = pad.
+void arrange_slots(int Np, int Nfn, int NFB, const int32_t *fmask, const std::vector<uint32_t> &lmap, int ntiles_full,
+                   std::vector<int> &pos2slot) {
+  const int NPOS = 4 * NFB;
+  pos2slot.assign(NPOS, -1);
+  for (int j = 0; j < Nfn; ++j) pos2slot[j] = j;
+  std::vector<int> samples;
+  for (int i = 0; i < 32 && ntiles_full > 0; ++i) samples.push_back((int)((long long)i * ntiles_full / 32));
+  samples.erase(std::unique(samples.begin(), samples.end()), samples.end());
+  auto mult = [](const int *addr, int n) {  // wavefronts of one 16-lane 8-byte access: max distinct addresses per bank
+    int worst = 1;
+    for (int b = 0; b < 16; ++b) {
+      int seen[16], ns = 0;
+      for (int i = 0; i < n; ++i) {
+        if ((addr[i] & 15) != b) continue;
+        bool dup = false;
+        for (int q = 0; q < ns; ++q) dup = dup || seen[q] == addr[i];
+        if (!dup) seen[ns++] = addr[i];
+      }
+      worst = std::max(worst, ns);
+    }
+    return worst;
+  };
+  auto group_cost = [&](const int *grp) {  // grp[4]: slots at positions 4*kb .. 4*kb+3
+    int addr[16], n = 0;
+    long long cost = 0;
+    for (int c = 0; c < 4; ++c)
+      for (int t = 0; t < 4; ++t)
+        if (grp[t] >= 0) addr[n++] = 4 * c * Np + fmask[grp[t]];
+    cost += (long long)mult(addr, n) * 8 * (long long)samples.size();
+    for (int T : samples)
+      for (int w = 0; w < 4; ++w)
+        for (int half = 0; half < 2; ++half) {
+          n = 0;
+          for (int cc = 0; cc < 4; ++cc) {
+            const int c = 4 * half + cc, e = w + 4 * (c < 4 ? c : (c ^ 1));
+            for (int t = 0; t < 4; ++t)
+              if (grp[t] >= 0) addr[n++] = (int)(lmap[((size_t)T * kTile + e) * Nfn + grp[t]] & 0xffffu);
+          }
+          cost += mult(addr, n);
+        }
+    return cost;
+  };
+  std::vector<long long> gc(NFB);
+  for (int kb = 0; kb < NFB; ++kb) gc[kb] = group_cost(&pos2slot[4 * kb]);
+  uint64_t rng = 0x9E3779B97F4A7C15ull;
+  auto rnd = [&](int n) { rng = rng * 6364136223846793005ull + 1442695040888963407ull; return (int)((rng >> 33) % (uint64_t)n); };
+  for (int iter = 0; iter < 4000 && NFB > 1; ++iter) {
+    const int a = rnd(NPOS), b = rnd(NPOS);
+    const int ka = a / 4, kb = b / 4;
+    if (ka == kb || pos2slot[a] == pos2slot[b]) continue;
+    std::swap(pos2slot[a], pos2slot[b]);
+    bool ok = true;  // every k-block keeps at least one real slot (pads duplicate it)
+    for (int k : {ka, kb}) ok = ok && (pos2slot[4 * k] >= 0 || pos2slot[4 * k + 1] >= 0 || pos2slot[4 * k + 2] >= 0 || pos2slot[4 * k + 3] >= 0);
+    const long long na = ok ? group_cost(&pos2slot[4 * ka]) : 0, nb = ok ? group_cost(&pos2slot[4 * kb]) : 0;
+    if (ok && na + nb <= gc[ka] + gc[kb]) {
+      gc[ka] = na;
+      gc[kb] = nb;
+    } else {
+      std::swap(pos2slot[a], pos2slot[b]);
+    }
+  }
 }
 
 #define BDG_FUSED_ORDERS(X) X(3, 2) X(6, 3) X(10, 4) X(15, 5) X(21, 6)
@@ -742,14 +812,9 @@ int fused_supported(const bdg_sw2d *s) {
 // host arrays of create (vmapP entries >= Np*K address halo slots and are always ghosts).  Sets fused_ops on
 // success; leaves it NULL (generic path) when a tile needs more ghost slots than the kernel can carry.
 cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const double *Lift, const int32_t *vmapP,
-                          const uint8_t *facetag) {
+                          const uint8_t *facetag, const int32_t *fmask) {
   const int Np = s->v.Np, Nfp = s->v.Nfp, Nfn = s->v.Nfn, K = s->v.K;
-  std::vector<double> frag;
-#define X(np, nfp) \
-  if (Np == np && Nfp == nfp) build_afrag<np, nfp>(Dr, Ds, Lift, frag);
-  BDG_FUSED_ORDERS(X)
-#undef X
-  if (frag.empty()) return cudaErrorNotSupported;
+  if (!fused_supported(s)) return cudaErrorNotSupported;
 
   const int ntiles = (K + kTile - 1) / kTile;
   const int tnp = kTile * Np;
@@ -791,6 +856,27 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
         lmap[((size_t)kt0 + el) * Nfn + sl] = word;
       }
   }
+  // face-slot arrangement, operator fragments in that arrangement, per-position slot table
+  const int NFB = (Nfn + 3) / 4;
+  std::vector<int> pos2slot;
+  arrange_slots(Np, Nfn, NFB, fmask, lmap, K / kTile, pos2slot);
+  std::vector<double> frag;
+#define X(np, nfp) \
+  if (Np == np && Nfp == nfp) build_afrag<np, nfp>(Dr, Ds, Lift, pos2slot, frag);
+  BDG_FUSED_ORDERS(X)
+#undef X
+  std::vector<int32_t> slotinfo(4 * NFB);
+  for (int j = 0; j < 4 * NFB; ++j) {
+    int sl = pos2slot[j];
+    for (int t = 0; sl < 0 && t < 4; ++t) sl = pos2slot[j / 4 * 4 + t];  // pad: duplicate a real slot of the same k-block
+    slotinfo[j] = fmask[sl] | ((sl / Nfp) << 16) | (sl << 20);
+  }
+  if (getenv("BDG_VERBOSE")) {
+    fprintf(stderr, "[blitzdg_b200] face-slot arrangement:");
+    for (int j = 0; j < 4 * NFB; ++j) fprintf(stderr, " %d", pos2slot[j]);
+    fprintf(stderr, "\n");
+  }
+
   // Buffer sizing: the persistent kernel's tile buffers hold Gcap ghosts, chosen so that (almost) every tile
   // fits -- a few outliers (e.g. tiles whose elements are not neighbours of each other after a partition's
   // interior-first renumbering) must not dictate the shared memory and phase-1 work of all tiles.
@@ -834,6 +920,7 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
   if (rec.empty()) rec.push_back(make_int4(0, 0, 0, 0));
 
   ops->Np = Np; ops->Nfp = Nfp; ops->Gcap = Gcap; ops->Gmax = Gmax8;
+  ops->slotinfo = nullptr;
   ops->Afrag = nullptr; ops->lmap = nullptr; ops->gflat = nullptr; ops->goff = nullptr; ops->rec = nullptr; ops->biglist = nullptr;
   cudaError_t e;
   auto up = [&](auto **dst, const auto &vec) -> cudaError_t {
@@ -842,7 +929,7 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
     if (r != cudaSuccess) return r;
     return cudaMemcpy((void *)*dst, vec.data(), sizeof(T) * vec.size(), cudaMemcpyHostToDevice);
   };
-  if ((e = up(&ops->Afrag, frag)) != cudaSuccess || (e = up(&ops->lmap, lmap)) != cudaSuccess ||
+  if ((e = up(&ops->slotinfo, slotinfo)) != cudaSuccess || (e = up(&ops->Afrag, frag)) != cudaSuccess || (e = up(&ops->lmap, lmap)) != cudaSuccess ||
       (e = up(&ops->gflat, gflat)) != cudaSuccess || (e = up(&ops->goff, goff64)) != cudaSuccess ||
       (e = up(&ops->rec, rec)) != cudaSuccess || (e = up(&ops->biglist, big)) != cudaSuccess) {
     s->fused_ops = ops;
@@ -875,7 +962,7 @@ void fused_release(bdg_sw2d *s) {
     cudaFree(ops->prof);
   }
 #endif
-  cudaFree(ops->Afrag); cudaFree(ops->lmap); cudaFree(ops->gflat); cudaFree(ops->goff); cudaFree(ops->rec); cudaFree(ops->biglist);
+  cudaFree(ops->slotinfo); cudaFree(ops->Afrag); cudaFree(ops->lmap); cudaFree(ops->gflat); cudaFree(ops->goff); cudaFree(ops->rec); cudaFree(ops->biglist);
   delete ops;
   s->fused_ops = nullptr;
 }
@@ -890,7 +977,7 @@ cudaError_t launch_fused_stage(bdg_sw2d *s, const double *q_in, double *q_out, d
   args.lmap = ops->lmap; args.gflat = ops->gflat; args.goff = ops->goff; args.rec = ops->rec; args.biglist = ops->biglist;
   args.G = ops->Gmax; args.list_first = 0; args.use_list = 0;
   args.k0 = k0; args.k1 = k1; args.tile0 = 0; args.ntiles = 0;
-  args.write_rhs = write_rhs; args.slot = slot; args.a = a; args.b = b; args.prof = ops->prof;
+  args.write_rhs = write_rhs; args.slot = slot; args.a = a; args.b = b; args.prof = ops->prof; args.slotinfo = ops->slotinfo;
 #define X(np, nfp) \
   if (ops->Np == np && ops->Nfp == nfp) return launch_t<np, nfp>(s, args, ops);
   BDG_FUSED_ORDERS(X)
