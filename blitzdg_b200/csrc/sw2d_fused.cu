@@ -96,6 +96,9 @@ __device__ __forceinline__ void dmma884(double &d0, double &d1, double a, double
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
 
+// barrier of the kThreads compute threads (the persistent kernel has a fifth, copy-only warp that never joins it)
+__device__ __forceinline__ void compute_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kThreads) : "memory"); }
+
 __device__ __forceinline__ double dmax(double a, double b) { return a > b ? a : b; }
 
 // 1/x: MUFU seed (20+ bits) + two Newton steps; no denormal / inf handling (h > 0 here)
@@ -148,8 +151,17 @@ struct Cfg {
   static constexpr uint32_t txMeta = sizeof(uint32_t) * kTile * NFN + sizeof(double) * kTile * kAW;
   static constexpr size_t sizeA = A_REGS ? 0 : sizeof(double) * MB * KB * 32;
   // per tile buffer: Q[3][PS], Aff[kTile][13], Lm[kTile][NFN]; CTA-wide: R[3][TNP], Fl[4][PS], A, barriers
-  static size_t buf_bytes(int G) { return sizeof(double) * 3 * (TNP + G) + sizeof(double) * kTile * kAW + sizeof(uint32_t) * kTile * NFN; }
-  static size_t total(int nbuf, int G) { return nbuf * buf_bytes(G) + sizeof(double) * 3 * TNP + sizeof(double) * 4 * (TNP + G) + sizeA + 64 + 128 + (nbuf > 1 ? nbuf * sizeof(int32_t) * G : 0); }
+  static constexpr size_t buf_bytes(int G) { return sizeof(double) * 3 * (TNP + G) + sizeof(double) * kTile * kAW + sizeof(uint32_t) * kTile * NFN; }
+  static constexpr size_t total(int nbuf, int G) { return nbuf * buf_bytes(G) + sizeof(double) * 3 * TNP + sizeof(double) * 4 * (TNP + G) + sizeA + 64 + 128 + (nbuf > 1 ? nbuf * sizeof(int32_t) * G : 0); }
+  // Ghost slots of the persistent kernel's tile buffers: a COMPILE-TIME constant (every plane offset folds into the
+  // LDS/STS immediates), the largest multiple of 8 that keeps `ctas` CTAs per SM (228 KB per SM, 1 KB reserved per
+  // CTA); tiles with more ghosts run in the edge kernel.  Phase-1 work follows a tile's own ghost count, not this.
+  static constexpr int gfit(int ctas) {
+    const long budget = 233472 / ctas - 1024, fixed = (long)total(2, 0), per8 = (long)(total(2, 8) - total(2, 0));
+    const long g = budget > fixed ? (budget - fixed) / per8 * 8 : 0;
+    return (int)(g > 600 ? 600 : g);
+  }
+  static constexpr int GFIT = gfit(BDG_MINBLOCKS) >= 96 ? gfit(BDG_MINBLOCKS) : (gfit(2) >= 96 ? gfit(2) : gfit(1));
 };
 
 struct StageArgs {
@@ -219,17 +231,17 @@ __device__ __forceinline__ void phase1_nodes(const double *__restrict__ sQ, doub
 
 // The arithmetic of one tile that sits in shared memory (A1-A13 of SURVEY.md Appendix A).  sQ: [3][PS] own +
 // ghost nodes, sR: [3][TNP].  On return the tile's q and res planes hold the updated values (stage mode) -- or,
-// in write_rhs mode, rhs_out has been written and the tile is untouched.  Contains two __syncthreads() and an
+// in write_rhs mode, rhs_out has been written and the tile is untouched.  Contains two compute_sync() and an
 // optional wait on the res barrier before phase 3; the caller makes the tile visible first.
 // The operator fragments (Areg / sA) arrive pre-multiplied by dt (by 1 in write_rhs mode), so the accumulators,
 // started from a*res, end as the new res.  All three phases are branch-free on their hot path: padding slots are
 // clamped to a valid neighbour (their operator columns are zero), the wall reflection is a rare warp-level
 // fix-up pass, and every thread keeps several independent dependency chains in flight.
-template <int NP, int NFP, class Mid>
+template <int NP, int NFP>
 __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs &p, double *__restrict__ sQ, double *__restrict__ sR,
                                              const double *__restrict__ sAff, const uint32_t *__restrict__ sLm, double *__restrict__ sFl,
                                              const double *__restrict__ sA, const double *Areg, const int *fm, int PS, int nnodes, long long kt0,
-                                             bool need_res, uint64_t *bar_res, uint32_t res_parity, Mid mid PROF_ARGS) {
+                                             bool need_res, uint64_t *bar_res, uint32_t res_parity PROF_ARGS) {
   using C = Cfg<NP, NFP>;
   constexpr int NFN = C::NFN, NPB = C::NPB, NFB = C::NFB, KB = C::KB, MB = C::MB, TNP = C::TNP;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -250,8 +262,7 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
       phase1_nodes<1>(sQ, sFl, PS, threadIdx.x + i * kThreads, last, g, half_g);
   }
   PROF_T(2);
-  __syncthreads();
-  mid();  // the caller's copy duties that had to wait for the previous tile's last reader (persistent kernel)
+  compute_sync();
   PROF_T(3);
 
   // ---- phase 2: face slots of my element: '+' trace, BC, speed, flux jump (A1-A8) ---------------------
@@ -331,7 +342,7 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   };
   if (any_wall) pass_b(std::true_type{}); else pass_b(std::false_type{});
   PROF_T(4);
-  __syncthreads();  // all '+' lookups into sQ/sFl are done: the tile may now be updated in place
+  compute_sync();  // all '+' lookups into sQ/sFl are done: the tile may now be updated in place
   PROF_T(5);
   // ---- phase 3: B fragments -> DMMA (six independent accumulator chains: 3 fields x MB row blocks) -> stage update
   const double rx = af[0], sx = af[1], ry = af[2], sy = af[3];
@@ -472,7 +483,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_fused_edge(Sw2dView v, StageArg
   __syncthreads();
 
   PROF_DECL
-  compute_tile<NP, NFP>(v, p, sQ, sR, sAff, sLm, S.Fl(), S.A(), Areg, fm, PS, TNP + gc, kt0, need_res, nullptr, 0, [] {} PROF_PASS);
+  compute_tile<NP, NFP>(v, p, sQ, sR, sAff, sLm, S.Fl(), S.A(), Areg, fm, PS, TNP + gc, kt0, need_res, nullptr, 0 PROF_PASS);
   if (p.write_rhs) return;
 
   if (all_active) {
@@ -500,93 +511,136 @@ __global__ void __launch_bounds__(kThreads, 3) k_fused_edge(Sw2dView v, StageArg
 }
 
 // ---- persistent kernel: full, fully active tiles with at most Gcap ghosts, addressed through the record list
-// rec[] = {tile id, ghost count, ghost offset}.  Two tile buffers.  The bulk load of tile j (own nodes of q,
-// geometry, trace map) also carries record j+3 into a ring and the ghost source list of tile j+1 into the id
-// buffer paired with j's tile buffer, so the loop holds no prefetched values in registers: at the top of
-// iteration it the tile barrier says tile it, its ghosts, record it+3 and the ids of tile it+1 are in shared
-// memory; the ghost gathers of tile it+1 (8-byte cp.async from L2) are issued from those ids and fly during the
-// computation of tile it.  Results leave through bulk stores; the buffers they read are refilled after the first
-// barrier of the NEXT tile (the `mid` hook), when the stores have long drained, so no warp stalls on the drain.
-// The copy duties are spread over the warps: lane 0 of warp f < 3 moves field plane f of q and res, lane 0 of
-// warp 3 the geometry, trace map, record and ids.
+// rec[] = {tile id, ghost count, ghost offset}.  Warp-specialised: warps 0..3 only compute (compute_tile); warp 4
+// owns every copy -- the bulk loads of a tile's own nodes / geometry / trace map (which also carry record j+3
+// into a ring and the ghost source list of tile j+1 into an id buffer), the 8-byte cp.async ghost gathers, the res
+// loads, the bulk stores of the results and their drain -- so no compute warp ever waits on the copy engine.
+// Two tile buffers; mbarriers: full[b] (tile in buffer b landed: 1 expect_tx arrival + 32 cp.async arrivals),
+// resfull (res planes landed, or -- in a stage with a = 0 -- merely "R is free again"), done[b] (the compute warps
+// have finished the tile in buffer b).  Copy warp, step it: wait done(it-1) -> store tile it-1 -> gather the ghosts
+// of tile it+1 (ids came with tile it) -> drain -> res of tile it -> bulk load of tile it+1 into the drained buffer.
+// 2 warpgroups: warps 0..3 compute, warp 4 copies, warps 5..7 only give their registers back (setmaxnreg works per
+// warpgroup): launched at 80 registers/thread (3 CTAs/SM), the compute warpgroup grows to 136, the other shrinks to 24.
+constexpr int kThreadsWS = 2 * kThreads;
+
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
 template <int NP, int NFP>
-__global__ void __launch_bounds__(kThreads, BDG_MINBLOCKS) k_fused_persistent(Sw2dView v, StageArgs p) {
+__global__ void __launch_bounds__(kThreadsWS, BDG_MINBLOCKS) k_fused_persistent(Sw2dView v, StageArgs p) {
   using C = Cfg<NP, NFP>;
   constexpr int TNP = C::TNP;
   extern __shared__ __align__(128) unsigned char smem[];
-  const Smem<NP, NFP> S{smem, 2, p.G};
-  const int PS = S.PS();
-  uint64_t *bar = S.Bar();  // [0],[1]: tile buffers (kWarps expect_tx arrivals + kThreads cp.async arrivals); [2]: res (3 arrivals)
+  const Smem<NP, NFP> S{smem, 2, C::GFIT};
+  constexpr int PS = TNP + C::GFIT;
+  uint64_t *bar = S.Bar();  // [0],[1]: full[b]; [2]: resfull; [3],[4]: done[b]
   int4 *ring = S.Ring();
-  const int tid = threadIdx.x, w = tid >> 5;
-  const bool leader = (tid & 31) == 0;
+  const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
   const bool need_res = p.a != 0.0;
   const long long stride = v.stride;
   const int nmine = (p.ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // list positions blockIdx.x + i*gridDim.x
   const int4 *myrec = p.rec + p.list_first + blockIdx.x;
-  // all threads: 8-byte gathers of a tile's ghost nodes into buffer b, then one arrival on its barrier
-  auto gather = [&](int b, int gcount, const int32_t *ids) {
-    double *dst = S.Q(b) + TNP + tid;
-    const double *q0 = p.q_in;
-    int id[kGI];
-#pragma unroll
-    for (int u = 0; u < kGI; ++u) id[u] = tid + u * kThreads < gcount ? ids[tid + u * kThreads] : -1;
-#pragma unroll
-    for (int u = 0; u < kGI; ++u) {
-      if (id[u] >= 0) {
-        const double *src = q0 + id[u];
-        cp_async8(dst + u * kThreads, src);
-        cp_async8(dst + u * kThreads + PS, src + stride);
-        cp_async8(dst + u * kThreads + 2 * PS, src + 2 * stride);
-      }
-    }
-    cp_async_arrive(&bar[b]);
-  };
-  // warp leaders: my share of the bulk loads of list position j into buffer b (rj = its record, rj1 = the next one)
-  auto tile_load = [&](int b, int j, const int4 &rj, const int4 &rj1) {
-    const long long kt0 = (long long)rj.x * kTile;
-    if (w < 3) {
-      mbar_expect_tx(&bar[b], C::txQ);
-      bulk_g2s(S.Q(b) + w * PS, p.q_in + w * stride + kt0 * NP, C::txQ, &bar[b]);
-    } else {
-      const bool has_rec = j + 3 < nmine, has_ids = j + 1 < nmine && rj1.y > 0;
-      const uint32_t idb = has_ids ? sizeof(int32_t) * rj1.y : 0;
-      mbar_expect_tx(&bar[b], C::txMeta + (has_rec ? 16u : 0u) + idb);
-      bulk_g2s(S.Lm(b), p.lmap + kt0 * C::NFN, sizeof(uint32_t) * kTile * C::NFN, &bar[b]);
-      bulk_g2s(S.Aff(b), v.aff + kt0 * kAW, sizeof(double) * kTile * kAW, &bar[b]);
-      if (has_rec) bulk_g2s(&ring[(j + 3) & 7], myrec + (long long)(j + 3) * gridDim.x, 16, &bar[b]);
-      if (has_ids) bulk_g2s(S.Ids(b), p.gflat + (((long long)rj1.w << 32) | (unsigned)rj1.z), idb, &bar[b]);
-    }
-  };
-  auto res_load = [&](int tile) {
-    if (w < 3) {
-      mbar_expect_tx(&bar[2], C::txQ);
-      bulk_g2s(S.R() + w * TNP, p.res + w * stride + (long long)tile * kTile * NP, C::txQ, &bar[2]);
-    }
-  };
 
   if (tid == 0) {
-    mbar_init(&bar[0], kWarps + kThreads);
-    mbar_init(&bar[1], kWarps + kThreads);
-    mbar_init(&bar[2], 3);
+    mbar_init(&bar[0], 1 + 32);
+    mbar_init(&bar[1], 1 + 32);
+    mbar_init(&bar[2], 1);
+    mbar_init(&bar[3], 1);
+    mbar_init(&bar[4], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (tid < 3 && tid < nmine) ring[tid] = __ldg(myrec + (long long)tid * gridDim.x);
   __syncthreads();
-  {
-    const int4 r0 = ring[0], r1 = ring[nmine > 1 ? 1 : 0], r2 = ring[nmine > 2 ? 2 : 0];
-    if (leader) {
-      tile_load(0, 0, r0, r1);
-      if (nmine > 1) tile_load(1, 1, r1, r2);
-      if (need_res) res_load(r0.x);
+
+  if (w >= kWarps) {  // ------------------------------------------------------------------ copy warp
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
+    if (w > kWarps) return;
+    auto gather = [&](int b, int gcount, const int32_t *ids) {
+      double *dst = S.Q(b) + TNP;
+      for (int x = lane; x < gcount; x += 32) {
+        const double *src = p.q_in + ids[x];
+        cp_async8(dst + x, src);
+        cp_async8(dst + PS + x, src + stride);
+        cp_async8(dst + 2 * PS + x, src + 2 * stride);
+      }
+      cp_async_arrive(&bar[b]);
+    };
+    // lane 0: bulk loads of list position j into buffer b (rj = its record, rj1 = the next one)
+    auto tile_load = [&](int b, int j, const int4 &rj, const int4 &rj1) {
+      const long long kt0 = (long long)rj.x * kTile;
+      const bool has_rec = j + 3 < nmine, has_ids = j + 1 < nmine && rj1.y > 0;
+      const uint32_t idb = has_ids ? sizeof(int32_t) * rj1.y : 0;
+      mbar_expect_tx(&bar[b], 3 * C::txQ + C::txMeta + (has_rec ? 16u : 0u) + idb);
+      for (int f = 0; f < 3; ++f) bulk_g2s(S.Q(b) + f * PS, p.q_in + f * stride + kt0 * NP, C::txQ, &bar[b]);
+      bulk_g2s(S.Lm(b), p.lmap + kt0 * C::NFN, sizeof(uint32_t) * kTile * C::NFN, &bar[b]);
+      bulk_g2s(S.Aff(b), v.aff + kt0 * kAW, sizeof(double) * kTile * kAW, &bar[b]);
+      if (has_rec) bulk_g2s(&ring[(j + 3) & 7], myrec + (long long)(j + 3) * gridDim.x, 16, &bar[b]);
+      if (has_ids) bulk_g2s(S.Ids(b), p.gflat + (((long long)rj1.w << 32) | (unsigned)rj1.z), idb, &bar[b]);
+    };
+    auto res_ready = [&](int tile) {  // lane 0: R is free; fill it (a != 0) or just say so
+      if (need_res) {
+        mbar_expect_tx(&bar[2], 3 * C::txQ);
+        for (int f = 0; f < 3; ++f) bulk_g2s(S.R() + f * TNP, p.res + f * stride + (long long)tile * kTile * NP, C::txQ, &bar[2]);
+      } else {
+        mbar_arrive(&bar[2]);
+      }
+    };
+    auto store_tile = [&](int b, int tile) {  // lane 0
+      const long long base = (long long)tile * kTile * NP;
+      for (int f = 0; f < 3; ++f) {
+        bulk_s2g(p.q_out + f * stride + base, S.Q(b) + f * PS, C::txQ);
+        bulk_s2g(p.res + f * stride + base, S.R() + f * TNP, C::txQ);
+      }
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    };
+    {
+      const int4 r0 = ring[0], r1 = ring[nmine > 1 ? 1 : 0];
+      if (lane == 0) {
+        tile_load(0, 0, r0, r1);
+        res_ready(r0.x);
+      }
+      gather(0, r0.y, p.gflat + (((long long)r0.w << 32) | (unsigned)r0.z));  // first tile: ids straight from global memory
     }
-    gather(0, r0.y, p.gflat + (((long long)r0.w << 32) | (unsigned)r0.z));  // first tile: ids straight from global memory
+    int prev_tile = 0;
+    for (int it = 0; it < nmine; ++it) {
+      const int b = it & 1, pb = b ^ 1;
+      if (it > 0) {
+        mbar_wait(&bar[3 + pb], ((it - 1) >> 1) & 1);
+        if (lane == 0) store_tile(pb, prev_tile);
+      }
+      int4 rn = make_int4(0, 0, 0, 0), rn2 = rn;
+      if (it + 1 < nmine) {
+        mbar_wait(&bar[b], (it >> 1) & 1);  // tile it has landed: ids of tile it+1, record it+3
+        rn = ring[(it + 1) & 7];
+        rn2 = ring[(it + 2 < nmine ? it + 2 : it + 1) & 7];
+        gather(pb, rn.y, S.Ids(b));
+      }
+      const int4 rc = ring[it & 7];
+      if (lane == 0) {
+        if (it > 0) {
+          asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+          res_ready(rc.x);
+        }
+        if (it + 1 < nmine) tile_load(pb, it + 1, rn, rn2);
+      }
+      prev_tile = rc.x;
+      __syncwarp();
+    }
+    mbar_wait(&bar[3 + ((nmine - 1) & 1)], ((nmine - 1) >> 1) & 1);
+    if (lane == 0) {
+      store_tile((nmine - 1) & 1, prev_tile);
+      asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    }
+    return;
   }
+
+  // ---------------------------------------------------------------------------------------- compute warps
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 136;");
   double Areg[C::A_REGS ? C::MB * C::KB : 1];
   int fm[C::NFB];
   load_constants<NP, NFP>(p, v, Areg, S.A(), fm, v.scal[S_DT]);
-  __syncthreads();
-
+  compute_sync();
   PROF_DECL
   for (int it = 0; it < nmine; ++it) {
     const int b = it & 1;
@@ -594,33 +648,14 @@ __global__ void __launch_bounds__(kThreads, BDG_MINBLOCKS) k_fused_persistent(Sw
     mbar_wait(&bar[b], (it >> 1) & 1);
     PROF_T(1);
     const int4 rc = ring[it & 7];
-    const int4 rn = ring[(it + 1 < nmine ? it + 1 : it) & 7];
-    if (it + 1 < nmine) gather(b ^ 1, rn.y, S.Ids(b));
-    const long long kt0 = (long long)rc.x * kTile;
-    // After the first barrier of this tile nobody reads the previous tile's buffers any more and its bulk stores
-    // (issued ~2000 cycles ago) have read them out: the leaders refill them without having stalled their warps.
-    auto mid = [&] {
-      if (leader && it > 0) {
-        if (w < 3) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-        if (it + 1 < nmine) tile_load(b ^ 1, it + 1, rn, ring[(it + 2 < nmine ? it + 2 : it) & 7]);
-        if (need_res) res_load(rc.x);
-      }
-    };
-    compute_tile<NP, NFP>(v, p, S.Q(b), S.R(), S.Aff(b), S.Lm(b), S.Fl(), S.A(), Areg, fm, PS, TNP + rc.y, kt0, need_res,
-                          need_res ? &bar[2] : nullptr, it & 1, mid PROF_PASS);
+    compute_tile<NP, NFP>(v, p, S.Q(b), S.R(), S.Aff(b), S.Lm(b), S.Fl(), S.A(), Areg, fm, PS, TNP + rc.y, (long long)rc.x * kTile, need_res,
+                          &bar[2], it & 1 PROF_PASS);
     PROF_T(7);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    __syncthreads();
+    compute_sync();
+    if (tid == 0) mbar_arrive(&bar[3 + b]);
     PROF_T(8);
-    if (leader && w < 3) {
-      const long long base = kt0 * NP;
-      bulk_s2g(p.q_out + w * stride + base, S.Q(b) + w * PS, C::txQ);
-      bulk_s2g(p.res + w * stride + base, S.R() + w * TNP, C::txQ);
-      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-    }
-    PROF_T(9);
   }
-  if (leader && w < 3) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 #ifdef BDG_PHASEPROF
   if ((tid & 31) == 0 && p.prof)
     for (int i = 0; i < 12; ++i) atomicAdd((unsigned long long *)p.prof + (tid >> 5) * 12 + i, (unsigned long long)pacc[i]);
@@ -649,14 +684,17 @@ cudaError_t launch_t(bdg_sw2d *s, StageArgs a, const FusedOps *ops) {
   static int ctas_per_sm[16] = {};
   static int attr_key[16] = {};
   const int dev = s->device & 15;
-  const size_t smem_edge = C::total(1, ops->Gmax), smem_pers = C::total(2, ops->Gcap);
+  size_t smem_edge = C::total(1, ops->Gmax), smem_pers = C::total(2, ops->Gcap);
+#ifdef BDG_PHASEPROF
+  if (getenv("BDG_EXTRA_SMEM")) smem_pers += atoi(getenv("BDG_EXTRA_SMEM"));  // occupancy experiments: 1 or 2 CTAs per SM
+#endif
   cudaError_t e;
   if (attr_key[dev] != ops->Gmax * 4096 + ops->Gcap + 1) {
     if ((e = cudaFuncSetAttribute(k_fused_edge<NP, NFP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_edge)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_fused_persistent<NP, NFP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pers)) != cudaSuccess) return e;
     cudaFuncSetAttribute(k_fused_edge<NP, NFP>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     cudaFuncSetAttribute(k_fused_persistent<NP, NFP>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm[dev], k_fused_persistent<NP, NFP>, kThreads, smem_pers)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm[dev], k_fused_persistent<NP, NFP>, kThreadsWS, smem_pers)) != cudaSuccess) return e;
     if ((e = cudaDeviceGetAttribute(&g_sm_count[dev], cudaDevAttrMultiProcessorCount, s->device)) != cudaSuccess) return e;
     if (ctas_per_sm[dev] < 1) return cudaErrorLaunchOutOfResources;
     attr_key[dev] = ops->Gmax * 4096 + ops->Gcap + 1;
@@ -690,7 +728,7 @@ cudaError_t launch_t(bdg_sw2d *s, StageArgs a, const FusedOps *ops) {
       // while a halo exchange is in flight leave a few SMs one CTA short, so the NCCL send/recv kernel finds room
       if (s->comm && !s->peer_ok && s->n_nbr > 0 && a.k0 == 0 && a.k1 < s->v.K) grid -= 16;
       if (grid > m.ntiles) grid = m.ntiles;
-      k_fused_persistent<NP, NFP><<<grid, kThreads, smem_pers, s->stream>>>(s->v, m);
+      k_fused_persistent<NP, NFP><<<grid, kThreadsWS, smem_pers, s->stream>>>(s->v, m);
       s->launches++;
     }
     const int jb0 = (int)(std::lower_bound(ops->big_tiles.begin(), ops->big_tiles.end(), p0) - ops->big_tiles.begin());
@@ -884,21 +922,12 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
   for (int T = 0; T < ntiles; ++T) cnt[T] = (int)(goff[T + 1] - goff[T]);
   std::vector<int> sorted = cnt;
   std::sort(sorted.begin(), sorted.end());
-  int cap = sorted[(size_t)((ntiles - 1) * 0.97)];
-  {  // as long as the persistent kernel keeps its CTAs per SM, every tile is a regular tile (phase-1 work follows the
-     // tile's own ghost count, only the buffer size follows the cap)
-    size_t per_g = 0, fixed = 0;
+  int cap = 0;  // the persistent kernel's compile-time ghost capacity
 #define X(np, nfp) \
-    if (Np == np && Nfp == nfp) { fixed = Cfg<np, nfp>::total(2, 0); per_g = Cfg<np, nfp>::total(2, 8) - fixed; }
-    BDG_FUSED_ORDERS(X)
+  if (Np == np && Nfp == nfp) cap = Cfg<np, nfp>::GFIT;
+  BDG_FUSED_ORDERS(X)
 #undef X
-    const size_t budget = (233472 / BDG_MINBLOCKS) - 1024;  // 228 KB per SM, 1 KB reserved per CTA
-    const int gfit = fixed < budget ? (int)((budget - fixed) / per_g) * 8 : 0;
-    if (Gmax <= gfit) cap = Gmax;
-    else if (cap < gfit) cap = gfit;
-  }
-  if (Gmax - cap <= 16) cap = Gmax;
-  const int Gcap = std::max(8, (cap + 7) / 8 * 8), Gmax8 = std::max(8, (Gmax + 7) / 8 * 8);
+  const int Gcap = cap, Gmax8 = std::max(8, (Gmax + 7) / 8 * 8);
   if (getenv("BDG_VERBOSE"))
     fprintf(stderr, "[blitzdg_b200] fused tiles %d, ghosts per tile: mean %.1f median %d cap %d max %d\n", ntiles,
             (double)gflat.size() / ntiles, sorted[ntiles / 2], Gcap, Gmax);
