@@ -124,7 +124,7 @@ EXPORTS = [
     "bdg_sw2d_get_state", "bdg_sw2d_rhs", "bdg_sw2d_timestep", "bdg_sw2d_step", "bdg_sw2d_sync", "bdg_sw2d_check",
     "bdg_sw2d_set_variant", "bdg_sw2d_get_variant", "bdg_sw2d_launch_count", "bdg_sw2d_stream",
     "bdg_sw2d_algorithmic_bytes_per_stage", "bdg_nccl_unique_id", "bdg_sw2d_comm_init",
-    "bdg_sw2d_halo_pack_to_host", "bdg_sw2d_halo_set_ghosts", "bdg_version",
+    "bdg_sw2d_halo_pack_to_host", "bdg_sw2d_halo_set_ghosts", "bdg_element_order", "bdg_version",
 ]
 
 
@@ -171,6 +171,7 @@ def load():
     L.bdg_sw2d_comm_init.argtypes = [vp, vp]
     L.bdg_sw2d_halo_pack_to_host.argtypes = [vp, _dp]
     L.bdg_sw2d_halo_set_ghosts.argtypes = [vp, _dp]
+    L.bdg_element_order.argtypes = [_ip, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _ip]
     L.bdg_version.restype = C.c_int
     _lib = L
     return L

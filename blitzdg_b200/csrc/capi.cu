@@ -139,7 +139,16 @@ int dev_upload(bdg_sw2d *s, T **p, const T *host, size_t n) {
 }  // namespace
 
 // ====================================================================================== lifetime
-extern "C" int bdg_version(void) { return 100; }
+extern "C" int bdg_version(void) { return 101; }
+
+extern "C" int bdg_element_order(const int32_t *vmapP, int32_t Np, int32_t Nfp, int32_t Nfaces, int32_t K, int32_t n_interior,
+                                 int32_t *perm_out) {
+  if (!vmapP || !perm_out || Np <= 0 || Nfp <= 0 || K <= 0 || (Nfaces != 3 && Nfaces != 4)) return BDG_E_INVALID;
+  std::vector<int32_t> perm;
+  build_element_order(vmapP, Np, Nfp, Nfaces, K, n_interior, 32, perm);
+  for (int32_t k = 0; k < K; ++k) perm_out[k] = perm.empty() ? k : perm[k];
+  return BDG_OK;
+}
 
 extern "C" const char *bdg_last_error(const bdg_sw2d *s) { return s ? s->err : g_create_err; }
 

@@ -134,6 +134,14 @@ int bdg_sw2d_comm_init(bdg_sw2d *s, const void *id /* BDG_NCCL_ID_BYTES */);
 int bdg_sw2d_halo_pack_to_host(bdg_sw2d *s, double *send_buf /* 3*n_send */);
 int bdg_sw2d_halo_set_ghosts(bdg_sw2d *s, const double *recv_buf /* 3*n_ghost */);
 
+/* Introspection (host only, no GPU needed): the device element order bdg_sw2d_create would choose for this
+ * connectivity -- perm_out[k_device] = caller's element.  The reference keeps the .msh order
+ * (src/MeshManager.cpp:130-247); the device path regroups elements into compact 32-element patches
+ * (blitzdg_b200/csrc/sw2d_order.cu) and hides the permutation behind set_state/get_state/rhs.
+ * vmapP as in bdg_dgcontext2d; n_interior as in bdg_halo (K when there is no halo). */
+int bdg_element_order(const int32_t *vmapP, int32_t Np, int32_t Nfp, int32_t Nfaces, int32_t K, int32_t n_interior,
+                      int32_t *perm_out);
+
 int bdg_version(void);
 
 #ifdef __cplusplus
