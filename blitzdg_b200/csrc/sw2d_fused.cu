@@ -146,6 +146,9 @@ struct Cfg {
 #define BDG_AREGS_MAX 36
 #endif
   static constexpr bool A_REGS = (MB * KB <= BDG_AREGS_MAX);
+  // Face blocks: k-block kb < 3 of the LIFT part holds (up to 4) slots of face kb only, the remaining slots sit in
+  // the k-blocks >= 3 -- the face of a position is then a compile-time constant except in those last blocks.
+  static constexpr bool FACE_BLOCKS = NFB >= 3 && (NFP <= 4 || 3 * (NFP - 4) <= 4 * (NFB - 3));
   static constexpr int TNP = kTile * NP;      // own nodes per tile
   static constexpr uint32_t txQ = sizeof(double) * TNP;  // one field plane of a tile
   static constexpr uint32_t txMeta = sizeof(uint32_t) * kTile * NFN + sizeof(double) * kTile * kAW;
@@ -294,7 +297,8 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
     auto pass_a = [&](auto with_wall) {
 #pragma unroll
       for (int kb = 0; kb < NFB; ++kb) {
-        const int f = (fm[kb] >> 16) & 15;
+        const bool fixed_face = C::FACE_BLOCKS && kb < 3;
+        const int f = fixed_face ? kb : (fm[kb] >> 16) & 15;
         const int m = eo + (fm[kb] & 0xffff), r = word[kb] & 0xffffu;
         double spdP = sFl[3 * PS + r];
         const double spdM = sFl[3 * PS + m];
@@ -303,9 +307,15 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
           wall_trace(af[4 + 3 * f], af[5 + 3 * f], sQ[m], sQ[PS + m], sQ[2 * PS + m], a0, a1, a2, a3, a4, spdP);
         }
         const double sp = dmax(spdM, spdP);
-        lam0 = f == 0 ? dmax(lam0, sp) : lam0;
-        lam1 = f == 1 ? dmax(lam1, sp) : lam1;
-        lam2 = f == 2 ? dmax(lam2, sp) : lam2;
+        if (fixed_face) {  // the only position of this thread on face kb so far
+          if (kb == 0) lam0 = sp;
+          if (kb == 1) lam1 = sp;
+          if (kb == 2) lam2 = sp;
+        } else {
+          lam0 = f == 0 ? dmax(lam0, sp) : lam0;
+          lam1 = f == 1 ? dmax(lam1, sp) : lam1;
+          lam2 = f == 2 ? dmax(lam2, sp) : lam2;
+        }
       }
     };
     if (any_wall) pass_a(std::true_type{}); else pass_a(std::false_type{});
@@ -321,7 +331,7 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   auto pass_b = [&](auto with_wall) {
 #pragma unroll
   for (int kb = 0; kb < NFB; ++kb) {
-    const int f = (fm[kb] >> 16) & 15;
+    const int f = (C::FACE_BLOCKS && kb < 3) ? kb : (fm[kb] >> 16) & 15;
     const int m = eo + (fm[kb] & 0xffff), r = word[kb] & 0xffffu;
     const double nx = af[4 + 3 * f], ny = af[5 + 3 * f], hfs = 0.5 * af[6 + 3 * f];
     const double l = f == 0 ? lam0 : (f == 1 ? lam1 : lam2);
@@ -770,11 +780,20 @@ void build_afrag(const double *Dr, const double *Ds, const double *Lift, const s
 // read the '-' traces (element stride Np, 4 elements x 4 positions per k-block) and the '+' traces (wherever the
 // mesh puts the neighbours).  A short local search over position swaps minimises the wavefronts of those loads,
 // the '+' side counted on a sample of the mesh's own tiles.  pos2slot[j] = slot at B-fragment position j, -1 = pad.
-void arrange_slots(int Np, int Nfn, int NFB, const int32_t *fmask, const std::vector<uint32_t> &lmap, int ntiles_full,
-                   std::vector<int> &pos2slot) {
+void arrange_slots(int Np, int Nfp, int Nfn, int NFB, bool face_blocks, const int32_t *fmask, const std::vector<uint32_t> &lmap,
+                   int ntiles_full, std::vector<int> &pos2slot) {
   const int NPOS = 4 * NFB;
   pos2slot.assign(NPOS, -1);
-  for (int j = 0; j < Nfn; ++j) pos2slot[j] = j;
+  if (face_blocks) {  // Cfg::FACE_BLOCKS: k-block kb < 3 holds slots of face kb only, the rest go to the k-blocks >= 3
+    int spill = 12;
+    for (int f = 0; f < 3; ++f)
+      for (int j = 0; j < Nfp; ++j) pos2slot[j < 4 ? 4 * f + j : spill++] = f * Nfp + j;
+  } else {
+    for (int j = 0; j < Nfn; ++j) pos2slot[j] = j;
+  }
+  auto allowed = [&](int pos) {  // the face-block rule at one position
+    return !face_blocks || pos >= 12 || pos2slot[pos] < 0 || pos2slot[pos] / Nfp == pos / 4;
+  };
   std::vector<int> samples;
   for (int i = 0; i < 32 && ntiles_full > 0; ++i) samples.push_back((int)((long long)i * ntiles_full / 32));
   samples.erase(std::unique(samples.begin(), samples.end()), samples.end());
@@ -816,17 +835,17 @@ void arrange_slots(int Np, int Nfn, int NFB, const int32_t *fmask, const std::ve
   for (int kb = 0; kb < NFB; ++kb) gc[kb] = group_cost(&pos2slot[4 * kb]);
   uint64_t rng = 0x9E3779B97F4A7C15ull;
   auto rnd = [&](int n) { rng = rng * 6364136223846793005ull + 1442695040888963407ull; return (int)((rng >> 33) % (uint64_t)n); };
-  for (int iter = 0; iter < 4000 && NFB > 1; ++iter) {
+  for (int iter = 0; iter < 20000 && NFB > 1; ++iter) {
     const int a = rnd(NPOS), b = rnd(NPOS);
     const int ka = a / 4, kb = b / 4;
-    if (ka == kb || pos2slot[a] == pos2slot[b]) continue;
+    if (pos2slot[a] == pos2slot[b]) continue;
     std::swap(pos2slot[a], pos2slot[b]);
-    bool ok = true;  // every k-block keeps at least one real slot (pads duplicate it)
+    bool ok = allowed(a) && allowed(b);  // and every k-block keeps at least one real slot (pads duplicate it)
     for (int k : {ka, kb}) ok = ok && (pos2slot[4 * k] >= 0 || pos2slot[4 * k + 1] >= 0 || pos2slot[4 * k + 2] >= 0 || pos2slot[4 * k + 3] >= 0);
-    const long long na = ok ? group_cost(&pos2slot[4 * ka]) : 0, nb = ok ? group_cost(&pos2slot[4 * kb]) : 0;
-    if (ok && na + nb <= gc[ka] + gc[kb]) {
+    const long long na = ok ? group_cost(&pos2slot[4 * ka]) : 0, nb = ok ? (ka == kb ? 0 : group_cost(&pos2slot[4 * kb])) : 0;
+    if (ok && na + nb <= gc[ka] + (ka == kb ? 0 : gc[kb])) {
       gc[ka] = na;
-      gc[kb] = nb;
+      if (ka != kb) gc[kb] = nb;
     } else {
       std::swap(pos2slot[a], pos2slot[b]);
     }
@@ -897,7 +916,12 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
   // face-slot arrangement, operator fragments in that arrangement, per-position slot table
   const int NFB = (Nfn + 3) / 4;
   std::vector<int> pos2slot;
-  arrange_slots(Np, Nfn, NFB, fmask, lmap, K / kTile, pos2slot);
+  bool face_blocks = false;
+#define X(np, nfp) \
+  if (Np == np && Nfp == nfp) face_blocks = Cfg<np, nfp>::FACE_BLOCKS;
+  BDG_FUSED_ORDERS(X)
+#undef X
+  arrange_slots(Np, Nfp, Nfn, NFB, face_blocks, fmask, lmap, K / kTile, pos2slot);
   std::vector<double> frag;
 #define X(np, nfp) \
   if (Np == np && Nfp == nfp) build_afrag<np, nfp>(Dr, Ds, Lift, pos2slot, frag);
