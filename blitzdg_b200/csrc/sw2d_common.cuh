@@ -67,6 +67,7 @@ struct bdg_sw2d {
   int32_t *d_perm;      // device element k = caller's element d_perm[k] (sw2d_order.cu); NULL = identity
   uint8_t *d_bctag, *d_facetag;
   double *d_scal;
+  double *d_vfrag;      // operator fragments of the generic DMMA volume kernel (sw2d_volume_dmma.cu), NULL if Np > 64
   void *fused_ops;      // operator fragments of the fused path (device), NULL if unsupported
   int fused_ok;
   double t;             // host mirror of the time (exact for fixed dt)
@@ -111,6 +112,10 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
 cudaError_t launch_fused_stage(bdg_sw2d *s, const double *q_in, double *q_out, double *res, int k0, int k1, double a,
                                double b, int write_rhs, double *rhs_out, int slot);
 void fused_release(bdg_sw2d *s);
+// generic path, second launch on the fp64 tensor pipe (sw2d_volume_dmma.cu)
+cudaError_t volume_dmma_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const double *Lift);
+int volume_dmma_supported(const bdg_sw2d *s);
+cudaError_t launch_volume_dmma(bdg_sw2d *s, double *q, double *res, double *out, int mode, double a, double b);
 // device element order (sw2d_order.cu): perm[new] = old, empty = identity
 #include <vector>
 void build_element_order(const int32_t *vmapP, int Np, int Nfp, int Nf, int K, int n_interior, int tile, std::vector<int32_t> &perm);

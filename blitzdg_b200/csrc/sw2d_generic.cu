@@ -5,6 +5,8 @@
 //
 // Arithmetic follows SURVEY.md Appendix A (reference src/sw2d/main.cpp:279-484,
 // src/sw2d-simple/main.cpp:181-356) node for node; only the sweep structure differs.
+#include <cstdlib>
+
 #include "sw2d_common.cuh"
 
 namespace {
@@ -303,6 +305,8 @@ cudaError_t launch_generic_face(bdg_sw2d *s, const double *q, int k0, int k1, in
 }
 
 cudaError_t launch_generic_volume(bdg_sw2d *s, double *q, double *res, double *out, int mode, double a, double b) {
+  static const bool scalar_only = getenv("BDG_VOLUME_SCALAR") != nullptr;  // study switch: the thread-per-node kernel
+  if (!scalar_only && volume_dmma_supported(s)) return launch_volume_dmma(s, q, res, out, mode, a, b);
   const int Np = s->v.Np, Nfn = s->v.Nfn;
   int EB = 256 / Np;
   if (EB < 1) EB = 1;

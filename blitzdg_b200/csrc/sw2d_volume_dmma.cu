@@ -1,0 +1,299 @@
+// Volume + LIFT + stage-update kernel of the generic path on the fp64 tensor pipe (DMMA), for any element shape
+// and order with Np <= 64: the second launch of a generic stage (after k_face wrote Fscale*dFlux).
+//   reference: volume term src/sw2d/main.cpp:434-442 [sw2d-simple :332-339], surface term :444-458 [:341-355],
+//   sources :460-483, stage update include/LSERK4.hpp:16-27 + src/advec1d/main.cpp:98,101.
+//
+// At N = 8 triangles (Np = 45) or N = 6 quads (Np = 49) the contraction is 52-61 kflop per element and stage against
+// 4.5-7 KB of compulsory traffic: the path is bound by the fp64 pipe, not by HBM, which is the
+// case north_star reserves for tensor cores.  A warp owns 8 elements (the n = 8 columns of mma.m8n8k4.f64); the
+// constant operator A = [-Dr | -Ds | LIFT], padded to 8-row / 4-column blocks, sits in shared memory in A-fragment
+// order (one conflict-free 8-byte load per lane and DMMA); B fragments are built in registers straight from the
+// state (lane = 4*column + t holds node 4*kb + t of its element: every (element, node) flux is evaluated exactly once).
+//   AFFINE (straight-sided triangles): chain-rule factors are element constants and are folded in before the
+//     contraction, RHS_i = A * [rx F_i + ry G_i ; sx F_i + sy G_i ; Fscale dF_i]: 3 accumulator sets.
+//   otherwise (quads, per-node metrics): Dr F, Ds F, Dr G, Ds G and LIFT*flux are accumulated separately, one field
+//     at a time, and combined with the nodal rx, sx, ry, sy in the epilogue (reference operation order).
+// The RHS filter (a15) is not handled here: launch_generic_volume keeps the scalar kernel for it.
+#include <vector>
+
+#include "sw2d_common.cuh"
+
+namespace {
+
+constexpr int kVW = 4;  // warps per CTA
+
+__device__ __forceinline__ void dmma884(double &d0, double &d1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+// 1/x: MUFU seed + two Newton steps (h > 0)
+__device__ __forceinline__ double frcp(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  double e = fma(-x, r, 1.0);
+  r = fma(r, e, r);
+  e = fma(-x, r, 1.0);
+  return fma(r, e, r);
+}
+
+struct VolArgs {
+  const double *Afrag;  // [MB][KB][32]
+  int NPB, NFB, KB;     // k-blocks of Dr (= of Ds), of LIFT, total
+  double *q, *res;
+  const double *sflux;
+  double *out;
+  int mode;             // 0: write RHS to out, 1: LSERK4 stage update
+  double a, b;
+  int ngroups;          // ceil(K / 8)
+};
+
+struct Flux {
+  double hu, hv, F2, G2, G3;
+};
+__device__ __forceinline__ Flux nodal_flux(const Sw2dView &v, const double *q, long long m) {
+  const double h = q[m], hu = q[v.stride + m], hv = q[2 * v.stride + m];
+  const double r = frcp(h), u = hu * r, w = hv * r, gh2 = (0.5 * v.g * h) * h;
+  return Flux{hu, hv, fma(hu, u, gh2), hu * w, fma(hv, w, gh2)};
+}
+
+// RHS_i at node m of the C fragment -> sources (full mode) -> out / stage update.  q is NOT written here when
+// `defer_q` (the non-affine path still needs the old state for the next field).
+__device__ __forceinline__ void finish_node(const Sw2dView &v, const VolArgs &p, long long m, int i, double rhs, double dt, bool defer_q) {
+  if (v.full && i > 0) {  // A11 sources (main.cpp:460-483)
+    const double h = p.q[m], hu = p.q[v.stride + m], hv = p.q[2 * v.stride + m];
+    const double r = frcp(h), u = hu * r, w = hv * r, nu = sqrt(u * u + w * w);
+    if (i == 1) rhs = rhs + v.g * h * v.Hx[m] + (-v.CD * u * nu) + v.fcor * hv;
+    else rhs = rhs + v.g * h * v.Hy[m] + (-v.CD * w * nu) + (-v.fcor * hu);
+  }
+  if (p.mode == 0) {
+    p.out[(long long)i * v.Np * v.K + m] = rhs;
+  } else {
+    double s = dt * rhs;
+    if (p.a != 0.0) s = fma(p.a, p.res[i * v.stride + m], s);
+    p.res[i * v.stride + m] = s;
+    if (!defer_q) p.q[i * v.stride + m] = fma(p.b, s, p.q[i * v.stride + m]);
+  }
+}
+
+template <int MB, bool AFFINE>
+__global__ void __launch_bounds__(kVW * 32, 3) k_volume_dmma(Sw2dView v, VolArgs p) {
+  extern __shared__ __align__(16) double sA[];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int c = lane >> 2, t = lane & 3, gr = lane >> 2;
+  const int Np = v.Np, Nfn = v.Nfn, NPB = p.NPB, NFB = p.NFB, KB = p.KB;
+  const long long nF = (long long)Nfn * v.K;
+  for (int x = threadIdx.x; x < MB * KB * 32; x += blockDim.x) sA[x] = __ldg(p.Afrag + x);
+  __syncthreads();
+  const double dt = p.mode ? v.scal[S_DT] : 0.0;
+  const double *q = p.q;
+
+  for (int g = blockIdx.x * kVW + w; g < p.ngroups; g += gridDim.x * kVW) {
+    const long long kbase = 8LL * g;
+    const long long kB = min(kbase + c, (long long)v.K - 1);  // my B-fragment column's element (ragged end: duplicate)
+    if (AFFINE) {
+      const double rx = v.rx[kB * Np], sx = v.sx[kB * Np], ry = v.ry[kB * Np], sy = v.sy[kB * Np];
+      double acc[3][MB][2];
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int rb = 0; rb < MB; ++rb) acc[i][rb][0] = acc[i][rb][1] = 0.0;
+#pragma unroll 2
+      for (int kb = 0; kb < NPB; ++kb) {
+        const Flux f = nodal_flux(v, q, kB * Np + min(4 * kb + t, Np - 1));  // padding rows of B meet zero columns of A
+        double ba[3], bb[3];
+        ba[0] = fma(rx, f.hu, ry * f.hv); bb[0] = fma(sx, f.hu, sy * f.hv);
+        ba[1] = fma(rx, f.F2, ry * f.G2); bb[1] = fma(sx, f.F2, sy * f.G2);
+        ba[2] = fma(rx, f.G2, ry * f.G3); bb[2] = fma(sx, f.G2, sy * f.G3);
+#pragma unroll
+        for (int rb = 0; rb < MB; ++rb) {
+          const double a1 = sA[(rb * KB + kb) * 32 + lane], a2 = sA[(rb * KB + NPB + kb) * 32 + lane];
+#pragma unroll
+          for (int i = 0; i < 3; ++i) dmma884(acc[i][rb][0], acc[i][rb][1], a1, ba[i]);
+#pragma unroll
+          for (int i = 0; i < 3; ++i) dmma884(acc[i][rb][0], acc[i][rb][1], a2, bb[i]);
+        }
+      }
+      for (int kb = 0; kb < NFB; ++kb) {
+        const long long i0 = kB * Nfn + min(4 * kb + t, Nfn - 1);
+        const double s0 = p.sflux[i0], s1 = p.sflux[nF + i0], s2 = p.sflux[2 * nF + i0];
+#pragma unroll
+        for (int rb = 0; rb < MB; ++rb) {
+          const double a3 = sA[(rb * KB + 2 * NPB + kb) * 32 + lane];
+          dmma884(acc[0][rb][0], acc[0][rb][1], a3, s0);
+          dmma884(acc[1][rb][0], acc[1][rb][1], a3, s1);
+          dmma884(acc[2][rb][0], acc[2][rb][1], a3, s2);
+        }
+      }
+      __syncwarp();  // every lane's state loads of these 8 elements precede the in-place update
+#pragma unroll
+      for (int rb = 0; rb < MB; ++rb) {
+        const int n = 8 * rb + gr;
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+          const long long k = kbase + 2 * t + cc;
+          if (n < Np && k < v.K) {
+            const long long m = k * Np + n;
+            double r0 = acc[0][rb][cc], r1 = acc[1][rb][cc], r2 = acc[2][rb][cc];
+            if (v.full) {  // sources need the old state of all three fields: evaluate before any of them is updated
+              const double h = q[m], hu = q[v.stride + m], hv = q[2 * v.stride + m];
+              const double r = frcp(h), u = hu * r, ww = hv * r, nu = sqrt(u * u + ww * ww);
+              r1 = r1 + v.g * h * v.Hx[m] + (-v.CD * u * nu) + v.fcor * hv;
+              r2 = r2 + v.g * h * v.Hy[m] + (-v.CD * ww * nu) + (-v.fcor * hu);
+            }
+            const double rr[3] = {r0, r1, r2};
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+              if (p.mode == 0) {
+                p.out[(long long)i * Np * v.K + m] = rr[i];
+              } else {
+                double s = dt * rr[i];
+                if (p.a != 0.0) s = fma(p.a, p.res[i * v.stride + m], s);
+                p.res[i * v.stride + m] = s;
+                p.q[i * v.stride + m] = fma(p.b, s, p.q[i * v.stride + m]);
+              }
+            }
+          }
+        }
+      }
+    } else {
+      // per-node metrics: one field at a time; C = {Dr X, Ds X, Dr Y, Ds Y, LIFT s} with X,Y = (F_i, G_i)
+#pragma unroll 1
+      for (int i = 0; i < 3; ++i) {
+        double aRX[MB][2], aSX[MB][2], aRY[MB][2], aSY[MB][2], aL[MB][2];
+#pragma unroll
+        for (int rb = 0; rb < MB; ++rb)
+          aRX[rb][0] = aRX[rb][1] = aSX[rb][0] = aSX[rb][1] = aRY[rb][0] = aRY[rb][1] = aSY[rb][0] = aSY[rb][1] = aL[rb][0] = aL[rb][1] = 0.0;
+#pragma unroll 2
+        for (int kb = 0; kb < NPB; ++kb) {
+          const Flux f = nodal_flux(v, q, kB * Np + min(4 * kb + t, Np - 1));
+          const double X = i == 0 ? f.hu : (i == 1 ? f.F2 : f.G2), Y = i == 0 ? f.hv : (i == 1 ? f.G2 : f.G3);
+#pragma unroll
+          for (int rb = 0; rb < MB; ++rb) {
+            const double a1 = sA[(rb * KB + kb) * 32 + lane], a2 = sA[(rb * KB + NPB + kb) * 32 + lane];
+            dmma884(aRX[rb][0], aRX[rb][1], a1, X);
+            dmma884(aSX[rb][0], aSX[rb][1], a2, X);
+            dmma884(aRY[rb][0], aRY[rb][1], a1, Y);
+            dmma884(aSY[rb][0], aSY[rb][1], a2, Y);
+          }
+        }
+        for (int kb = 0; kb < NFB; ++kb) {
+          const double s = p.sflux[i * nF + kB * Nfn + min(4 * kb + t, Nfn - 1)];
+#pragma unroll
+          for (int rb = 0; rb < MB; ++rb) dmma884(aL[rb][0], aL[rb][1], sA[(rb * KB + 2 * NPB + kb) * 32 + lane], s);
+        }
+#pragma unroll
+        for (int rb = 0; rb < MB; ++rb) {
+          const int n = 8 * rb + gr;
+#pragma unroll
+          for (int cc = 0; cc < 2; ++cc) {
+            const long long k = kbase + 2 * t + cc;
+            if (n < Np && k < v.K) {
+              const long long m = k * Np + n;
+              // A holds -Dr, -Ds: RHS_i = -(rx Dr F + sx Ds F) - (ry Dr G + sy Ds G) + LIFT s   (main.cpp:434-458)
+              double rhs = fma(v.rx[m], aRX[rb][cc], v.sx[m] * aSX[rb][cc]);
+              rhs = rhs + fma(v.ry[m], aRY[rb][cc], v.sy[m] * aSY[rb][cc]);
+              rhs = rhs + aL[rb][cc];
+              finish_node(v, p, m, i, rhs, dt, true);
+            }
+          }
+        }
+      }
+      if (p.mode == 1) {  // all three fields have read the old state: q_i += b * res_i  (advec1d/main.cpp:101)
+        __syncwarp();
+#pragma unroll
+        for (int rb = 0; rb < MB; ++rb) {
+          const int n = 8 * rb + gr;
+#pragma unroll
+          for (int cc = 0; cc < 2; ++cc) {
+            const long long k = kbase + 2 * t + cc;
+            if (n < Np && k < v.K) {
+              const long long m = k * Np + n;
+#pragma unroll
+              for (int i = 0; i < 3; ++i) p.q[i * v.stride + m] = fma(p.b, p.res[i * v.stride + m], p.q[i * v.stride + m]);
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
+template <int MB>
+cudaError_t launch_mb(bdg_sw2d *s, const VolArgs &a, size_t smem) {
+  static int ctas[16][2] = {};
+  static size_t smem_set[16][2] = {};
+  const int dev = s->device & 15, aff = s->is_affine ? 1 : 0;
+  auto kern = aff ? k_volume_dmma<MB, true> : k_volume_dmma<MB, false>;
+  if (smem != smem_set[dev][aff]) {  // one instance serves every order with this row-block count: the operator size varies
+    cudaError_t e;
+    if ((e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas[dev][aff], kern, kVW * 32, smem)) != cudaSuccess) return e;
+    if (ctas[dev][aff] < 1) return cudaErrorLaunchOutOfResources;
+    smem_set[dev][aff] = smem;
+  }
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device);
+  int grid = sms * ctas[dev][aff];
+  const int need = (a.ngroups + kVW - 1) / kVW;
+  if (grid > need) grid = need;
+  kern<<<grid, kVW * 32, smem, s->stream>>>(s->v, a);
+  s->launches++;
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+// Operator fragments of the generic DMMA volume kernel: A = [-Dr | -Ds | LIFT] in m8n8k4 A-fragment order
+// [row block][k block][lane] (row = lane/4, column = lane%4).  Leaves s->d_vfrag NULL when Np > 64.
+cudaError_t volume_dmma_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const double *Lift) {
+  const int Np = s->v.Np, Nfn = s->v.Nfn;
+  s->d_vfrag = nullptr;
+  if (Np > 64) return cudaSuccess;
+  const int MB = (Np + 7) / 8, NPB = (Np + 3) / 4, NFB = (Nfn + 3) / 4, KB = 2 * NPB + NFB;
+  std::vector<double> frag((size_t)MB * KB * 32, 0.0);
+  for (int rb = 0; rb < MB; ++rb)
+    for (int kb = 0; kb < KB; ++kb)
+      for (int lane = 0; lane < 32; ++lane) {
+        const int row = 8 * rb + lane / 4;
+        double val = 0.0;
+        if (row < Np) {
+          if (kb < NPB) {
+            const int j = 4 * kb + lane % 4;
+            if (j < Np) val = -Dr[row * Np + j];
+          } else if (kb < 2 * NPB) {
+            const int j = 4 * (kb - NPB) + lane % 4;
+            if (j < Np) val = -Ds[row * Np + j];
+          } else {
+            const int j = 4 * (kb - 2 * NPB) + lane % 4;
+            if (j < Nfn) val = Lift[row * Nfn + j];
+          }
+        }
+        frag[((size_t)rb * KB + kb) * 32 + lane] = val;
+      }
+  cudaError_t e = cudaMalloc((void **)&s->d_vfrag, sizeof(double) * frag.size());
+  if (e != cudaSuccess) return e;
+  return cudaMemcpy(s->d_vfrag, frag.data(), sizeof(double) * frag.size(), cudaMemcpyHostToDevice);
+}
+
+int volume_dmma_supported(const bdg_sw2d *s) { return s->d_vfrag != nullptr && !s->v.use_filter; }
+
+cudaError_t launch_volume_dmma(bdg_sw2d *s, double *q, double *res, double *out, int mode, double a, double b) {
+  const int Np = s->v.Np, Nfn = s->v.Nfn;
+  VolArgs p;
+  p.Afrag = s->d_vfrag;
+  p.NPB = (Np + 3) / 4; p.NFB = (Nfn + 3) / 4; p.KB = 2 * p.NPB + p.NFB;
+  p.q = q; p.res = res; p.sflux = s->sflux; p.out = out; p.mode = mode; p.a = a; p.b = b;
+  p.ngroups = (s->v.K + 7) / 8;
+  const int MB = (Np + 7) / 8;
+  const size_t smem = sizeof(double) * MB * p.KB * 32;
+  switch (MB) {
+    case 1: return launch_mb<1>(s, p, smem);
+    case 2: return launch_mb<2>(s, p, smem);
+    case 3: return launch_mb<3>(s, p, smem);
+    case 4: return launch_mb<4>(s, p, smem);
+    case 5: return launch_mb<5>(s, p, smem);
+    case 6: return launch_mb<6>(s, p, smem);
+    case 7: return launch_mb<7>(s, p, smem);
+    case 8: return launch_mb<8>(s, p, smem);
+  }
+  return cudaErrorNotSupported;
+}

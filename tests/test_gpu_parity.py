@@ -262,6 +262,9 @@ def test_full_size_properties_1M_triangles():
         Ra = sol.computeRHS()
         sol.set_variant(2)
         Rb = sol.computeRHS()
+        # two summation orders of the same contraction: the gap is the conditioning of the volume term, which
+        # grows like rx ~ 1/h_mesh (cancellation of the constant g h^2/2 part): 5e-13 on a 64x32 grid, 2.5e-12 on
+        # 250x125, 1.2e-11 here (tools/dbg_variants.py)
         for a, b in zip(Ra, Rb):
-            assert relerr(a, b) < 1e-11
+            assert relerr(a, b) < 5e-11
     sol.close()
