@@ -49,10 +49,15 @@ struct VolArgs {
 struct Flux {
   double hu, hv, F2, G2, G3;
 };
-__device__ __forceinline__ Flux nodal_flux(const Sw2dView &v, const double *q, long long m) {
-  const double h = q[m], hu = q[v.stride + m], hv = q[2 * v.stride + m];
-  const double r = frcp(h), u = hu * r, w = hv * r, gh2 = (0.5 * v.g * h) * h;
-  return Flux{hu, hv, fma(hu, u, gh2), hu * w, fma(hv, w, gh2)};
+struct State {
+  double h, hu, hv;
+};
+__device__ __forceinline__ State load_state(const Sw2dView &v, const double *q, long long m) {
+  return State{q[m], q[v.stride + m], q[2 * v.stride + m]};
+}
+__device__ __forceinline__ Flux nodal_flux(const Sw2dView &v, const State &s) {
+  const double r = frcp(s.h), u = s.hu * r, w = s.hv * r, gh2 = (0.5 * v.g * s.h) * s.h;
+  return Flux{s.hu, s.hv, fma(s.hu, u, gh2), s.hu * w, fma(s.hv, w, gh2)};
 }
 
 // RHS_i at node m of the C fragment -> sources (full mode) -> out / stage update.  q is NOT written here when
@@ -96,9 +101,14 @@ __global__ void __launch_bounds__(kVW * 32, 3) k_volume_dmma(Sw2dView v, VolArgs
       for (int i = 0; i < 3; ++i)
 #pragma unroll
         for (int rb = 0; rb < MB; ++rb) acc[i][rb][0] = acc[i][rb][1] = 0.0;
+      // the state loads run two k-blocks ahead of the DMMAs that consume them (a k-block is MB*6 DMMAs ~ 600 cycles)
+      State st0 = load_state(v, q, kB * Np + min(t, Np - 1)), st1 = load_state(v, q, kB * Np + min(4 + t, Np - 1));
 #pragma unroll 2
       for (int kb = 0; kb < NPB; ++kb) {
-        const Flux f = nodal_flux(v, q, kB * Np + min(4 * kb + t, Np - 1));  // padding rows of B meet zero columns of A
+        const State st2 = load_state(v, q, kB * Np + min(4 * (kb + 2) + t, Np - 1));
+        const Flux f = nodal_flux(v, st0);  // padding rows of B meet zero columns of A
+        st0 = st1;
+        st1 = st2;
         double ba[3], bb[3];
         ba[0] = fma(rx, f.hu, ry * f.hv); bb[0] = fma(sx, f.hu, sy * f.hv);
         ba[1] = fma(rx, f.F2, ry * f.G2); bb[1] = fma(sx, f.F2, sy * f.G2);
@@ -112,9 +122,12 @@ __global__ void __launch_bounds__(kVW * 32, 3) k_volume_dmma(Sw2dView v, VolArgs
           for (int i = 0; i < 3; ++i) dmma884(acc[i][rb][0], acc[i][rb][1], a2, bb[i]);
         }
       }
+      long long i0 = kB * Nfn + min(t, Nfn - 1);
+      double n0 = p.sflux[i0], n1 = p.sflux[nF + i0], n2 = p.sflux[2 * nF + i0];
       for (int kb = 0; kb < NFB; ++kb) {
-        const long long i0 = kB * Nfn + min(4 * kb + t, Nfn - 1);
-        const double s0 = p.sflux[i0], s1 = p.sflux[nF + i0], s2 = p.sflux[2 * nF + i0];
+        const double s0 = n0, s1 = n1, s2 = n2;
+        i0 = kB * Nfn + min(4 * (kb + 1) + t, Nfn - 1);
+        n0 = p.sflux[i0]; n1 = p.sflux[nF + i0]; n2 = p.sflux[2 * nF + i0];
 #pragma unroll
         for (int rb = 0; rb < MB; ++rb) {
           const double a3 = sA[(rb * KB + 2 * NPB + kb) * 32 + lane];
@@ -127,28 +140,41 @@ __global__ void __launch_bounds__(kVW * 32, 3) k_volume_dmma(Sw2dView v, VolArgs
 #pragma unroll
       for (int rb = 0; rb < MB; ++rb) {
         const int n = 8 * rb + gr;
+        const bool ok0 = n < Np && kbase + 2 * t < v.K, ok1 = n < Np && kbase + 2 * t + 1 < v.K;
+        const long long m0 = (kbase + 2 * t) * Np + n, m1 = m0 + Np;
+        // all loads of the row block first (the stores below may alias them as far as the compiler knows)
+        double qo[2][3], ro[2][3], hx[2] = {0.0, 0.0}, hy[2] = {0.0, 0.0};
 #pragma unroll
         for (int cc = 0; cc < 2; ++cc) {
-          const long long k = kbase + 2 * t + cc;
-          if (n < Np && k < v.K) {
-            const long long m = k * Np + n;
-            double r0 = acc[0][rb][cc], r1 = acc[1][rb][cc], r2 = acc[2][rb][cc];
-            if (v.full) {  // sources need the old state of all three fields: evaluate before any of them is updated
-              const double h = q[m], hu = q[v.stride + m], hv = q[2 * v.stride + m];
-              const double r = frcp(h), u = hu * r, ww = hv * r, nu = sqrt(u * u + ww * ww);
-              r1 = r1 + v.g * h * v.Hx[m] + (-v.CD * u * nu) + v.fcor * hv;
-              r2 = r2 + v.g * h * v.Hy[m] + (-v.CD * ww * nu) + (-v.fcor * hu);
-            }
-            const double rr[3] = {r0, r1, r2};
+          const bool ok = cc ? ok1 : ok0;
+          const long long m = cc ? m1 : m0;
+#pragma unroll
+          for (int i = 0; i < 3; ++i) {
+            qo[cc][i] = (ok && (p.mode == 1 || v.full)) ? q[i * v.stride + m] : 1.0;
+            ro[cc][i] = (ok && p.mode == 1 && p.a != 0.0) ? p.res[i * v.stride + m] : 0.0;
+          }
+          if (ok && v.full) { hx[cc] = v.Hx[m]; hy[cc] = v.Hy[m]; }
+        }
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+          const bool ok = cc ? ok1 : ok0;
+          const long long m = cc ? m1 : m0;
+          double rr[3] = {acc[0][rb][cc], acc[1][rb][cc], acc[2][rb][cc]};
+          if (v.full) {  // A11 sources (main.cpp:460-483) from the old state
+            const double h = qo[cc][0], hu = qo[cc][1], hv = qo[cc][2];
+            const double r = frcp(h), u = hu * r, ww = hv * r, nu = sqrt(u * u + ww * ww);
+            rr[1] = rr[1] + v.g * h * hx[cc] + (-v.CD * u * nu) + v.fcor * hv;
+            rr[2] = rr[2] + v.g * h * hy[cc] + (-v.CD * ww * nu) + (-v.fcor * hu);
+          }
+          if (ok) {
 #pragma unroll
             for (int i = 0; i < 3; ++i) {
               if (p.mode == 0) {
                 p.out[(long long)i * Np * v.K + m] = rr[i];
               } else {
-                double s = dt * rr[i];
-                if (p.a != 0.0) s = fma(p.a, p.res[i * v.stride + m], s);
-                p.res[i * v.stride + m] = s;
-                p.q[i * v.stride + m] = fma(p.b, s, p.q[i * v.stride + m]);
+                const double sres = fma(p.a, ro[cc][i], dt * rr[i]);
+                p.res[i * v.stride + m] = sres;
+                p.q[i * v.stride + m] = fma(p.b, sres, qo[cc][i]);
               }
             }
           }
@@ -162,9 +188,13 @@ __global__ void __launch_bounds__(kVW * 32, 3) k_volume_dmma(Sw2dView v, VolArgs
 #pragma unroll
         for (int rb = 0; rb < MB; ++rb)
           aRX[rb][0] = aRX[rb][1] = aSX[rb][0] = aSX[rb][1] = aRY[rb][0] = aRY[rb][1] = aSY[rb][0] = aSY[rb][1] = aL[rb][0] = aL[rb][1] = 0.0;
+        State st0 = load_state(v, q, kB * Np + min(t, Np - 1)), st1 = load_state(v, q, kB * Np + min(4 + t, Np - 1));
 #pragma unroll 2
         for (int kb = 0; kb < NPB; ++kb) {
-          const Flux f = nodal_flux(v, q, kB * Np + min(4 * kb + t, Np - 1));
+          const State st2 = load_state(v, q, kB * Np + min(4 * (kb + 2) + t, Np - 1));
+          const Flux f = nodal_flux(v, st0);
+          st0 = st1;
+          st1 = st2;
           const double X = i == 0 ? f.hu : (i == 1 ? f.F2 : f.G2), Y = i == 0 ? f.hv : (i == 1 ? f.G2 : f.G3);
 #pragma unroll
           for (int rb = 0; rb < MB; ++rb) {
