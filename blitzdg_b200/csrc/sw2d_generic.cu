@@ -135,6 +135,58 @@ __global__ void k_face(Sw2dView v, const double *__restrict__ q, double *__restr
   }
 }
 
+// 1/x by MUFU seed + two Newton steps (x = 0 gives NaN like the reference's 0/0)
+__device__ __forceinline__ double frcp(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  double e = fma(-x, r, 1.0);
+  r = fma(r, e, r);
+  e = fma(-x, r, 1.0);
+  return fma(r, e, r);
+}
+
+// A5-A8, one thread per face NODE (coalesced trace-map / geometry reads and sflux writes; every trace is loaded
+// once): wave speeds go through shared memory for the per-face maximum (sw2d-simple main.cpp:305-312).
+// EB elements per CTA, thread = e*Nfn + slot.
+__global__ void k_face_nodes(Sw2dView v, const double *__restrict__ q, double *__restrict__ sflux, int k0, int k1, int slot, int EB) {
+  extern __shared__ double sspd[];
+  const int Nfn = v.Nfn, Nfp = v.Nfp, tid = threadIdx.x;
+  const int e = tid / Nfn, sl = tid - e * Nfn;
+  const long long k = k0 + (long long)blockIdx.x * EB + e;
+  const bool active = e < EB && k < k1;
+  if (blockIdx.x == 0 && tid == 0 && v.lf_global) v.scal[slot ^ 1] = 0.0;  // re-arm the other slot (slots 2,3)
+  const double g = v.g;
+  Trace T;
+  double rM = 0.0, rP = 0.0;
+  if (active) {
+    T = load_trace(v, q, (int)k, sl, v.scal[S_T]);
+    rM = frcp(T.hM);
+    rP = frcp(T.hP);
+    const double uM = T.huM * rM, vM = T.hvM * rM, uP = T.huP * rP, vP = T.hvP * rP;
+    const double sM = sqrt(uM * uM + vM * vM) + sqrt(g * T.hM), sP = sqrt(uP * uP + vP * vP) + sqrt(g * T.hP);
+    sspd[tid] = sM > sP ? sM : sP;
+  }
+  __syncthreads();
+  if (!active) return;
+  double lam;
+  if (v.lf_global) {
+    lam = v.scal[slot];
+  } else {
+    const double *sp = sspd + e * Nfn + (sl / Nfp) * Nfp;
+    lam = sp[0];
+    for (int j = 1; j < Nfp; ++j) lam = sp[j] > lam ? sp[j] : lam;
+  }
+  const long long i = k * Nfn + sl, nF = (long long)Nfn * v.K;
+  const double dh = T.hM - T.hP, dhu = T.huM - T.huP, dhv = T.hvM - T.hvP;
+  const double ghM = (0.5 * g * T.hM) * T.hM, ghP = (0.5 * g * T.hP) * T.hP;
+  const double F2M = (T.huM * T.huM) * rM + ghM, G2M = (T.huM * T.hvM) * rM, G3M = (T.hvM * T.hvM) * rM + ghM;
+  const double F2P = (T.huP * T.huP) * rP + ghP, G2P = (T.huP * T.hvP) * rP, G3P = (T.hvP * T.hvP) * rP + ghP;
+  const double fs = v.Fscale[i];
+  sflux[i] = fs * (0.5 * (dhu * T.nx + dhv * T.ny - lam * dh));
+  sflux[nF + i] = fs * (0.5 * ((F2M - F2P) * T.nx + (G2M - G2P) * T.ny - lam * dhu));
+  sflux[2 * nF + i] = fs * (0.5 * ((G2M - G2P) * T.nx + (G3M - G3P) * T.ny - lam * dhv));
+}
+
 // A9-A13: thread per (element, node); EB elements per CTA
 __global__ void k_volume(Sw2dView v, double *__restrict__ q, double *__restrict__ res, const double *__restrict__ sflux,
                          double *__restrict__ out, int mode, double a, double b, int EB) {
@@ -298,8 +350,15 @@ cudaError_t launch_generic_speed(bdg_sw2d *s, const double *q, int slot) {
 
 cudaError_t launch_generic_face(bdg_sw2d *s, const double *q, int k0, int k1, int slot) {
   if (k1 <= k0) return cudaSuccess;
-  const long long nfaces = (long long)(k1 - k0) * s->v.Nf;
-  k_face<<<(unsigned)((nfaces + 127) / 128), 128, 0, s->stream>>>(s->v, q, s->sflux, k0, k1, slot);
+  static const bool per_face = getenv("BDG_FACE_SCALAR") != nullptr;  // study switch: the thread-per-face kernel
+  if (per_face) {
+    const long long nfaces = (long long)(k1 - k0) * s->v.Nf;
+    k_face<<<(unsigned)((nfaces + 127) / 128), 128, 0, s->stream>>>(s->v, q, s->sflux, k0, k1, slot);
+  } else {
+    const int Nfn = s->v.Nfn;
+    const int EB = Nfn >= 256 ? 1 : 256 / Nfn, threads = (EB * Nfn + 31) / 32 * 32;
+    k_face_nodes<<<(unsigned)((k1 - k0 + EB - 1) / EB), threads, sizeof(double) * threads, s->stream>>>(s->v, q, s->sflux, k0, k1, slot, EB);
+  }
   s->launches++;
   return cudaGetLastError();
 }
