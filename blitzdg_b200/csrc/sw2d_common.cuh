@@ -67,6 +67,8 @@ struct bdg_sw2d {
   int32_t *d_perm;      // device element k = caller's element d_perm[k] (sw2d_order.cu); NULL = identity
   uint8_t *d_bctag, *d_facetag;
   double *d_scal;
+  double *d_Dq;         // quads with a tensor-product basis: 1-D differentiation matrix [quad_n][quad_n], else NULL
+  int quad_n;
   double *d_vfrag;      // operator fragments of the generic DMMA volume kernel (sw2d_volume_dmma.cu), NULL if Np > 64
   void *fused_ops;      // operator fragments of the fused path (device), NULL if unsupported
   int fused_ok;

@@ -14,6 +14,8 @@
 //   otherwise (quads, per-node metrics): Dr F, Ds F, Dr G, Ds G and LIFT*flux are accumulated separately, one field
 //     at a time, and combined with the nodal rx, sx, ry, sy in the epilogue (reference operation order).
 // The RHS filter (a15) is not handled here: launch_generic_volume keeps the scalar kernel for it.
+#include <cmath>
+#include <cstdlib>
 #include <vector>
 
 #include "sw2d_common.cuh"
@@ -44,6 +46,8 @@ struct VolArgs {
   int mode;             // 0: write RHS to out, 1: LSERK4 stage update
   double a, b;
   int ngroups;          // ceil(K / 8)
+  const double *Dq;     // quads with a tensor-product basis: the 1-D differentiation matrix [nq][nq], else NULL
+  int nq;
 };
 
 struct Flux {
@@ -76,6 +80,57 @@ __device__ __forceinline__ void finish_node(const Sw2dView &v, const VolArgs &p,
     if (p.a != 0.0) s = fma(p.a, p.res[i * v.stride + m], s);
     p.res[i * v.stride + m] = s;
     if (!defer_q) p.q[i * v.stride + m] = fma(p.b, s, p.q[i * v.stride + m]);
+  }
+}
+
+// Epilogue in the C-fragment layout (row n = 8*rb + lane/4, columns = elements kbase + 2*(lane%4) + {0,1}):
+// acc = RHS_i without sources -> sources (full mode, A11) -> out (mode 0) / LSERK4 stage update in place (mode 1).
+template <int MB>
+__device__ __forceinline__ void stage_epilogue(const Sw2dView &v, const VolArgs &p, double (&acc)[3][MB][2], long long kbase, int lane, double dt) {
+  const int gr = lane >> 2, t = lane & 3, Np = v.Np;
+  const double *q = p.q;
+#pragma unroll
+  for (int rb = 0; rb < MB; ++rb) {
+    const int n = 8 * rb + gr;
+    const bool ok0 = n < Np && kbase + 2 * t < v.K, ok1 = n < Np && kbase + 2 * t + 1 < v.K;
+    const long long m0 = (kbase + 2 * t) * Np + n, m1 = m0 + Np;
+    // all loads of the row block first (the stores below may alias them as far as the compiler knows)
+    double qo[2][3], ro[2][3], hx[2] = {0.0, 0.0}, hy[2] = {0.0, 0.0};
+#pragma unroll
+    for (int cc = 0; cc < 2; ++cc) {
+      const bool ok = cc ? ok1 : ok0;
+      const long long m = cc ? m1 : m0;
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        qo[cc][i] = (ok && (p.mode == 1 || v.full)) ? q[i * v.stride + m] : 1.0;
+        ro[cc][i] = (ok && p.mode == 1 && p.a != 0.0) ? p.res[i * v.stride + m] : 0.0;
+      }
+      if (ok && v.full) { hx[cc] = v.Hx[m]; hy[cc] = v.Hy[m]; }
+    }
+#pragma unroll
+    for (int cc = 0; cc < 2; ++cc) {
+      const bool ok = cc ? ok1 : ok0;
+      const long long m = cc ? m1 : m0;
+      double rr[3] = {acc[0][rb][cc], acc[1][rb][cc], acc[2][rb][cc]};
+      if (v.full) {  // A11 sources (main.cpp:460-483) from the old state
+        const double h = qo[cc][0], hu = qo[cc][1], hv = qo[cc][2];
+        const double r = frcp(h), u = hu * r, ww = hv * r, nu = sqrt(u * u + ww * ww);
+        rr[1] = rr[1] + v.g * h * hx[cc] + (-v.CD * u * nu) + v.fcor * hv;
+        rr[2] = rr[2] + v.g * h * hy[cc] + (-v.CD * ww * nu) + (-v.fcor * hu);
+      }
+      if (ok) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          if (p.mode == 0) {
+            p.out[(long long)i * Np * v.K + m] = rr[i];
+          } else {
+            const double sres = fma(p.a, ro[cc][i], dt * rr[i]);
+            p.res[i * v.stride + m] = sres;
+            p.q[i * v.stride + m] = fma(p.b, sres, qo[cc][i]);
+          }
+        }
+      }
+    }
   }
 }
 
@@ -137,49 +192,7 @@ __global__ void __launch_bounds__(kVW * 32, 3) k_volume_dmma(Sw2dView v, VolArgs
         }
       }
       __syncwarp();  // every lane's state loads of these 8 elements precede the in-place update
-#pragma unroll
-      for (int rb = 0; rb < MB; ++rb) {
-        const int n = 8 * rb + gr;
-        const bool ok0 = n < Np && kbase + 2 * t < v.K, ok1 = n < Np && kbase + 2 * t + 1 < v.K;
-        const long long m0 = (kbase + 2 * t) * Np + n, m1 = m0 + Np;
-        // all loads of the row block first (the stores below may alias them as far as the compiler knows)
-        double qo[2][3], ro[2][3], hx[2] = {0.0, 0.0}, hy[2] = {0.0, 0.0};
-#pragma unroll
-        for (int cc = 0; cc < 2; ++cc) {
-          const bool ok = cc ? ok1 : ok0;
-          const long long m = cc ? m1 : m0;
-#pragma unroll
-          for (int i = 0; i < 3; ++i) {
-            qo[cc][i] = (ok && (p.mode == 1 || v.full)) ? q[i * v.stride + m] : 1.0;
-            ro[cc][i] = (ok && p.mode == 1 && p.a != 0.0) ? p.res[i * v.stride + m] : 0.0;
-          }
-          if (ok && v.full) { hx[cc] = v.Hx[m]; hy[cc] = v.Hy[m]; }
-        }
-#pragma unroll
-        for (int cc = 0; cc < 2; ++cc) {
-          const bool ok = cc ? ok1 : ok0;
-          const long long m = cc ? m1 : m0;
-          double rr[3] = {acc[0][rb][cc], acc[1][rb][cc], acc[2][rb][cc]};
-          if (v.full) {  // A11 sources (main.cpp:460-483) from the old state
-            const double h = qo[cc][0], hu = qo[cc][1], hv = qo[cc][2];
-            const double r = frcp(h), u = hu * r, ww = hv * r, nu = sqrt(u * u + ww * ww);
-            rr[1] = rr[1] + v.g * h * hx[cc] + (-v.CD * u * nu) + v.fcor * hv;
-            rr[2] = rr[2] + v.g * h * hy[cc] + (-v.CD * ww * nu) + (-v.fcor * hu);
-          }
-          if (ok) {
-#pragma unroll
-            for (int i = 0; i < 3; ++i) {
-              if (p.mode == 0) {
-                p.out[(long long)i * Np * v.K + m] = rr[i];
-              } else {
-                const double sres = fma(p.a, ro[cc][i], dt * rr[i]);
-                p.res[i * v.stride + m] = sres;
-                p.q[i * v.stride + m] = fma(p.b, sres, qo[cc][i]);
-              }
-            }
-          }
-        }
-      }
+      stage_epilogue<MB>(v, p, acc, kbase, lane, dt);
     } else {
       // per-node metrics: one field at a time; C = {Dr X, Ds X, Dr Y, Ds Y, LIFT s} with X,Y = (F_i, G_i)
 #pragma unroll 1
@@ -247,6 +260,111 @@ __global__ void __launch_bounds__(kVW * 32, 3) k_volume_dmma(Sw2dView v, VolArgs
   }
 }
 
+// ---- quads with a tensor-product nodal basis (QuadNodesProvisioner: node = i1*n + i2, Dr = D (x) I, Ds = I (x) D,
+// reference src/QuadNodesProvisioner.cpp:204-260): sum factorisation.  Per element and flux component U (an n x n
+// matrix) Dr U = D U and Ds U = U D^T are two 8x8x8 products instead of two Np x Np ones: 24 DMMAs per element for
+// the volume term instead of ~137.  Both products are laid out so that their C fragments coincide (row i1, columns
+// i2 = 2t, 2t+1 of ONE element): Dr U takes -D as the A operand and U as B, Ds U takes U as A and -D^T as B -- the
+// same register serves both.  The warp stages an element's nodal fluxes in shared memory (every flux evaluated once),
+// combines the four products with the nodal rx, sx, ry, sy, parks the volume RHS of its 8 elements in shared memory
+// and then runs the dense LIFT contraction across the 8 elements (columns = elements) from there.
+template <int MB>
+__global__ void __launch_bounds__(kVW * 32, 3) k_volume_quad_sf(Sw2dView v, VolArgs p) {
+  extern __shared__ __align__(16) double sm[];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int c = lane >> 2, t = lane & 3, gr = lane >> 2;
+  const int Np = v.Np, Nfn = v.Nfn, n = p.nq, NPB = p.NPB, NFB = p.NFB, KB = p.KB;
+  constexpr int VS = MB * 8;  // padded nodes per element in the parked volume RHS
+  const long long nF = (long long)Nfn * v.K;
+  double *sL = sm;                                                      // LIFT fragments [MB][NFB][32]
+  double *sF = sL + MB * NFB * 32 + w * (5 * 64 + 3 * 8 * VS);          // my warp: flux planes hu,hv,F2,G2,G3 [5][8x8]
+  double *sV = sF + 5 * 64;                                             // my warp: volume RHS [3][8 elements][VS]
+  for (int x = threadIdx.x; x < MB * NFB * 32; x += blockDim.x) {
+    const int rb = x / (NFB * 32), r = x - rb * NFB * 32;
+    sL[x] = __ldg(p.Afrag + (rb * KB + 2 * NPB) * 32 + r);
+  }
+  for (int x = lane; x < 3 * 8 * VS; x += 32) sV[x] = 0.0;
+  double aD[2];  // -D as A fragment (row gr, column 4*kb+t) == -D^T as B fragment (k = 4*kb+t, column c = gr)
+#pragma unroll
+  for (int kb = 0; kb < 2; ++kb) aD[kb] = (gr < n && 4 * kb + t < n) ? -__ldg(p.Dq + gr * n + 4 * kb + t) : 0.0;
+  __syncthreads();
+  const double dt = p.mode ? v.scal[S_DT] : 0.0;
+  const double *q = p.q;
+
+  for (int g = blockIdx.x * kVW + w; g < p.ngroups; g += gridDim.x * kVW) {
+    const long long kbase = 8LL * g;
+    for (int j = 0; j < 8; ++j) {
+      const long long e = kbase + j;
+      if (e >= v.K) break;  // warp-uniform (ragged last group: the epilogue guards its stores)
+      // phase A: nodal fluxes of element e into the 8x8 planes (padding = 0)
+#pragma unroll
+      for (int rep = 0; rep < 2; ++rep) {
+        const int idx = lane + 32 * rep, i1 = idx >> 3, i2 = idx & 7;
+        Flux f{0.0, 0.0, 0.0, 0.0, 0.0};
+        if (i1 < n && i2 < n) f = nodal_flux(v, load_state(v, q, e * Np + i1 * n + i2));
+        sF[idx] = f.hu; sF[64 + idx] = f.hv; sF[128 + idx] = f.F2; sF[192 + idx] = f.G2; sF[256 + idx] = f.G3;
+      }
+      // nodal metrics at my two C-fragment nodes (i1 = gr, i2 = 2t + cc)
+      double rxv[2], sxv[2], ryv[2], syv[2];
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        const bool ok = gr < n && 2 * t + cc < n;
+        const long long m = e * Np + (ok ? gr * n + 2 * t + cc : 0);
+        rxv[cc] = v.rx[m]; sxv[cc] = v.sx[m]; ryv[cc] = v.ry[m]; syv[cc] = v.sy[m];
+      }
+      __syncwarp();
+      // phase B: per field the four 8x8x8 products, combined with the metrics (main.cpp:434-442)
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        const double *X = sF + (i == 0 ? 0 : (i == 1 ? 128 : 192)), *Y = sF + (i == 0 ? 64 : (i == 1 ? 192 : 256));
+        double drx[2] = {0.0, 0.0}, dsx[2] = {0.0, 0.0}, dry[2] = {0.0, 0.0}, dsy[2] = {0.0, 0.0};
+#pragma unroll
+        for (int kb = 0; kb < 2; ++kb) {
+          dmma884(drx[0], drx[1], aD[kb], X[(4 * kb + t) * 8 + c]);
+          dmma884(dry[0], dry[1], aD[kb], Y[(4 * kb + t) * 8 + c]);
+          dmma884(dsx[0], dsx[1], X[gr * 8 + 4 * kb + t], aD[kb]);
+          dmma884(dsy[0], dsy[1], Y[gr * 8 + 4 * kb + t], aD[kb]);
+        }
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc)
+          if (gr < n && 2 * t + cc < n) {
+            double r = fma(rxv[cc], drx[cc], sxv[cc] * dsx[cc]);
+            r = r + fma(ryv[cc], dry[cc], syv[cc] * dsy[cc]);
+            sV[(i * 8 + j) * VS + gr * n + 2 * t + cc] = r;
+          }
+      }
+      __syncwarp();  // the planes are rewritten for the next element
+    }
+    // LIFT across the 8 elements (columns = elements), accumulators start from the parked volume RHS
+    double acc[3][MB][2];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int rb = 0; rb < MB; ++rb) {
+        acc[i][rb][0] = sV[(i * 8 + 2 * t) * VS + 8 * rb + gr];
+        acc[i][rb][1] = sV[(i * 8 + 2 * t + 1) * VS + 8 * rb + gr];
+      }
+    const long long kB = min(kbase + c, (long long)v.K - 1);
+    long long i0 = kB * Nfn + min(t, Nfn - 1);
+    double n0 = p.sflux[i0], n1 = p.sflux[nF + i0], n2 = p.sflux[2 * nF + i0];
+    for (int kb = 0; kb < NFB; ++kb) {
+      const double s0 = n0, s1 = n1, s2 = n2;
+      i0 = kB * Nfn + min(4 * (kb + 1) + t, Nfn - 1);
+      n0 = p.sflux[i0]; n1 = p.sflux[nF + i0]; n2 = p.sflux[2 * nF + i0];
+#pragma unroll
+      for (int rb = 0; rb < MB; ++rb) {
+        const double a3 = sL[(rb * NFB + kb) * 32 + lane];
+        dmma884(acc[0][rb][0], acc[0][rb][1], a3, s0);
+        dmma884(acc[1][rb][0], acc[1][rb][1], a3, s1);
+        dmma884(acc[2][rb][0], acc[2][rb][1], a3, s2);
+      }
+    }
+    __syncwarp();
+    stage_epilogue<MB>(v, p, acc, kbase, lane, dt);
+    __syncwarp();
+  }
+}
+
 template <int MB>
 cudaError_t launch_mb(bdg_sw2d *s, const VolArgs &a, size_t smem) {
   static int ctas[16][2] = {};
@@ -266,6 +384,29 @@ cudaError_t launch_mb(bdg_sw2d *s, const VolArgs &a, size_t smem) {
   const int need = (a.ngroups + kVW - 1) / kVW;
   if (grid > need) grid = need;
   kern<<<grid, kVW * 32, smem, s->stream>>>(s->v, a);
+  s->launches++;
+  return cudaGetLastError();
+}
+
+template <int MB>
+cudaError_t launch_quad(bdg_sw2d *s, const VolArgs &a) {
+  static int ctas[16] = {};
+  static size_t smem_set[16] = {};
+  const int dev = s->device & 15;
+  const size_t smem = sizeof(double) * ((size_t)MB * a.NFB * 32 + (size_t)kVW * (5 * 64 + 3 * 8 * MB * 8));
+  if (smem != smem_set[dev]) {
+    cudaError_t e;
+    if ((e = cudaFuncSetAttribute(k_volume_quad_sf<MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas[dev], k_volume_quad_sf<MB>, kVW * 32, smem)) != cudaSuccess) return e;
+    if (ctas[dev] < 1) return cudaErrorLaunchOutOfResources;
+    smem_set[dev] = smem;
+  }
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device);
+  int grid = sms * ctas[dev];
+  const int need = (a.ngroups + kVW - 1) / kVW;
+  if (grid > need) grid = need;
+  k_volume_quad_sf<MB><<<grid, kVW * 32, smem, s->stream>>>(s->v, a);
   s->launches++;
   return cudaGetLastError();
 }
@@ -301,7 +442,34 @@ cudaError_t volume_dmma_prepare(bdg_sw2d *s, const double *Dr, const double *Ds,
       }
   cudaError_t e = cudaMalloc((void **)&s->d_vfrag, sizeof(double) * frag.size());
   if (e != cudaSuccess) return e;
-  return cudaMemcpy(s->d_vfrag, frag.data(), sizeof(double) * frag.size(), cudaMemcpyHostToDevice);
+  if ((e = cudaMemcpy(s->d_vfrag, frag.data(), sizeof(double) * frag.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return e;
+  // quads: is the basis a tensor product with node = i1*n + i2, Dr = D (x) I, Ds = I (x) D ?  (sum-factorised kernel)
+  s->d_Dq = nullptr;
+  s->quad_n = 0;
+  if (s->v.Nf == 4) {
+    int n = 1;
+    while (n * n < Np) ++n;
+    if (n * n == Np && n >= 2 && n <= 8 && s->v.Nfp == n) {
+      std::vector<double> D((size_t)n * n);
+      double scale = 0.0, err = 0.0;
+      for (int a = 0; a < n; ++a)
+        for (int b = 0; b < n; ++b) { D[a * n + b] = Dr[(a * n) * Np + b * n]; scale = fmax(scale, fabs(D[a * n + b])); }
+      for (int i1 = 0; i1 < n; ++i1)
+        for (int i2 = 0; i2 < n; ++i2)
+          for (int j1 = 0; j1 < n; ++j1)
+            for (int j2 = 0; j2 < n; ++j2) {
+              const int r = i1 * n + i2, cidx = j1 * n + j2;
+              err = fmax(err, fabs(Dr[r * Np + cidx] - (i2 == j2 ? D[i1 * n + j1] : 0.0)));
+              err = fmax(err, fabs(Ds[r * Np + cidx] - (i1 == j1 ? D[i2 * n + j2] : 0.0)));
+            }
+      if (err <= 1e-12 * scale) {
+        if ((e = cudaMalloc((void **)&s->d_Dq, sizeof(double) * D.size())) != cudaSuccess) return e;
+        if ((e = cudaMemcpy(s->d_Dq, D.data(), sizeof(double) * D.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return e;
+        s->quad_n = n;
+      }
+    }
+  }
+  return cudaSuccess;
 }
 
 int volume_dmma_supported(const bdg_sw2d *s) { return s->d_vfrag != nullptr && !s->v.use_filter; }
@@ -313,7 +481,19 @@ cudaError_t launch_volume_dmma(bdg_sw2d *s, double *q, double *res, double *out,
   p.NPB = (Np + 3) / 4; p.NFB = (Nfn + 3) / 4; p.KB = 2 * p.NPB + p.NFB;
   p.q = q; p.res = res; p.sflux = s->sflux; p.out = out; p.mode = mode; p.a = a; p.b = b;
   p.ngroups = (s->v.K + 7) / 8;
+  p.Dq = s->d_Dq; p.nq = s->quad_n;
   const int MB = (Np + 7) / 8;
+  static const bool quad_dense = getenv("BDG_QUAD_DENSE") != nullptr;  // study switch: dense Dr/Ds contraction for quads
+  if (s->d_Dq && !quad_dense) {
+    switch (MB) {
+      case 1: return launch_quad<1>(s, p);
+      case 2: return launch_quad<2>(s, p);
+      case 4: return launch_quad<4>(s, p);
+      case 5: return launch_quad<5>(s, p);
+      case 7: return launch_quad<7>(s, p);
+      case 8: return launch_quad<8>(s, p);
+    }
+  }
   const size_t smem = sizeof(double) * MB * p.KB * 32;
   switch (MB) {
     case 1: return launch_mb<1>(s, p, smem);
