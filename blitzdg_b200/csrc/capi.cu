@@ -688,14 +688,7 @@ static int enqueue_stage(bdg_sw2d *s, int write_rhs, double *rhs_out, double a, 
     // previous stage.  Cut elements first, then publish their new traces into the neighbours' next buffer,
     // then the interior elements -- the NVLink transfer hides behind the interior launch.
     double *qo = s->q[s->cur ^ 1];
-    static int prof_on = getenv("BDG_PROF") ? 1 : 0;
-    static cudaEvent_t pev[6];
-    static long pcount = 0;
-    const bool prof = prof_on && (++pcount == 700);
-    if (prof) for (auto &x : pev) cudaEventCreate(&x);
-#define PREC(i) if (prof) cudaEventRecord(pev[i], s->stream)
-    PREC(0);
-    if (s->put_pending) {  // join the previous stage's put before its source buffer can be written again
+    if (s->put_pending) {  // join a put that is still in flight before its source buffer can be written again
       CU(cudaStreamWaitEvent(s->stream, s->ev_recv, 0));
       s->put_pending = 0;
     }
@@ -703,24 +696,29 @@ static int enqueue_stage(bdg_sw2d *s, int write_rhs, double *rhs_out, double a, 
       if ((e = launch_put(s, q, s->cur, ++s->epoch, 0)) != cudaSuccess) return fail(s, BDG_E_CUDA, "put: %s", cudaGetErrorString(e));
       s->ghost_valid = 1;
     }
-    if ((e = launch_wait_epoch(s, s->epoch)) != cudaSuccess) return fail(s, BDG_E_CUDA, "wait: %s", cudaGetErrorString(e));
-    PREC(1);
-    if ((e = launch_fused_stage(s, q, qo, s->res, ksplit, K, a, b, write_rhs, rhs_out, slot)) != cudaSuccess)
-      return fail(s, BDG_E_CUDA, "fused(cut): %s", cudaGetErrorString(e));
-    PREC(2);
-    if (!write_rhs && (e = launch_put(s, qo, s->cur ^ 1, ++s->epoch, 1)) != cudaSuccess)
-      return fail(s, BDG_E_CUDA, "put: %s", cudaGetErrorString(e));
-    PREC(3);
-    if ((e = launch_fused_stage(s, q, qo, s->res, 0, ksplit, a, b, write_rhs, rhs_out, slot)) != cudaSuccess)
-      return fail(s, BDG_E_CUDA, "fused(interior): %s", cudaGetErrorString(e));
-    PREC(4);
-    if (prof) {
-      cudaStreamSynchronize(s->stream);
-      float t[4];
-      for (int i = 0; i < 4; ++i) cudaEventElapsedTime(&t[i], pev[i], pev[i + 1]);
-      fprintf(stderr, "[BDG_PROF rank %d] wait %.1f us, cut %.1f us, put %.1f us, interior %.1f us (launches so far %lld)\n", s->rank,
-              1e3 * t[0], 1e3 * t[1], 1e3 * t[2], 1e3 * t[3], (long long)s->launches);
+    if (write_rhs) {  // bdg_sw2d_rhs: one evaluation, nothing to overlap
+      if ((e = launch_wait_epoch(s, s->epoch)) != cudaSuccess) return fail(s, BDG_E_CUDA, "wait: %s", cudaGetErrorString(e));
+      if ((e = launch_fused_stage(s, q, qo, s->res, 0, K, a, b, write_rhs, rhs_out, slot)) != cudaSuccess)
+        return fail(s, BDG_E_CUDA, "fused(rhs): %s", cudaGetErrorString(e));
+      return BDG_OK;
     }
+    // Fork: the high-priority side stream runs  wait-for-epoch -> cut elements -> put (publishes epoch+1)  while the
+    // main stream runs the interior elements; the two launches touch disjoint elements of q[cur^1] / res and both
+    // only read q[cur].  Join: the main stream waits for the side stream, so everything enqueued after this stage
+    // (the next stage, get_state, the dt reduction ...) sees the complete buffer.
+    cudaStream_t main_stream = s->stream;
+    CU(cudaEventRecord(s->ev_pack, main_stream));
+    CU(cudaStreamWaitEvent(s->comm_stream, s->ev_pack, 0));
+    s->stream = s->comm_stream;
+    e = launch_wait_epoch(s, s->epoch);
+    if (e == cudaSuccess) e = launch_fused_stage(s, q, qo, s->res, ksplit, K, a, b, 0, nullptr, slot);
+    if (e == cudaSuccess) e = launch_put(s, qo, s->cur ^ 1, ++s->epoch, 0);
+    s->stream = main_stream;
+    if (e != cudaSuccess) return fail(s, BDG_E_CUDA, "fused(cut)/put: %s", cudaGetErrorString(e));
+    CU(cudaEventRecord(s->ev_recv, s->comm_stream));
+    if ((e = launch_fused_stage(s, q, qo, s->res, 0, ksplit, a, b, 0, nullptr, slot)) != cudaSuccess)
+      return fail(s, BDG_E_CUDA, "fused(interior): %s", cudaGetErrorString(e));
+    CU(cudaStreamWaitEvent(main_stream, s->ev_recv, 0));
     if (!write_rhs) s->cur ^= 1;
     return BDG_OK;
   }
