@@ -177,7 +177,11 @@ def test_blow_up_guard(coarse_box_mesh):
 
 
 @pytest.mark.parametrize("shape,N,nx,ny,jit", [("tri", 4, 64, 32, 0.0), ("tri", 4, 48, 24, 0.2), ("tri", 8, 24, 12, 0.0),
-                                              ("quad", 6, 32, 16, 0.2)])
+                                              ("quad", 6, 32, 16, 0.2),
+                                              # ragged element counts (K % 8 != 0, K % 32 != 0): DMMA column padding,
+                                              # partial tiles, every row-block count of the generic DMMA kernels
+                                              ("tri", 6, 9, 7, 0.0), ("tri", 3, 11, 5, 0.15), ("tri", 5, 7, 5, 0.1),
+                                              ("quad", 4, 9, 7, 0.2), ("quad", 7, 5, 5, 0.1), ("quad", 2, 7, 3, 0.2)])
 def test_synthetic_mesh_rhs_and_steps(shape, N, nx, ny, jit):
     mesh = structured_mesh(shape, nx, ny, jitter=jit)
     ctx = provision(mesh, N).get_DGContext()
