@@ -185,6 +185,7 @@ struct StageArgs {
   int write_rhs;
   int slot;               // scal slot of the global LF speed
   const int32_t *slotinfo;  // [4*NFB]: face-slot arrangement: local '-' node | face << 16 | slot << 20 per B-fragment position
+  unsigned int *sched;    // persistent kernel: {next list position to claim, CTAs finished} of this stream's launches
   long long *prof;        // BDG_PHASEPROF builds: [kWarps][12] cycle sums
   double a, b;            // LSERK4 stage coefficients
 };
@@ -549,8 +550,12 @@ __global__ void __launch_bounds__(kThreadsWS, BDG_MINBLOCKS) k_fused_persistent(
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
   const bool need_res = p.a != 0.0;
   const long long stride = v.stride;
-  const int nmine = (p.ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // list positions blockIdx.x + i*gridDim.x
-  const int4 *myrec = p.rec + p.list_first + blockIdx.x;
+  // Tiles are claimed dynamically (atomic counter p.sched[0], list positions 0..ntiles-1): a CTA that starts late
+  // -- its SM slot was still held by the cut-element launch of a partitioned run -- or sits on a slower SM simply
+  // claims fewer.  The record of local tile j+3 is claimed and fetched together with tile j; a failed claim leaves an
+  // end marker (x < 0) in the ring instead.
+  const int4 *recs = p.rec + p.list_first;
+  const int4 kEnd = make_int4(-1, 0, 0, 0);
 
   if (tid == 0) {
     mbar_init(&bar[0], 1 + 32);
@@ -560,7 +565,10 @@ __global__ void __launch_bounds__(kThreadsWS, BDG_MINBLOCKS) k_fused_persistent(
     mbar_init(&bar[4], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (tid < 3 && tid < nmine) ring[tid] = __ldg(myrec + (long long)tid * gridDim.x);
+  if (tid == 0) {
+    const unsigned base = atomicAdd(p.sched, 3u);
+    for (unsigned i = 0; i < 3; ++i) ring[i] = base + i < (unsigned)p.ntiles ? __ldg(recs + base + i) : kEnd;
+  }
   __syncthreads();
 
   if (w >= kWarps) {  // ------------------------------------------------------------------ copy warp
@@ -576,16 +584,31 @@ __global__ void __launch_bounds__(kThreadsWS, BDG_MINBLOCKS) k_fused_persistent(
       }
       cp_async_arrive(&bar[b]);
     };
-    // lane 0: bulk loads of list position j into buffer b (rj = its record, rj1 = the next one)
+    bool more = true;  // lane 0: a claim may still succeed
+    auto finish = [&] {  // lane 0, last action of the CTA: the last CTA of the launch re-arms the scheduler
+      __threadfence();
+      if (atomicAdd(p.sched + 1, 1u) == gridDim.x - 1) {
+        p.sched[0] = 0u;
+        p.sched[1] = 0u;
+      }
+    };
+    // lane 0: bulk loads of local tile j into buffer b (rj = its record, rj1 = the next one); claims record j+3
     auto tile_load = [&](int b, int j, const int4 &rj, const int4 &rj1) {
       const long long kt0 = (long long)rj.x * kTile;
-      const bool has_rec = j + 3 < nmine, has_ids = j + 1 < nmine && rj1.y > 0;
+      unsigned pos3 = 0;
+      bool has_rec = false;
+      if (more) {
+        pos3 = atomicAdd(p.sched, 1u);
+        has_rec = more = pos3 < (unsigned)p.ntiles;
+      }
+      if (!has_rec) ring[(j + 3) & 7] = kEnd;  // ordered before the arrive below, which the readers acquire
+      const bool has_ids = rj1.x >= 0 && rj1.y > 0;
       const uint32_t idb = has_ids ? sizeof(int32_t) * rj1.y : 0;
       mbar_expect_tx(&bar[b], 3 * C::txQ + C::txMeta + (has_rec ? 16u : 0u) + idb);
       for (int f = 0; f < 3; ++f) bulk_g2s(S.Q(b) + f * PS, p.q_in + f * stride + kt0 * NP, C::txQ, &bar[b]);
       bulk_g2s(S.Lm(b), p.lmap + kt0 * C::NFN, sizeof(uint32_t) * kTile * C::NFN, &bar[b]);
       bulk_g2s(S.Aff(b), v.aff + kt0 * kAW, sizeof(double) * kTile * kAW, &bar[b]);
-      if (has_rec) bulk_g2s(&ring[(j + 3) & 7], myrec + (long long)(j + 3) * gridDim.x, 16, &bar[b]);
+      if (has_rec) bulk_g2s(&ring[(j + 3) & 7], recs + pos3, 16, &bar[b]);
       if (has_ids) bulk_g2s(S.Ids(b), p.gflat + (((long long)rj1.w << 32) | (unsigned)rj1.z), idb, &bar[b]);
     };
     auto res_ready = [&](int tile) {  // lane 0: R is free; fill it (a != 0) or just say so
@@ -605,42 +628,48 @@ __global__ void __launch_bounds__(kThreadsWS, BDG_MINBLOCKS) k_fused_persistent(
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
     };
     {
-      const int4 r0 = ring[0], r1 = ring[nmine > 1 ? 1 : 0];
+      const int4 r0 = ring[0], r1 = ring[1];
+      if (r0.x < 0) {  // every tile was claimed before this CTA started
+        if (lane == 0) finish();
+        return;
+      }
       if (lane == 0) {
         tile_load(0, 0, r0, r1);
         res_ready(r0.x);
       }
       gather(0, r0.y, p.gflat + (((long long)r0.w << 32) | (unsigned)r0.z));  // first tile: ids straight from global memory
     }
-    int prev_tile = 0;
-    for (int it = 0; it < nmine; ++it) {
+    int prev_tile = 0, it = 0;
+    for (;; ++it) {
       const int b = it & 1, pb = b ^ 1;
+      __syncwarp();
+      const int4 rc = ring[it & 7];  // came with tile it-3 (or from the prologue)
+      if (rc.x < 0) break;
       if (it > 0) {
         mbar_wait(&bar[3 + pb], ((it - 1) >> 1) & 1);
         if (lane == 0) store_tile(pb, prev_tile);
       }
-      int4 rn = make_int4(0, 0, 0, 0), rn2 = rn;
-      if (it + 1 < nmine) {
-        mbar_wait(&bar[b], (it >> 1) & 1);  // tile it has landed: ids of tile it+1, record it+3
-        rn = ring[(it + 1) & 7];
-        rn2 = ring[(it + 2 < nmine ? it + 2 : it + 1) & 7];
+      const int4 rn = ring[(it + 1) & 7];  // came with tile it-2
+      int4 rn2 = kEnd;
+      if (rn.x >= 0) {
+        mbar_wait(&bar[b], (it >> 1) & 1);  // tile it has landed: ids of tile it+1, records up to it+3
+        rn2 = ring[(it + 2) & 7];
         gather(pb, rn.y, S.Ids(b));
       }
-      const int4 rc = ring[it & 7];
       if (lane == 0) {
         if (it > 0) {
           asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
           res_ready(rc.x);
         }
-        if (it + 1 < nmine) tile_load(pb, it + 1, rn, rn2);
+        if (rn.x >= 0) tile_load(pb, it + 1, rn, rn2);
       }
       prev_tile = rc.x;
-      __syncwarp();
     }
-    mbar_wait(&bar[3 + ((nmine - 1) & 1)], ((nmine - 1) >> 1) & 1);
+    mbar_wait(&bar[3 + ((it - 1) & 1)], ((it - 1) >> 1) & 1);  // it = number of tiles this CTA processed (>= 1)
     if (lane == 0) {
-      store_tile((nmine - 1) & 1, prev_tile);
+      store_tile((it - 1) & 1, prev_tile);
       asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      finish();
     }
     return;
   }
@@ -652,12 +681,13 @@ __global__ void __launch_bounds__(kThreadsWS, BDG_MINBLOCKS) k_fused_persistent(
   load_constants<NP, NFP>(p, v, Areg, S.A(), fm, v.scal[S_DT]);
   compute_sync();
   PROF_DECL
-  for (int it = 0; it < nmine; ++it) {
+  for (int it = 0;; ++it) {
     const int b = it & 1;
+    const int4 rc = ring[it & 7];  // came with tile it-3 (or from the prologue); x < 0: no more tiles for this CTA
+    if (rc.x < 0) break;
     PROF_T(0);
     mbar_wait(&bar[b], (it >> 1) & 1);
     PROF_T(1);
-    const int4 rc = ring[it & 7];
     compute_tile<NP, NFP>(v, p, S.Q(b), S.R(), S.Aff(b), S.Lm(b), S.Fl(), S.A(), Areg, fm, PS, TNP + rc.y, (long long)rc.x * kTile, need_res,
                           &bar[2], it & 1 PROF_PASS);
     PROF_T(7);
@@ -675,6 +705,7 @@ __global__ void __launch_bounds__(kThreadsWS, BDG_MINBLOCKS) k_fused_persistent(
 struct FusedOps {
   double *Afrag;
   int32_t *slotinfo;
+  unsigned int *sched;  // [2 streams][2]
   uint32_t *lmap;
   int32_t *gflat;
   long long *goff;
@@ -974,8 +1005,13 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
 
   ops->Np = Np; ops->Nfp = Nfp; ops->Gcap = Gcap; ops->Gmax = Gmax8;
   ops->slotinfo = nullptr;
-  ops->Afrag = nullptr; ops->lmap = nullptr; ops->gflat = nullptr; ops->goff = nullptr; ops->rec = nullptr; ops->biglist = nullptr;
+  ops->sched = nullptr;
   cudaError_t e;
+  if ((e = cudaMalloc((void **)&ops->sched, 4 * sizeof(unsigned int))) != cudaSuccess || (e = cudaMemset(ops->sched, 0, 4 * sizeof(unsigned int))) != cudaSuccess) {
+    delete ops;
+    return e;
+  }
+  ops->Afrag = nullptr; ops->lmap = nullptr; ops->gflat = nullptr; ops->goff = nullptr; ops->rec = nullptr; ops->biglist = nullptr;
   auto up = [&](auto **dst, const auto &vec) -> cudaError_t {
     using T = typename std::remove_reference<decltype(vec[0])>::type;
     cudaError_t r = cudaMalloc((void **)dst, sizeof(T) * vec.size());
@@ -1015,7 +1051,7 @@ void fused_release(bdg_sw2d *s) {
     cudaFree(ops->prof);
   }
 #endif
-  cudaFree(ops->slotinfo); cudaFree(ops->Afrag); cudaFree(ops->lmap); cudaFree(ops->gflat); cudaFree(ops->goff); cudaFree(ops->rec); cudaFree(ops->biglist);
+  cudaFree(ops->sched); cudaFree(ops->slotinfo); cudaFree(ops->Afrag); cudaFree(ops->lmap); cudaFree(ops->gflat); cudaFree(ops->goff); cudaFree(ops->rec); cudaFree(ops->biglist);
   delete ops;
   s->fused_ops = nullptr;
 }
@@ -1031,6 +1067,7 @@ cudaError_t launch_fused_stage(bdg_sw2d *s, const double *q_in, double *q_out, d
   args.G = ops->Gmax; args.list_first = 0; args.use_list = 0;
   args.k0 = k0; args.k1 = k1; args.tile0 = 0; args.ntiles = 0;
   args.write_rhs = write_rhs; args.slot = slot; args.a = a; args.b = b; args.prof = ops->prof; args.slotinfo = ops->slotinfo;
+  args.sched = ops->sched + (s->stream == s->comm_stream ? 2 : 0);  // launches on the two streams may overlap
 #define X(np, nfp) \
   if (ops->Np == np && ops->Nfp == nfp) return launch_t<np, nfp>(s, args, ops);
   BDG_FUSED_ORDERS(X)
