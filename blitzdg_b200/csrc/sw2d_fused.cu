@@ -237,8 +237,8 @@ __device__ __forceinline__ void phase1_nodes(const double *__restrict__ sQ, doub
 // ghost nodes, sR: [3][TNP].  On return the tile's q and res planes hold the updated values (stage mode) -- or,
 // in write_rhs mode, rhs_out has been written and the tile is untouched.  Contains two compute_sync() and an
 // optional wait on the res barrier before phase 3; the caller makes the tile visible first.
-// The operator fragments (Areg / sA) arrive pre-multiplied by dt (by 1 in write_rhs mode), so the accumulators,
-// started from a*res, end as the new res.  All three phases are branch-free on their hot path: padding slots are
+// The operator fragments (Areg / sA) arrive pre-multiplied by dt (by 1 in write_rhs mode), so the accumulators
+// hold dt*RHS and the new res is a*res + acc.  All three phases are branch-free on their hot path: padding slots are
 // clamped to a valid neighbour (their operator columns are zero), the wall reflection is a rare warp-level
 // fix-up pass, and every thread keeps several independent dependency chains in flight.
 template <int NP, int NFP>
@@ -357,22 +357,15 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   PROF_T(5);
   // ---- phase 3: B fragments -> DMMA (six independent accumulator chains: 3 fields x MB row blocks) -> stage update
   const double rx = af[0], sx = af[1], ry = af[2], sy = af[3];
-  if (bar_res) mbar_wait(bar_res, res_parity);
-  PROF_T(6);
   const int gr = lane >> 2;  // C fragment row within a row block
   const int c0 = 2 * t, c1 = 2 * t + 1;
   const int e0 = w + 4 * (c0 < 4 ? c0 : (c0 ^ 1));  // C fragment column 2t   -> element E(2t)
   const int e1 = w + 4 * (c1 < 4 ? c1 : (c1 ^ 1));  // C fragment column 2t+1 -> element E(2t+1)
   double acc[3][MB][2];
 #pragma unroll
-  for (int rb = 0; rb < MB; ++rb) {
-    const int n = min(8 * rb + gr, NP - 1);
+  for (int rb = 0; rb < MB; ++rb)
 #pragma unroll
-    for (int i = 0; i < 3; ++i) {
-      acc[i][rb][0] = need_res ? p.a * sR[i * TNP + e0 * NP + n] : 0.0;
-      acc[i][rb][1] = need_res ? p.a * sR[i * TNP + e1 * NP + n] : 0.0;
-    }
-  }
+    for (int i = 0; i < 3; ++i) acc[i][rb][0] = acc[i][rb][1] = 0.0;
 #pragma unroll
   for (int kb = 0; kb < NPB; ++kb) {
     const int n = eo + min(4 * kb + t, NP - 1);  // padding rows of B meet zero columns of A
@@ -400,6 +393,10 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
       for (int i = 0; i < 3; ++i) dmma884(acc[i][rb][0], acc[i][rb][1], a3, sfl[kb][i]);
     }
   }
+  // res is first needed here, a whole DMMA chain after the tile's other inputs: its load (which has to wait for the
+  // previous tile's store to drain from the same buffer) hides behind the contraction
+  if (bar_res) mbar_wait(bar_res, res_parity);
+  PROF_T(6);
   __syncwarp();  // every lane's B-fragment reads of this warp's elements precede the in-place update below
   // epilogue: rows n = 8*rb + gr of elements e0, e1; acc = a*res + dt*rhs (stage mode) or rhs (write_rhs mode)
   if (p.write_rhs) {
@@ -425,7 +422,7 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
 #pragma unroll
           for (int cc = 0; cc < 2; ++cc) {
             const int o = (cc ? e1 : e0) * NP + n;
-            const double rs = acc[i][rb][cc];
+            const double rs = need_res ? fma(p.a, sR[i * TNP + o], acc[i][rb][cc]) : acc[i][rb][cc];
             sR[i * TNP + o] = rs;
             sQ[i * PS + o] = fma(p.b, rs, sQ[i * PS + o]);
           }
