@@ -99,7 +99,9 @@ __device__ __forceinline__ void dmma884(double &d0, double &d1, double a, double
 // barrier of the kThreads compute threads (the persistent kernel has a fifth, copy-only warp that never joins it)
 __device__ __forceinline__ void compute_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kThreads) : "memory"); }
 
-__device__ __forceinline__ double dmax(double a, double b) { return a > b ? a : b; }
+// max of two NON-NEGATIVE doubles (wave speeds) through their bit patterns: integer compares instead of DSETP keep
+// the shared fp64 pipe for the arithmetic; a NaN compares largest and so reaches the blow-up guard
+__device__ __forceinline__ double dmax(double a, double b) { return __double_as_longlong(a) > __double_as_longlong(b) ? a : b; }
 
 // 1/x: MUFU seed (20+ bits) + two Newton steps; no denormal / inf handling (h > 0 here)
 __device__ __forceinline__ double frcp(double x) {
