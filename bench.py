@@ -40,6 +40,9 @@ def parse():
     ap.add_argument("--ny", type=int, default=500, help="cells in y PER GPU")
     ap.add_argument("--variant", type=int, default=0, help="0 auto, 1 generic, 2 fused")
     ap.add_argument("--mode", default="simple", choices=["simple", "full"])
+    ap.add_argument("--stepper", default="lserk4", choices=["lserk4", "ssprk2"],
+                    help="ssprk2 = the src/sw2d driver loop (SURVEY.md 8f rank 1): with --mode full the top edge becomes an open "
+                         "boundary with tide, sloping 150-200 m bathymetry and a sponge behind the open boundary")
     ap.add_argument("--block", default="", help="element order: '' = cell-major, 'BXxBY' = blocks of BX x BY cells (locality study)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -122,7 +125,20 @@ def build_problem(args, rank, world):
         epart = strip_partition(cy, world)
         ctx, halo, _ = build_local(mesh, epart, rank, args.order)
     H, h, hu, hv = gaussian_hump(ctx.x, ctx.y)
+    if args.stepper == "ssprk2" and args.mode == "full":
+        H, h = coastal_setup(ctx, h - H)
     return ctx, halo, (H, h, hu, hv), mesh.get_NumElements()
+
+
+def coastal_setup(ctx, eta):
+    """The coastal workload of --stepper ssprk2 --mode full: boundary faces on the top edge (y = max) become Out faces
+    (tidal forcing, reference src/sw2d/main.cpp:348-353), depth 150-200 m sloping in x.  Returns H, h."""
+    wall = np.asarray(ctx.BCmap[3]).reshape(-1, ctx.Nfp)
+    yv = ctx.y.T.reshape(-1)[np.asarray(ctx.vmapM)[wall]]
+    top = (yv > ctx.y.max() - 1e-9).all(axis=1)
+    ctx.BCmap = {3: wall[~top].reshape(-1), 2: wall[top].reshape(-1)}
+    H = 175.0 + 25.0 * ctx.x
+    return H, H + eta
 
 
 def cpu_oracle_rate(args, threads, target_seconds=12.0):
@@ -138,21 +154,36 @@ def cpu_oracle_rate(args, threads, target_seconds=12.0):
     ctx = provision(mesh, args.order).get_DGContext()
     H, h, hu, hv = gaussian_hump(ctx.x, ctx.y)
     full = args.mode == "full"
+    rk2 = args.stepper == "ssprk2"
+    Hx = Hy = np.zeros_like(H)
+    sponge = None
+    if rk2 and full:
+        from blitzdg_b200.sw2d import bedSlopes, buildSpongeCoeff
+
+        H, h = coastal_setup(ctx, h - H)
+        Hx, Hy = bedSlopes(ctx, H)
+        sponge = buildSpongeCoeff(ctx, 10000.0, 0.1)
     orcs = []
     for _ in range(threads):
         o = Oracle(ctx, CFL=0.65, lf_mode=1 if full else 0, sources=1 if full else 0)
         if full:
-            o.set_bathymetry(H, np.zeros_like(H), np.zeros_like(H))
+            o.set_bathymetry(H, Hx, Hy)
         orcs.append((o, h.copy(), hu.copy(), hv.copy(), [np.zeros_like(h) for _ in range(3)]))
     dt = 0.5 * orcs[0][0].timestep(h, hu, hv, use_abs=True)[0]
     t0 = time.perf_counter()
-    orcs[0][0].step(orcs[0][1], orcs[0][2], orcs[0][3], orcs[0][4], 1, dt)  # calibrate (also warm-up)
+    def advance(i, n):
+        o, a, b, c, r = orcs[i]
+        if rk2:
+            o.step_ssprk2(a, b, c, n, dt, sponge=sponge)
+        else:
+            o.step(a, b, c, r, n, dt)
+
+    advance(0, 1)  # calibrate (also warm-up)
     one = time.perf_counter() - t0
     nsteps = max(1, int(target_seconds / max(one, 1e-3)))
 
     def work(i):
-        o, a, b, c, r = orcs[i]
-        o.step(a, b, c, r, nsteps, dt)
+        advance(i, nsteps)
 
     ths = [threading.Thread(target=work, args=(i,)) for i in range(threads)]
     t0 = time.perf_counter()
@@ -161,9 +192,9 @@ def cpu_oracle_rate(args, threads, target_seconds=12.0):
     for t in ths:
         t.join()
     el = time.perf_counter() - t0
-    dsu = 3.0 * ctx.Np * ctx.K * 5 * nsteps * threads
-    sample = "%d thread(s) x %d LSERK4 steps on a %dx%d %s slab (%d elements, N=%d), %.1f s" % (
-        threads, nsteps, nxs, nys, args.shape, ctx.K, args.order, el)
+    dsu = 3.0 * ctx.Np * ctx.K * (2 if rk2 else 5) * nsteps * threads
+    sample = "%d thread(s) x %d " % (threads, nsteps) + ("SSP-RK2" if rk2 else "LSERK4") + " steps on a %dx%d %s slab (%d elements, N=%d), %.1f s" % (
+        nxs, nys, args.shape, ctx.K, args.order, el)
     return dsu / el, sample, el / nsteps
 
 
@@ -198,6 +229,17 @@ def run_reference(args):
 def workload_config(args, world, variant):
     fam = "triangles" if args.shape == "tri" else "quads"
     Kper = args.nx * args.ny * (2 if args.shape == "tri" else 1)
+    rk2 = args.stepper == "ssprk2"
+    if rk2:
+        return {
+            "workload": "sw2d driver loop (SSP-RK2 + sponge relaxation, reference src/sw2d/main.cpp:192-244) on synthetic structured %s mesh, "
+                        "%d elements per GPU, N=%d, %s" % (fam, Kper, args.order,
+                        "full physics: global LF, star states, sources, open top edge with tide, 150-200 m bathymetry, sponge" if args.mode == "full"
+                        else "sw2d-simple physics, all-wall BC, no sponge"),
+            "elements_per_gpu": Kper, "order": args.order, "ssprk2_steps_per_step": OUTPUT_INTERVAL, "stages_per_step": 2 * OUTPUT_INTERVAL,
+            "partition": "single GPU" if world == 1 else "%d horizontal strips, NCCL send/recv halo" % world,
+            "l2": "working set (>=1 GB of state per GPU) exceeds the 126 MB L2; no explicit flush", "kernel_variant": variant,
+        }
     return {
         "workload": "sw2d on synthetic structured %s mesh, %d elements per GPU (%dx%d cells), N=%d, LSERK4, per-face LF, all-wall BC"
                     % (fam, Kper, args.nx, args.ny, args.order) if args.mode == "simple" else
@@ -230,7 +272,18 @@ def run_b200(args):
     sol = SW2dSolver(ctx, mode=args.mode, halo=halo, device=local)
     if args.variant:
         sol.set_variant(args.variant)
-    sol.set_bathymetry(H, np.zeros_like(H), np.zeros_like(H))  # flat bottom; also feeds eta = h - H of the blow-up guard
+    rk2 = args.stepper == "ssprk2"
+    nst = 2 if rk2 else 5  # RHS evaluations per time step
+    has_sponge = False
+    if rk2 and args.mode == "full":
+        from blitzdg_b200.sw2d import bedSlopes, buildSpongeCoeff
+
+        Hx, Hy = bedSlopes(ctx, H)
+        sol.set_bathymetry(H, Hx, Hy)
+        sol.set_sponge(buildSpongeCoeff(ctx, 10000.0, 0.1))
+        has_sponge = True
+    else:
+        sol.set_bathymetry(H, np.zeros_like(H), np.zeros_like(H))  # flat bottom; also feeds eta = h - H of the blow-up guard
     if world > 1:
         idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:
@@ -239,6 +292,8 @@ def run_b200(args):
         sol.comm_init(bytes(idt.cpu().numpy().tobytes()))
     sol.set_state(h, hu, hv)
     dt = 0.5 * sol.computeTimeStep() * (0.65 / sol.num.CFL)  # reference formula (sw2d-simple CFL 0.65), halved for LSERK4 margin
+    if rk2:
+        dt = sol.computeTimeStep()  # the src/sw2d driver's own CFL 0.25 (main.cpp:56)
     stream = torch.cuda.ExternalStream(sol.stream, device=torch.device("cuda", local))
 
     def barrier():
@@ -263,7 +318,8 @@ def run_b200(args):
         return float(ms.item())
 
     # ---- device-resident throughput ------------------------------------------------------------
-    kstep = lambda: sol.step(OUTPUT_INTERVAL, dt, sync=False)
+    advance = sol.step_ssprk2 if rk2 else sol.step
+    kstep = lambda: advance(OUTPUT_INTERVAL, dt, sync=False)
     for _ in range(max(3, args.warmup)):
         kstep()
     sampler = ClockSampler(local)
@@ -274,7 +330,7 @@ def run_b200(args):
     launches = sol.launch_count - l0
     clocks = sampler.stop() if rank == 0 else None
     eta_max = sol.check()
-    stages = 5 * OUTPUT_INTERVAL * args.steps
+    stages = nst * OUTPUT_INTERVAL * args.steps
     dsu_total = 3.0 * ctx.Np * K_global * stages
     value = dsu_total / (ms * 1e-3)
     lt = torch.tensor([launches], device="cuda", dtype=torch.float64)
@@ -282,6 +338,8 @@ def run_b200(args):
         dist.all_reduce(lt)
     peak, peak_src = peaks()
     alg_bytes = sol.algorithmic_bytes_per_stage  # this rank, one stage == one launch of the dominant kernel
+    if rk2:  # no residual planes: stage 1 reads q, writes q1 (48 B/node), stage 2 reads q1 and q, writes q (72 B/node); sponge 8 B/node
+        alg_bytes += (60.0 - 96.0 + (8.0 if has_sponge else 0.0)) * ctx.Np * ctx.K
     stage_ms = ms / stages
     achieved = alg_bytes / (stage_ms * 1e-3) / 1e9
     traffic = None
@@ -303,16 +361,16 @@ def run_b200(args):
 
         def e2e_step():
             sol.set_state(src[0], src[1], src[2])
-            sol.step(OUTPUT_INTERVAL, dt, sync=False)
+            advance(OUTPUT_INTERVAL, dt, sync=False)
             sol.get_state(out=dst)
 
         e2e_step()
         n_e2e = max(1, min(args.steps, 5))
         ms2 = timed(e2e_step, n_e2e)
         bytes_dir = 3 * ctx.Np * ctx.K * 8
-        e2e = {"value": 3.0 * ctx.Np * K_global * 5 * OUTPUT_INTERVAL * n_e2e / (ms2 * 1e-3), "unit": UNIT,
+        e2e = {"value": 3.0 * ctx.Np * K_global * nst * OUTPUT_INTERVAL * n_e2e / (ms2 * 1e-3), "unit": UNIT,
                "h2d_bytes_per_step": bytes_dir, "d2h_bytes_per_step": bytes_dir, "steps": n_e2e,
-               "api": "bdg_sw2d_set_state (pinned host) -> bdg_sw2d_step -> bdg_sw2d_get_state"}
+               "api": "bdg_sw2d_set_state (pinned host) -> %s -> bdg_sw2d_get_state" % ("bdg_sw2d_step_ssprk2" if rk2 else "bdg_sw2d_step")}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -326,7 +384,8 @@ def run_b200(args):
             "data": "synthetic", "config": workload_config(args, world, sol.variant),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
-                         "launch_ms": stage_ms, "per": "rank 0, one fused RHS+stage launch"},
+                         "launch_ms": stage_ms,
+                         "per": "rank 0, one RHS+stage: " + ("one fused launch" if sol.variant == 2 and not rk2 else "the launches of the two-kernel path (face, volume)")},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(lt.item()), "clocks": clocks,
             "eta_max_after": eta_max, "dt": dt,
         }

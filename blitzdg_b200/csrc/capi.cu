@@ -166,7 +166,7 @@ extern "C" void bdg_sw2d_destroy(bdg_sw2d *s) {
   fused_release(s);
   void *ptrs[] = {s->q[0], s->q[1], s->res, s->rhs, s->sflux, s->d_Dr, s->d_Ds, s->d_Lift, s->d_Filt, s->d_rx, s->d_sx,
                   s->d_ry, s->d_sy, s->d_nx, s->d_ny, s->d_Fscale, s->d_aff, s->d_H, s->d_Hx, s->d_Hy, s->d_vmapP,
-                  s->d_fmask, s->d_bctag, s->d_facetag, s->d_scal, s->d_send_nodes, s->d_sendbuf, s->d_perm, s->d_vfrag, s->d_Dq};
+                  s->d_fmask, s->d_bctag, s->d_facetag, s->d_scal, s->d_send_nodes, s->d_sendbuf, s->d_perm, s->d_vfrag, s->d_Dq, s->d_sponge};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   free(s->h_nbr); free(s->h_send_off); free(s->h_recv_off);
@@ -446,6 +446,22 @@ extern "C" int bdg_sw2d_set_bathymetry(bdg_sw2d *s, const double *H, const doubl
   return BDG_OK;
 }
 
+// spongeCoeff of the src/sw2d driver (main.cpp:184-186, built by buildSpongeCoeff :517-553); used by bdg_sw2d_step_ssprk2
+extern "C" int bdg_sw2d_set_sponge(bdg_sw2d *s, const double *sigma) {
+  if (!s) return BDG_E_INVALID;
+  CU(cudaSetDevice(s->device));
+  if (!sigma) {
+    s->v.sponge = nullptr;
+    return BDG_OK;
+  }
+  int rc;
+  if (!s->d_sponge && (rc = dev_alloc(s, &s->d_sponge, s->nT))) return rc;
+  if ((rc = upload_transposed(s, sigma, s->d_sponge, s->v.Np, s->v.K))) return rc;
+  s->v.sponge = s->d_sponge;
+  CU(cudaStreamSynchronize(s->stream));
+  return BDG_OK;
+}
+
 extern "C" int bdg_sw2d_set_state(bdg_sw2d *s, const double *h, const double *hu, const double *hv, double t) {
   if (!s || !h || !hu || !hv) return BDG_E_INVALID;
   CU(cudaSetDevice(s->device));
@@ -673,17 +689,20 @@ static int use_fused(const bdg_sw2d *s) {
 
 // One RHS evaluation of the live state.  write_rhs: store RHS planes into rhs_out (bdg_sw2d_rhs);
 // otherwise apply LSERK4 stage (a,b).  slot alternates the global-LF scalar between S_GMAX0/1.
-static int enqueue_stage(bdg_sw2d *s, int write_rhs, double *rhs_out, double a, double b, int slot) {
+// rk2 = 2, 3: first / second SSP-RK2 stage of the src/sw2d driver instead (generic path; the state is read from
+// q[cur], the result goes to q[cur^1], which in the second stage still holds q^n, and the buffers swap).
+static int enqueue_stage(bdg_sw2d *s, int write_rhs, double *rhs_out, double a, double b, int slot, int rk2 = 0) {
   if (s->v.full && !s->v.H) return fail(s, BDG_E_INVALID, "sources=1 needs bdg_sw2d_set_bathymetry first");
   double *q = s->q[s->cur];
   const int K = s->v.K;
   const bool halo = s->comm && s->n_nbr > 0;
   // interior/cut split rounded down to a whole 32-element tile of the fused kernel: computing a few interior
   // elements with the cut launch is harmless and keeps both launches free of partially active tiles
-  const int ksplit = halo ? (use_fused(s) ? s->n_interior / 32 * 32 : s->n_interior) : K;
+  const bool fused = use_fused(s) && !rk2;
+  const int ksplit = halo ? (fused ? s->n_interior / 32 * 32 : s->n_interior) : K;
   int rc;
   cudaError_t e;
-  if (halo && s->peer_ok && use_fused(s)) {
+  if (halo && s->peer_ok && fused) {
     // Peer-memory halo (sw2d_halo.cu): ghosts of the live buffer were stored by the neighbours during the
     // previous stage.  Cut elements first, then publish their new traces into the neighbours' next buffer,
     // then the interior elements -- the NVLink transfer hides behind the interior launch.
@@ -733,7 +752,7 @@ static int enqueue_stage(bdg_sw2d *s, int write_rhs, double *rhs_out, double a, 
     if ((e = launch_generic_speed(s, q, slot)) != cudaSuccess) return fail(s, BDG_E_CUDA, "speed: %s", cudaGetErrorString(e));
     if ((rc = allreduce_max(s, s->d_scal + slot))) return rc;
   }
-  if (use_fused(s)) {
+  if (fused) {
     double *qo = s->q[s->cur ^ 1];
     if ((e = launch_fused_stage(s, q, qo, s->res, 0, ksplit, a, b, write_rhs, rhs_out, slot)) != cudaSuccess)
       return fail(s, BDG_E_CUDA, "fused(interior): %s", cudaGetErrorString(e));
@@ -749,8 +768,9 @@ static int enqueue_stage(bdg_sw2d *s, int write_rhs, double *rhs_out, double a, 
     if ((e = launch_generic_face(s, q, 0, ksplit, slot)) != cudaSuccess) return fail(s, BDG_E_CUDA, "face: %s", cudaGetErrorString(e));
     if (halo && !s->v.lf_global && (rc = halo_wait(s))) return rc;
     if ((e = launch_generic_face(s, q, ksplit, K, slot)) != cudaSuccess) return fail(s, BDG_E_CUDA, "face: %s", cudaGetErrorString(e));
-    if ((e = launch_generic_volume(s, q, s->res, rhs_out, write_rhs ? 0 : 1, a, b)) != cudaSuccess)
+    if ((e = launch_generic_volume(s, q, s->res, rhs_out, write_rhs ? 0 : (rk2 ? rk2 : 1), a, b, s->q[s->cur ^ 1])) != cudaSuccess)
       return fail(s, BDG_E_CUDA, "volume: %s", cudaGetErrorString(e));
+    if (rk2 && !write_rhs) s->cur ^= 1;
   }
   return BDG_OK;
 }
@@ -810,6 +830,39 @@ extern "C" int bdg_sw2d_step(bdg_sw2d *s, int32_t nsteps, double dt) {
     if (adaptive && (rc = enqueue_dt(s))) return rc;
     for (int stage = 0; stage < 5; ++stage) {  // reference src/advec1d/main.cpp:92-102
       if ((rc = enqueue_stage(s, 0, nullptr, rk4a[stage], rk4b[stage], slot))) return rc;
+      slot ^= 1;
+    }
+    if (device_time) {
+      if ((e = launch_advance_time(s)) != cudaSuccess) return fail(s, BDG_E_CUDA, "advance: %s", cudaGetErrorString(e));
+    } else {
+      s->t += dt;
+    }
+  }
+  if (!device_time && nsteps > 0) CU(cudaMemcpyAsync(s->d_scal + S_T, &s->t, sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  return BDG_OK;
+}
+
+// The time loop of the src/sw2d driver (reference src/sw2d/main.cpp:192-244): per step dt = computeTimeStep (dt <= 0)
+// or the caller's, two RHS evaluations at the same time t in Heun's SSP-RK2 form, the sponge relaxation of hu, hv
+// after each of them, t += dt.  Four launches per step (face + volume per stage), nothing leaves the device.
+extern "C" int bdg_sw2d_step_ssprk2(bdg_sw2d *s, int32_t nsteps, double dt) {
+  if (!s || nsteps < 0) return BDG_E_INVALID;
+  CU(cudaSetDevice(s->device));
+  const bool adaptive = !(dt > 0.0);
+  const bool device_time = adaptive || (s->v.full && s->prm.tide_amp != 0.0);
+  int rc;
+  cudaError_t e;
+  if (!adaptive) CU(cudaMemcpyAsync(s->d_scal + S_DT, &dt, sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  if (s->v.lf_global) CU(cudaMemsetAsync(s->d_scal + S_GMAX0, 0, 2 * sizeof(double), s->stream));
+  if (adaptive) {
+    CU(cudaMemsetAsync(s->d_scal + S_DTMAX, 0, sizeof(double), s->stream));
+    s->adaptive_used = 1;
+  }
+  int slot = S_GMAX0;
+  for (int st = 0; st < nsteps; ++st) {
+    if (adaptive && (rc = enqueue_dt(s))) return rc;
+    for (int stage = 0; stage < 2; ++stage) {
+      if ((rc = enqueue_stage(s, 0, nullptr, 0.0, 1.0, slot, 2 + stage))) return rc;
       slot ^= 1;
     }
     if (device_time) {

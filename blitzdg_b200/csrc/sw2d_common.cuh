@@ -33,8 +33,24 @@ struct Sw2dView {
   const uint8_t *bctag;                  // [K][Nfn] BCTag per face node (0 interior)
   const uint8_t *facetag;                // [K][Nf]  BCTag per face (fused path), 255 = mixed
   const double *H, *Hx, *Hy;             // H: [Np*K + n_ghost]; Hx,Hy: [Np*K]; NULL when unset
+  const double *sponge;                  // [Np*K] sponge coefficient (src/sw2d/main.cpp:184-186); NULL = none
   double *scal;                          // S_COUNT device scalars
 };
+
+// Time-stepper forms of the volume kernels' epilogue; st = dt*RHS_i (modes 2, 3) or a*res_i + dt*RHS_i (mode 1),
+// qin = the state the RHS was evaluated on, qold = the previous content of the destination buffer:
+//   mode 1  LSERK4 stage            q  = qin + b*st                  (src/advec1d/main.cpp:98-101)
+//   mode 2  SSP-RK2 first stage     q1 = qin + st                    (src/sw2d/main.cpp:217-219)
+//   mode 3  SSP-RK2 second stage    q  = 0.5*(qold + qin + st)       (src/sw2d/main.cpp:230-232; qin = q1, qold = q^n)
+// followed in modes 2, 3 by the sponge relaxation of the momenta, hu /= 1 + sigma*hu*hu (main.cpp:222-224,235-236).
+#ifdef __CUDACC__
+__device__ __forceinline__ double stepper_value(int mode, double b, double st, double qin, double qold, int field, double sigma) {
+  if (mode == 1) return fma(b, st, qin);
+  double val = mode == 2 ? qin + st : 0.5 * ((qold + qin) + st);
+  if (field > 0 && sigma != 0.0) val = val / (1.0 + sigma * val * val);
+  return val;
+}
+#endif
 
 // peer-memory halo (sw2d_halo.cu): per neighbour i, the peer's two state buffers, plane stride, flag words
 constexpr int kMaxNbr = 8;
@@ -62,7 +78,7 @@ struct bdg_sw2d {
   double *rhs;          // [3][nT] scratch (bdg_sw2d_rhs) -- allocated on demand
   double *sflux;        // [3][nF] generic path: Fscale*dFlux
   double *d_Dr, *d_Ds, *d_Lift, *d_Filt, *d_rx, *d_sx, *d_ry, *d_sy, *d_nx, *d_ny, *d_Fscale, *d_aff;
-  double *d_H, *d_Hx, *d_Hy;
+  double *d_H, *d_Hx, *d_Hy, *d_sponge;
   int32_t *d_vmapP, *d_fmask;
   int32_t *d_perm;      // device element k = caller's element d_perm[k] (sw2d_order.cu); NULL = identity
   uint8_t *d_bctag, *d_facetag;
@@ -98,8 +114,9 @@ struct bdg_sw2d {
 // generic two-kernel path over elements [k0,k1): face fluxes into sflux, then volume+lift+update
 cudaError_t launch_generic_speed(bdg_sw2d *s, const double *q, int slot);
 cudaError_t launch_generic_face(bdg_sw2d *s, const double *q, int k0, int k1, int slot);
-// mode 0: write RHS to out (3 planes of nT); mode 1: LSERK4 stage update of q/res in place
-cudaError_t launch_generic_volume(bdg_sw2d *s, double *q, double *res, double *out, int mode, double a, double b);
+// mode 0: write RHS to out (3 planes of nT); mode 1: LSERK4 stage update of q/res in place; modes 2, 3: the two
+// SSP-RK2 stages of the src/sw2d driver, state read from q, result stored to qdst (see stepper_value)
+cudaError_t launch_generic_volume(bdg_sw2d *s, double *q, double *res, double *out, int mode, double a, double b, double *qdst);
 cudaError_t launch_dt_reduce(bdg_sw2d *s, const double *q);
 cudaError_t launch_dt_finalize(bdg_sw2d *s);
 cudaError_t launch_advance_time(bdg_sw2d *s);
@@ -117,7 +134,7 @@ void fused_release(bdg_sw2d *s);
 // generic path, second launch on the fp64 tensor pipe (sw2d_volume_dmma.cu)
 cudaError_t volume_dmma_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const double *Lift);
 int volume_dmma_supported(const bdg_sw2d *s);
-cudaError_t launch_volume_dmma(bdg_sw2d *s, double *q, double *res, double *out, int mode, double a, double b);
+cudaError_t launch_volume_dmma(bdg_sw2d *s, double *q, double *res, double *out, int mode, double a, double b, double *qdst);
 // device element order (sw2d_order.cu): perm[new] = old, empty = identity
 #include <vector>
 void build_element_order(const int32_t *vmapP, int Np, int Nfp, int Nf, int K, int n_interior, int tile, std::vector<int32_t> &perm);

@@ -189,7 +189,7 @@ __global__ void k_face_nodes(Sw2dView v, const double *__restrict__ q, double *_
 
 // A9-A13: thread per (element, node); EB elements per CTA
 __global__ void k_volume(Sw2dView v, double *__restrict__ q, double *__restrict__ res, const double *__restrict__ sflux,
-                         double *__restrict__ out, int mode, double a, double b, int EB) {
+                         double *__restrict__ out, int mode, double a, double b, int EB, double *__restrict__ qdst) {
   extern __shared__ double sm[];
   const int Np = v.Np, Nfn = v.Nfn;
   const int tid = threadIdx.x, e = tid / Np, n = tid - e * Np;
@@ -274,9 +274,18 @@ __global__ void k_volume(Sw2dView v, double *__restrict__ q, double *__restrict_
   } else {  // A13 (src/advec1d/main.cpp:98,101)
     const double dt = v.scal[S_DT];
     double s1 = dt * r1, s2 = dt * r2, s3 = dt * r3;
-    if (a != 0.0) { s1 = a * res[m] + s1; s2 = a * res[v.stride + m] + s2; s3 = a * res[2 * v.stride + m] + s3; }
-    res[m] = s1; res[v.stride + m] = s2; res[2 * v.stride + m] = s3;
-    q[m] = h + b * s1; q[v.stride + m] = hu + b * s2; q[2 * v.stride + m] = hv + b * s3;
+    if (mode == 1 && a != 0.0) { s1 = a * res[m] + s1; s2 = a * res[v.stride + m] + s2; s3 = a * res[2 * v.stride + m] + s3; }
+    if (mode == 1) {
+      res[m] = s1; res[v.stride + m] = s2; res[2 * v.stride + m] = s3;
+      q[m] = h + b * s1; q[v.stride + m] = hu + b * s2; q[2 * v.stride + m] = hv + b * s3;
+    } else {  // SSP-RK2 stages + sponge of the src/sw2d driver (stepper_value, sw2d_common.cuh); qdst != q
+      const double sg = v.sponge ? v.sponge[m] : 0.0;
+      double o1 = 0, o2 = 0, o3 = 0;
+      if (mode == 3) { o1 = qdst[m]; o2 = qdst[v.stride + m]; o3 = qdst[2 * v.stride + m]; }
+      qdst[m] = stepper_value(mode, b, s1, h, o1, 0, sg);
+      qdst[v.stride + m] = stepper_value(mode, b, s2, hu, o2, 1, sg);
+      qdst[2 * v.stride + m] = stepper_value(mode, b, s3, hv, o3, 2, sg);
+    }
   }
 }
 
@@ -363,16 +372,16 @@ cudaError_t launch_generic_face(bdg_sw2d *s, const double *q, int k0, int k1, in
   return cudaGetLastError();
 }
 
-cudaError_t launch_generic_volume(bdg_sw2d *s, double *q, double *res, double *out, int mode, double a, double b) {
+cudaError_t launch_generic_volume(bdg_sw2d *s, double *q, double *res, double *out, int mode, double a, double b, double *qdst) {
   static const bool scalar_only = getenv("BDG_VOLUME_SCALAR") != nullptr;  // study switch: the thread-per-node kernel
-  if (!scalar_only && volume_dmma_supported(s)) return launch_volume_dmma(s, q, res, out, mode, a, b);
+  if (!scalar_only && volume_dmma_supported(s)) return launch_volume_dmma(s, q, res, out, mode, a, b, qdst);
   const int Np = s->v.Np, Nfn = s->v.Nfn;
   int EB = 256 / Np;
   if (EB < 1) EB = 1;
   const int threads = ((EB * Np + 31) / 32) * 32;
   const size_t smem = sizeof(double) * ((size_t)5 * EB * Np + (size_t)3 * EB * Nfn);
   const unsigned grid = (unsigned)((s->v.K + EB - 1) / EB);
-  k_volume<<<grid, threads, smem, s->stream>>>(s->v, q, res, s->sflux, out, mode, a, b, EB);
+  k_volume<<<grid, threads, smem, s->stream>>>(s->v, q, res, s->sflux, out, mode, a, b, EB, mode >= 2 ? qdst : nullptr);
   s->launches++;
   return cudaGetLastError();
 }

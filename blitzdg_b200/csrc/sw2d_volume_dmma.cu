@@ -43,8 +43,9 @@ struct VolArgs {
   double *q, *res;
   const double *sflux;
   double *out;
-  int mode;             // 0: write RHS to out, 1: LSERK4 stage update
+  int mode;             // 0: write RHS to out, 1: LSERK4 stage update, 2/3: SSP-RK2 stages (stepper_value, sw2d_common.cuh)
   double a, b;
+  double *qdst;         // where the new state goes: q itself in mode 1, the other state buffer in modes 2, 3
   int ngroups;          // ceil(K / 8)
   const double *Dq;     // quads with a tensor-product basis: the 1-D differentiation matrix [nq][nq], else NULL
   int nq;
@@ -95,17 +96,19 @@ __device__ __forceinline__ void stage_epilogue(const Sw2dView &v, const VolArgs 
     const bool ok0 = n < Np && kbase + 2 * t < v.K, ok1 = n < Np && kbase + 2 * t + 1 < v.K;
     const long long m0 = (kbase + 2 * t) * Np + n, m1 = m0 + Np;
     // all loads of the row block first (the stores below may alias them as far as the compiler knows)
-    double qo[2][3], ro[2][3], hx[2] = {0.0, 0.0}, hy[2] = {0.0, 0.0};
+    double qo[2][3], ro[2][3], qd[2][3], hx[2] = {0.0, 0.0}, hy[2] = {0.0, 0.0}, sg[2] = {0.0, 0.0};
 #pragma unroll
     for (int cc = 0; cc < 2; ++cc) {
       const bool ok = cc ? ok1 : ok0;
       const long long m = cc ? m1 : m0;
 #pragma unroll
       for (int i = 0; i < 3; ++i) {
-        qo[cc][i] = (ok && (p.mode == 1 || v.full)) ? q[i * v.stride + m] : 1.0;
+        qo[cc][i] = (ok && (p.mode >= 1 || v.full)) ? q[i * v.stride + m] : 1.0;
         ro[cc][i] = (ok && p.mode == 1 && p.a != 0.0) ? p.res[i * v.stride + m] : 0.0;
+        qd[cc][i] = (ok && p.mode == 3) ? p.qdst[i * v.stride + m] : 0.0;
       }
       if (ok && v.full) { hx[cc] = v.Hx[m]; hy[cc] = v.Hy[m]; }
+      if (ok && p.mode >= 2 && v.sponge) sg[cc] = v.sponge[m];
     }
 #pragma unroll
     for (int cc = 0; cc < 2; ++cc) {
@@ -124,9 +127,9 @@ __device__ __forceinline__ void stage_epilogue(const Sw2dView &v, const VolArgs 
           if (p.mode == 0) {
             p.out[(long long)i * Np * v.K + m] = rr[i];
           } else {
-            const double sres = fma(p.a, ro[cc][i], dt * rr[i]);
-            p.res[i * v.stride + m] = sres;
-            p.q[i * v.stride + m] = fma(p.b, sres, qo[cc][i]);
+            const double sres = fma(p.a, ro[cc][i], dt * rr[i]);  // a = 0 in modes 2, 3
+            if (p.mode == 1) p.res[i * v.stride + m] = sres;
+            p.qdst[i * v.stride + m] = stepper_value(p.mode, p.b, sres, qo[cc][i], qd[cc][i], i, sg[cc]);
           }
         }
       }
@@ -240,7 +243,7 @@ __global__ void __launch_bounds__(kVW * 32, 3) k_volume_dmma(Sw2dView v, VolArgs
           }
         }
       }
-      if (p.mode == 1) {  // all three fields have read the old state: q_i += b * res_i  (advec1d/main.cpp:101)
+      if (p.mode >= 1) {  // all three fields have read the old state: q_i += b * res_i  (advec1d/main.cpp:101), or the SSP-RK2 forms
         __syncwarp();
 #pragma unroll
         for (int rb = 0; rb < MB; ++rb) {
@@ -251,7 +254,11 @@ __global__ void __launch_bounds__(kVW * 32, 3) k_volume_dmma(Sw2dView v, VolArgs
             if (n < Np && k < v.K) {
               const long long m = k * Np + n;
 #pragma unroll
-              for (int i = 0; i < 3; ++i) p.q[i * v.stride + m] = fma(p.b, p.res[i * v.stride + m], p.q[i * v.stride + m]);
+              for (int i = 0; i < 3; ++i) {
+                const double qold = p.mode == 3 ? p.qdst[i * v.stride + m] : 0.0;
+                const double sig = (p.mode >= 2 && v.sponge) ? v.sponge[m] : 0.0;
+                p.qdst[i * v.stride + m] = stepper_value(p.mode, p.b, p.res[i * v.stride + m], p.q[i * v.stride + m], qold, i, sig);
+              }
             }
           }
         }
@@ -474,12 +481,12 @@ cudaError_t volume_dmma_prepare(bdg_sw2d *s, const double *Dr, const double *Ds,
 
 int volume_dmma_supported(const bdg_sw2d *s) { return s->d_vfrag != nullptr && !s->v.use_filter; }
 
-cudaError_t launch_volume_dmma(bdg_sw2d *s, double *q, double *res, double *out, int mode, double a, double b) {
+cudaError_t launch_volume_dmma(bdg_sw2d *s, double *q, double *res, double *out, int mode, double a, double b, double *qdst) {
   const int Np = s->v.Np, Nfn = s->v.Nfn;
   VolArgs p;
   p.Afrag = s->d_vfrag;
   p.NPB = (Np + 3) / 4; p.NFB = (Nfn + 3) / 4; p.KB = 2 * p.NPB + p.NFB;
-  p.q = q; p.res = res; p.sflux = s->sflux; p.out = out; p.mode = mode; p.a = a; p.b = b;
+  p.q = q; p.res = res; p.sflux = s->sflux; p.out = out; p.mode = mode; p.a = mode >= 2 ? 0.0 : a; p.b = b; p.qdst = mode >= 2 ? qdst : q;
   p.ngroups = (s->v.K + 7) / 8;
   p.Dq = s->d_Dq; p.nq = s->quad_n;
   const int MB = (Np + 7) / 8;

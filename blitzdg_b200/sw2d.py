@@ -122,6 +122,17 @@ class SW2dSolver:
         if sync:
             self.sync()
 
+    def set_sponge(self, spongeCoeff):
+        """spongeCoeff [Np][K] of the src/sw2d driver (main.cpp:184-186); None removes it."""
+        a = self._in(spongeCoeff) if spongeCoeff is not None else None
+        self._ck(self.lib.bdg_sw2d_set_sponge(self.h, _dp(a)))
+
+    def step_ssprk2(self, nsteps, dt=0.0, sync=True):
+        """The src/sw2d driver's own loop body (main.cpp:192-244): SSP-RK2 + sponge relaxation, dt <= 0: adaptive."""
+        self._ck(self.lib.bdg_sw2d_step_ssprk2(self.h, int(nsteps), float(dt)))
+        if sync:
+            self.sync()
+
     def sync(self):
         self._ck(self.lib.bdg_sw2d_sync(self.h))
 
@@ -173,3 +184,56 @@ def nccl_unique_id():
     if rc != capi.BDG_OK:
         raise RuntimeError("ncclGetUniqueId failed")
     return buf.raw
+
+
+# ---- setup steps of the src/sw2d driver around the solver (host side, run once) ------------------------------
+def readDepthData(depthFile, Np, K):
+    """sw2d::readDepthData (src/sw2d/main.cpp:486-515): one depth per row, element-major (k outer, n inner),
+    floored at 150 m; rows missing at the end count as 0 (-> 150).  Returns H [Np][K]."""
+    vals = []
+    with open(depthFile) as fh:
+        for lineno, line in enumerate(fh, 1):
+            tok = line.strip().rstrip(",")
+            if not tok:
+                continue
+            try:
+                vals.append(float(tok))
+            except ValueError:
+                raise RuntimeError("readDepthData: %s:%d: not a number: %r" % (depthFile, lineno, tok))
+    if len(vals) > Np * K:
+        raise RuntimeError("readDepthData: %s holds %d values, the mesh has %d nodes" % (depthFile, len(vals), Np * K))
+    d = np.zeros(Np * K)
+    d[:len(vals)] = vals
+    return np.ascontiguousarray(np.maximum(d, 150.0).reshape(K, Np).T)
+
+
+def bedSlopes(ctx, H):
+    """Hx, Hy of the driver (src/sw2d/main.cpp:129-133): filtered nodal gradient of H."""
+    dr, ds = ctx.Dr @ H, ctx.Ds @ H
+    Hx, Hy = ctx.rx * dr + ctx.sx * ds, ctx.ry * dr + ctx.sy * ds
+    if getattr(ctx, "Filt", None) is not None:
+        Hx, Hy = ctx.Filt @ Hx, ctx.Filt @ Hy
+    return np.ascontiguousarray(Hx), np.ascontiguousarray(Hy)
+
+
+def buildSpongeCoeff(ctx, spongeStrength, radInfl, x=None, y=None):
+    """sw2d::buildSpongeCoeff (src/sw2d/main.cpp:517-553): strength*(1 - d/radInfl) where d < radInfl is the distance
+    from a volume node to the closest node of an Out face.  The reference scans every (node, Out node) pair; here a
+    k-d tree answers the same nearest-neighbour query, so meshes of 10^6 elements are provisioned in seconds."""
+    from scipy.spatial import cKDTree
+
+    from .bctypes import BCTag
+
+    x = ctx.x if x is None else x
+    y = ctx.y if y is None else y
+    Np, K = x.shape
+    out = np.asarray(ctx.BCmap.get(int(BCTag.Out), ()), dtype=np.int64)
+    coeff = np.zeros((Np, K))
+    if out.size == 0:
+        return coeff  # the reference throws out_of_range here (bcHash.at, SURVEY.md F3); an empty sponge is the useful answer
+    xv, yv = x.T.reshape(-1), y.T.reshape(-1)  # element-major vectors, the index space of vmapM
+    o = np.asarray(ctx.vmapM)[out]
+    tree = cKDTree(np.column_stack([xv[o], yv[o]]))
+    d, _ = tree.query(np.column_stack([xv, yv]))
+    c = np.where(d < radInfl, spongeStrength * (1.0 - d / radInfl), 0.0)
+    return np.ascontiguousarray(c.reshape(K, Np).T)

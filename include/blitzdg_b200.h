@@ -109,6 +109,14 @@ int bdg_sw2d_timestep(bdg_sw2d *s, double *dt_out);
  * device each step.  Asynchronous: returns after enqueueing; bdg_sw2d_sync waits. */
 int bdg_sw2d_step(bdg_sw2d *s, int32_t nsteps, double dt);
 int bdg_sw2d_sync(bdg_sw2d *s);
+/* The rest of the src/sw2d driver's time loop.
+ * set_sponge: spongeCoeff [Np][K] (reference src/sw2d/main.cpp:184-186, sw2d::buildSpongeCoeff :517-553); NULL = none.
+ * step_ssprk2: nsteps steps of the loop at reference src/sw2d/main.cpp:192-244 -- dt = computeTimeStep (dt <= 0) or
+ * the caller's, Heun's SSP-RK2 with both RHS evaluations at the step-start time (:213-232), the relaxation
+ * hu /= 1 + sponge*hu*hu, hv likewise, after each stage (:222-224, :235-236), t += dt.  Runs on the two-launch
+ * path (any element shape, any BC mix), all on device, asynchronous like bdg_sw2d_step. */
+int bdg_sw2d_set_sponge(bdg_sw2d *s, const double *sponge);
+int bdg_sw2d_step_ssprk2(bdg_sw2d *s, int32_t nsteps, double dt);
 /* blow-up guard of the drivers (reference src/sw2d/main.cpp:238-240): max|h-H| > 1e8 or NaN
  * => BDG_E_UNSTABLE.  eta_max may be NULL. */
 int bdg_sw2d_check(bdg_sw2d *s, double *eta_max);

@@ -33,6 +33,14 @@ def lib():
         L.oracle_sw2d_timestep.restype = C.c_double
         L.oracle_sw2d_step.argtypes = [C.POINTER(bdg_dgcontext2d), C.POINTER(bdg_sw2d_params), _dp, _dp, _dp, _dp, _dp, _dp,
                                        _dp, _dp, _dp, C.c_int, C.c_double, _dp]
+        L.oracle_sw2d_step_ssprk2.argtypes = [C.POINTER(bdg_dgcontext2d), C.POINTER(bdg_sw2d_params), _dp, _dp, _dp, _dp, _dp, _dp,
+                                              _dp, C.c_int, C.c_double, _dp]
+        L.oracle_build_sponge.argtypes = [C.POINTER(bdg_dgcontext2d), _dp, _dp, _ip, C.c_int, C.c_double, C.c_double, _dp]
+        L.oracle_build_sponge.restype = None
+        L.oracle_depth_to_H.argtypes = [_dp, C.c_size_t, C.c_int, C.c_int, _dp]
+        L.oracle_depth_to_H.restype = None
+        L.oracle_bed_slopes.argtypes = [C.POINTER(bdg_dgcontext2d), _dp, _dp, _dp]
+        L.oracle_bed_slopes.restype = None
         L.oracle_lserk4_stage.argtypes = [C.c_int, C.c_double, C.c_size_t, _dp, _dp, _dp]
         L.oracle_lserk4_stage.restype = None
         L.oracle_lserk4_coeffs.argtypes = [_dp, _dp]
@@ -90,3 +98,32 @@ class Oracle:
     @staticmethod
     def stage(stage, dt, rhs, res, q):
         lib().oracle_lserk4_stage(stage, dt, rhs.size, _d(rhs), _d(res), _d(q))
+
+    # ---- the rest of the src/sw2d driver ----
+    def step_ssprk2(self, h, hu, hv, nsteps, dt, t=0.0, sponge=None):
+        """In-place nsteps steps of the driver's SSP-RK2 + sponge loop; returns the new time."""
+        tt = C.c_double(t)
+        sponge = _c(sponge)
+        lib().oracle_sw2d_step_ssprk2(C.byref(self.cctx), C.byref(self.prm), _d(self.H), _d(self.Hx), _d(self.Hy), _d(sponge),
+                                      _d(h), _d(hu), _d(hv), nsteps, dt, C.byref(tt))
+        return tt.value
+
+    def build_sponge(self, x, y, out_nodes, strength, radInfl):
+        x, y = _c(x), _c(y)
+        out_nodes = np.ascontiguousarray(out_nodes, dtype=np.int32)
+        sp = np.zeros_like(x)
+        lib().oracle_build_sponge(C.byref(self.cctx), _d(x), _d(y), out_nodes.ctypes.data_as(_ip), out_nodes.size, strength, radInfl, _d(sp))
+        return sp
+
+    def bed_slopes(self, H):
+        H = _c(H)
+        Hx, Hy = np.empty_like(H), np.empty_like(H)
+        lib().oracle_bed_slopes(C.byref(self.cctx), _d(H), _d(Hx), _d(Hy))
+        return Hx, Hy
+
+    @staticmethod
+    def depth_to_H(values, Np, K):
+        values = np.ascontiguousarray(values, dtype=np.float64)
+        H = np.empty((Np, K))
+        lib().oracle_depth_to_H(_d(values), values.size, Np, K, _d(H))
+        return H

@@ -364,3 +364,101 @@ int oracle_sw2d_step(const bdg_dgcontext2d *dg, const bdg_sw2d_params *prm, cons
   free(R1); free(R2); free(R3);
   return 0;
 }
+
+/* ---- the rest of the src/sw2d driver around computeRHS ---------------------------- */
+
+/* sw2d::buildSpongeCoeff (src/sw2d/main.cpp:517-553): for every volume node the distance to the closest node of
+ * an Out face (x,y of the '-' side through vmapM); inside radInfl the coefficient falls linearly from
+ * spongeStrength at the boundary to 0.  x, y, sponge are [Np][K] row-major; out_nodes = BCmap[Out] (face-node ids).
+ * Nodes out of reach are left untouched (the driver zero-fills before the call, :185). */
+void oracle_build_sponge(const bdg_dgcontext2d *dg, const double *x, const double *y, const int32_t *out_nodes,
+                         int n_out, double strength, double radInfl, double *sponge) {
+  const int Np = dg->Np, K = dg->K;
+  const size_t nT = (size_t)Np * K;
+  double *xV = dalloc(nT), *yV = dalloc(nT);
+  oracle_full_to_vector(x, xV, Np, K);
+  oracle_full_to_vector(y, yV, Np, K);
+  for (int k = 0; k < K; ++k)
+    for (int n = 0; n < Np; ++n) {
+      const double x0 = x[(size_t)n * K + k], y0 = y[(size_t)n * K + k];
+      double closest = 1.0e12;
+      for (int i = 0; i < n_out; ++i) {
+        const int32_t o = dg->vmapM[out_nodes[i]];
+        const double dist = hypot(x0 - xV[o], y0 - yV[o]);
+        if (dist < radInfl && dist < closest) closest = dist;
+      }
+      if (closest < 1.0e12) sponge[(size_t)n * K + k] = strength * (1.0 - (closest / radInfl));
+    }
+  free(xV); free(yV);
+}
+
+/* sw2d::readDepthData (src/sw2d/main.cpp:486-515) after the file has been parsed: values arrive element-major
+ * (count runs over k then n), are floored at 150 and stored to H(n,k); missing values are 0 -> 150. */
+void oracle_depth_to_H(const double *values, size_t nvalues, int Np, int K, double *H) {
+  size_t count = 0;
+  for (int k = 0; k < K; ++k)
+    for (int n = 0; n < Np; ++n) {
+      double val = count < nvalues ? values[count] : 0.0;
+      if (val < 150.0) val = 150.0;
+      H[(size_t)n * K + k] = val;
+      ++count;
+    }
+}
+
+/* bed slopes (src/sw2d/main.cpp:129-133): Hx = rx*(Dr H) + sx*(Ds H), Hy likewise, then both filtered. */
+void oracle_bed_slopes(const bdg_dgcontext2d *dg, const double *H, double *Hx, double *Hy) {
+  const int Np = dg->Np, K = dg->K;
+  const size_t nT = (size_t)Np * K;
+  double *dr = dalloc(nT), *ds = dalloc(nT), *tx = dalloc(nT), *ty = dalloc(nT);
+  contract(dg->Dr, Np, Np, H, K, dr);
+  contract(dg->Ds, Np, Np, H, K, ds);
+  for (size_t m = 0; m < nT; ++m) {
+    tx[m] = dg->rx[m] * dr[m] + dg->sx[m] * ds[m];
+    ty[m] = dg->ry[m] * dr[m] + dg->sy[m] * ds[m];
+  }
+  if (dg->Filt) {
+    contract(dg->Filt, Np, Np, tx, K, Hx);
+    contract(dg->Filt, Np, Np, ty, K, Hy);
+  } else {
+    memcpy(Hx, tx, sizeof(double) * nT);
+    memcpy(Hy, ty, sizeof(double) * nT);
+  }
+  free(dr); free(ds); free(tx); free(ty);
+}
+
+/* the driver's time loop (src/sw2d/main.cpp:192-244): dt = computeTimeStep, Heun's SSP-RK2 with both RHS
+ * evaluations at the step-start time, sponge relaxation of hu, hv after each stage; sponge may be NULL. */
+int oracle_sw2d_step_ssprk2(const bdg_dgcontext2d *dg, const bdg_sw2d_params *prm, const double *H, const double *Hx,
+                            const double *Hy, const double *sponge, double *h, double *hu, double *hv, int nsteps,
+                            double dt, double *t) {
+  const size_t nT = (size_t)dg->Np * dg->K;
+  double *R1 = dalloc(nT), *R2 = dalloc(nT), *R3 = dalloc(nT), *h1 = dalloc(nT), *hu1 = dalloc(nT), *hv1 = dalloc(nT);
+  for (int s = 0; s < nsteps; ++s) {
+    const double dts = dt > 0 ? dt : oracle_sw2d_timestep(dg, prm, h, hu, hv, 0, NULL);
+    oracle_sw2d_rhs(dg, prm, H, Hx, Hy, h, hu, hv, *t, 0, NULL, R1, R2, R3);
+    for (size_t m = 0; m < nT; ++m) {
+      h1[m] = h[m] + dts * R1[m];
+      hu1[m] = hu[m] + dts * R2[m];
+      hv1[m] = hv[m] + dts * R3[m];
+    }
+    if (sponge)
+      for (size_t m = 0; m < nT; ++m) {
+        hu1[m] /= (1.0 + sponge[m] * hu1[m] * hu1[m]);
+        hv1[m] /= (1.0 + sponge[m] * hv1[m] * hv1[m]);
+      }
+    oracle_sw2d_rhs(dg, prm, H, Hx, Hy, h1, hu1, hv1, *t, 0, NULL, R1, R2, R3);
+    for (size_t m = 0; m < nT; ++m) {
+      h[m] = 0.5 * (h[m] + h1[m] + dts * R1[m]);
+      hu[m] = 0.5 * (hu[m] + hu1[m] + dts * R2[m]);
+      hv[m] = 0.5 * (hv[m] + hv1[m] + dts * R3[m]);
+    }
+    if (sponge)
+      for (size_t m = 0; m < nT; ++m) {
+        hu[m] /= (1.0 + sponge[m] * hu[m] * hu[m]);
+        hv[m] /= (1.0 + sponge[m] * hv[m] * hv[m]);
+      }
+    *t += dts;
+  }
+  free(R1); free(R2); free(R3); free(h1); free(hu1); free(hv1);
+  return 0;
+}
