@@ -166,10 +166,14 @@ extern "C" void bdg_sw2d_destroy(bdg_sw2d *s) {
   fused_release(s);
   void *ptrs[] = {s->q[0], s->q[1], s->res, s->rhs, s->sflux, s->d_Dr, s->d_Ds, s->d_Lift, s->d_Filt, s->d_rx, s->d_sx,
                   s->d_ry, s->d_sy, s->d_nx, s->d_ny, s->d_Fscale, s->d_aff, s->d_H, s->d_Hx, s->d_Hy, s->d_vmapP,
-                  s->d_fmask, s->d_bctag, s->d_facetag, s->d_scal, s->d_send_nodes, s->d_sendbuf, s->d_perm, s->d_vfrag, s->d_Dq, s->d_sponge};
+                  s->d_fmask, s->d_bctag, s->d_facetag, s->d_scal, s->d_send_nodes, s->d_sendbuf, s->d_perm, s->d_vfrag, s->d_Dq, s->d_sponge, s->d_IM, s->d_out};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   free(s->h_nbr); free(s->h_send_off); free(s->h_recv_off);
+  if (s->ev_out_state) cudaEventDestroy(s->ev_out_state);
+  if (s->ev_out_kernel) cudaEventDestroy(s->ev_out_kernel);
+  if (s->ev_out_done) cudaEventDestroy(s->ev_out_done);
+  if (s->out_stream) cudaStreamDestroy(s->out_stream);
   if (s->ev_pack) cudaEventDestroy(s->ev_pack);
   if (s->ev_recv) cudaEventDestroy(s->ev_recv);
   if (s->comm_stream) cudaStreamDestroy(s->comm_stream);
@@ -894,6 +898,59 @@ extern "C" int bdg_sw2d_check(bdg_sw2d *s, double *eta_max) {
   CU(cudaStreamSynchronize(s->stream));
   if (eta_max) *eta_max = r[1] != 0.0 ? NAN : r[0];
   if (r[1] != 0.0 || r[0] > 1e8) return fail(s, BDG_E_UNSTABLE, "A numerical instability has occurred!");  // reference main.cpp:238-240
+  return BDG_OK;
+}
+
+// ======================================================================================== output
+// SURVEY.md 8f rank 2 (sw2d_output.cu).  interp [n_out][Np] row-major: IM of splitElements (or any other interpolation).
+extern "C" int bdg_sw2d_set_output(bdg_sw2d *s, const double *interp, int32_t n_out) {
+  if (!s || !interp || n_out < 1 || n_out > 4096) return BDG_E_INVALID;
+  CU(cudaSetDevice(s->device));
+  if (s->out_stream) CU(cudaStreamSynchronize(s->out_stream));
+  if (s->d_IM) cudaFree(s->d_IM);
+  if (s->d_out) cudaFree(s->d_out);
+  s->d_IM = s->d_out = nullptr;
+  s->out_n = 0;
+  int rc;
+  if ((rc = dev_upload(s, &s->d_IM, interp, (size_t)n_out * s->v.Np))) return rc;
+  if ((rc = dev_alloc(s, &s->d_out, 3 * (size_t)n_out * s->v.K))) return rc;
+  if (!s->out_stream) {
+    CU(cudaStreamCreateWithFlags(&s->out_stream, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&s->ev_out_state, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&s->ev_out_kernel, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&s->ev_out_done, cudaEventDisableTiming));
+  }
+  CU(cudaStreamSynchronize(s->stream));
+  s->out_n = n_out;
+  return BDG_OK;
+}
+
+// Enqueues, behind everything already enqueued on this handle: eta = h - H, u = hu/h, v = hv/h of the live state,
+// each interpolated with interp, then their copies into the host arrays ([n_out][K] row-major; pinned memory makes
+// the copies asynchronous).  Only the interpolation kernel holds up later steps; the copies overlap them.
+extern "C" int bdg_sw2d_output_begin(bdg_sw2d *s, double *eta, double *u, double *v) {
+  if (!s) return BDG_E_INVALID;
+  if (!s->out_n) return fail(s, BDG_E_INVALID, "bdg_sw2d_output_begin needs bdg_sw2d_set_output first");
+  CU(cudaSetDevice(s->device));
+  CU(cudaEventRecord(s->ev_out_state, s->stream));
+  CU(cudaStreamWaitEvent(s->out_stream, s->ev_out_state, 0));
+  cudaError_t e = launch_output_fields(s, s->q[s->cur], s->out_stream);
+  if (e != cudaSuccess) return fail(s, BDG_E_CUDA, "output: %s", cudaGetErrorString(e));
+  CU(cudaEventRecord(s->ev_out_kernel, s->out_stream));
+  CU(cudaStreamWaitEvent(s->stream, s->ev_out_kernel, 0));  // the state buffer may be overwritten from here on
+  const size_t plane = (size_t)s->out_n * s->v.K;
+  double *dst[3] = {eta, u, v};
+  for (int c = 0; c < 3; ++c)
+    if (dst[c]) CU(cudaMemcpyAsync(dst[c], s->d_out + c * plane, sizeof(double) * plane, cudaMemcpyDeviceToHost, s->out_stream));
+  CU(cudaEventRecord(s->ev_out_done, s->out_stream));
+  return BDG_OK;
+}
+
+extern "C" int bdg_sw2d_output_wait(bdg_sw2d *s) {
+  if (!s) return BDG_E_INVALID;
+  if (!s->out_n) return BDG_OK;
+  CU(cudaSetDevice(s->device));
+  CU(cudaEventSynchronize(s->ev_out_done));
   return BDG_OK;
 }
 

@@ -106,6 +106,11 @@ struct bdg_sw2d {
   unsigned long long epoch;       // number of puts issued (identical on all ranks: same call sequence)
   int put_pending;                // a put on the communication stream has not been joined by the main stream yet
   int ghost_valid;                // the live buffer's ghost slots hold its neighbours' traces
+  // output path (sw2d_output.cu): interpolation matrix [out_n][Np], result [3][out_n*K] in the caller's layout
+  double *d_IM, *d_out;
+  int out_n;
+  cudaStream_t out_stream;
+  cudaEvent_t ev_out_state, ev_out_kernel, ev_out_done;
   int64_t launches;
   char err[512];
 };
@@ -122,6 +127,7 @@ cudaError_t launch_dt_finalize(bdg_sw2d *s);
 cudaError_t launch_advance_time(bdg_sw2d *s);
 cudaError_t launch_check(bdg_sw2d *s, const double *q);
 cudaError_t launch_pack(bdg_sw2d *s, const double *q, int with_H);
+cudaError_t launch_output_fields(bdg_sw2d *s, const double *q, cudaStream_t stream);  // eta, u, v interpolated into s->d_out
 cudaError_t launch_put(bdg_sw2d *s, const double *q, int buf, unsigned long long epoch, int side);
 cudaError_t launch_wait_epoch(bdg_sw2d *s, unsigned long long epoch);
 // fused DMMA path (affine triangles): q_in -> q_out, res in place, elements [k0,k1)

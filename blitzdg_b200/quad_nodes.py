@@ -129,3 +129,13 @@ class QuadNodesProvisioner(TriangleNodesProvisioner):
                 c += 1
         self.Filter = np.ascontiguousarray(self.V @ (np.diag(d) @ self.Vinv))
         return self.Filter
+
+    def splitTable(self):
+        """Equispaced (N+1)x(N+1) output lattice, one linear quad (v1,v2,v3,v4) per cell (src/QuadNodesProvisioner.cpp:728-770)."""
+        N = self.NumFacePoints - 1
+        rout = np.array([-1.0 + 2.0 * m / N for n in range(N + 1) for m in range(N + 1)])
+        sout = np.array([-1.0 + 2.0 * n / N for n in range(N + 1) for m in range(N + 1)])
+        c = np.arange((N + 1) * (N + 1)).reshape(N + 1, N + 1)
+        cells = [(c[n, m], c[n, m + 1], c[n + 1, m], c[n + 1, m + 1]) for n in range(N) for m in range(N)]
+        return rout, sout, np.array(cells, dtype=np.int64)
+

@@ -133,6 +133,23 @@ class SW2dSolver:
         if sync:
             self.sync()
 
+    # output path (blitzdg_b200/outputters.py::DeviceOutput drives it) ----------------
+    def set_output(self, interp):
+        """interp [n_out][Np]: the IM of splitElements (NodesProvisioner.computeInterpMatrix)."""
+        a = np.ascontiguousarray(interp, dtype=np.float64)
+        assert a.ndim == 2 and a.shape[1] == self.shape[0], a.shape
+        self._n_out = a.shape[0]
+        self._ck(self.lib.bdg_sw2d_set_output(self.h, _dp(a), a.shape[0]))
+
+    def output_begin(self, eta, u, v):
+        """eta, u, v: C-contiguous float64 [n_out][K] host arrays (pinned for asynchronous copies) or None."""
+        for a in (eta, u, v):
+            assert a is None or (a.dtype == np.float64 and a.flags.c_contiguous and a.shape == (self._n_out, self.shape[1]))
+        self._ck(self.lib.bdg_sw2d_output_begin(self.h, _dp(eta), _dp(u), _dp(v)))
+
+    def output_wait(self):
+        self._ck(self.lib.bdg_sw2d_output_wait(self.h))
+
     def sync(self):
         self._ck(self.lib.bdg_sw2d_sync(self.h))
 

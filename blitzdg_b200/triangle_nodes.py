@@ -283,6 +283,48 @@ class TriangleNodesProvisioner:
         self.Filter = np.ascontiguousarray(self.V @ (np.diag(d) @ self.Vinv))
         return self.Filter
 
+    # ------------------------------------------------------------ output support
+    def computeInterpMatrix(self, rout, sout):
+        """IM = Vout * V^-1 (src/TriangleNodesProvisioner.cpp:1140-1152, src/QuadNodesProvisioner.cpp:707-719)."""
+        Vout = self.computeVandermondeMatrix(self.NOrder, np.asarray(rout, float), np.asarray(sout, float))
+        return np.ascontiguousarray(Vout @ self.Vinv)
+
+    def splitTable(self):
+        """Equispaced output nodes and the linear sub-elements of one element (src/TriangleNodesProvisioner.cpp:1158-1204):
+        node (n,m) has r = -1 + 2m/N, s = -1 + 2n/N; triangles (v1,v2,v3) and (v2,v4,v3) per lattice cell.
+        Returns rout, sout, localE2V [numLocal][3]."""
+        N = self.NumFacePoints - 1
+        counter = -np.ones((N + 2, N + 2), dtype=np.int64)
+        rout, sout = [], []
+        for n in range(N + 1):
+            for m in range(N + 1 - n):
+                counter[n, m] = len(rout)
+                rout.append(-1.0 + 2.0 * m / N)
+                sout.append(-1.0 + 2.0 * n / N)
+        cells = []
+        for n in range(N + 1):
+            for m in range(N - n):
+                v1, v2, v3, v4 = counter[n, m], counter[n, m + 1], counter[n + 1, m], counter[n + 1, m + 1]
+                cells.append((v1, v2, v3))
+                if v4 >= 0:
+                    cells.append((v2, v4, v3))
+        return np.array(rout), np.array(sout), np.array(cells, dtype=np.int64)
+
+    def splitElements(self, x, y, field, interpolated=False):
+        """splitElements of the reference (src/TriangleNodesProvisioner.cpp:1154-1264, src/QuadNodesProvisioner.cpp:721-845):
+        x, y, field [Np][K] -> xnew, ynew, fieldnew [3 or 4][numLocal*K], every linear sub-element with its own corner
+        values.  interpolated=True: `field` already holds IM*field (the device output path), only x, y are interpolated."""
+        rout, sout, cells = self.splitTable()
+        IM = self.computeInterpMatrix(rout, sout)
+        K = field.shape[1]
+        fi = field if interpolated else IM @ field
+        idx = cells.T  # [corners][numLocal]
+
+        def corners(a):  # -> [corners][numLocal*K], element-major like E2Vnew
+            return np.ascontiguousarray(a[idx].transpose(0, 2, 1).reshape(idx.shape[0], -1))
+
+        return corners(IM @ x), corners(IM @ y), corners(fi)
+
     # ------------------------------------------------------------ getters
     def get_NumLocalPoints(self):
         return self.NumLocalPoints

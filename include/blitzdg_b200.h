@@ -121,6 +121,19 @@ int bdg_sw2d_step_ssprk2(bdg_sw2d *s, int32_t nsteps, double dt);
  * => BDG_E_UNSTABLE.  eta_max may be NULL. */
 int bdg_sw2d_check(bdg_sw2d *s, double *eta_max);
 
+/* --- output path ---------------------------------------------------------------------------
+ * Every outputInterval steps the drivers derive eta = h - H, u = hu/h, v = hv/h (reference src/sw2d/main.cpp:199-210)
+ * and VtkOutputter::writeFieldToFile (reference include/VtkOutputter.hpp:48-101) interpolates each to the equispaced
+ * nodes of the sub-element split, resultField = IM * field (splitElements, src/TriangleNodesProvisioner.cpp:1154-1227,
+ * src/QuadNodesProvisioner.cpp:721-800).  set_output: interp = that IM, [n_out][Np] row-major (copied).
+ * output_begin: enqueues the derivation + the three interpolations of the live state and the copies of the results
+ * into eta, u, v (host, [n_out][K] row-major, any may be NULL; pinned memory keeps the copies asynchronous) on a side
+ * stream: later bdg_sw2d_step calls only wait for the interpolation kernel, not for the copies.
+ * output_wait: blocks until the host arrays of the last output_begin are complete. */
+int bdg_sw2d_set_output(bdg_sw2d *s, const double *interp, int32_t n_out);
+int bdg_sw2d_output_begin(bdg_sw2d *s, double *eta, double *u, double *v);
+int bdg_sw2d_output_wait(bdg_sw2d *s);
+
 /* --- plumbing ----------------------------------------------------------------------------- */
 /* kernel variant used by step(): 0 = auto, 1 = generic two-kernel path, 2 = fused DMMA path */
 int bdg_sw2d_set_variant(bdg_sw2d *s, int32_t variant);
