@@ -302,12 +302,14 @@ def run_b200(args):
         torch.cuda.synchronize()
         sol.sync()
 
-    def timed(fn, steps):
+    def timed(fn, steps, tail=None):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         for _ in range(steps):
             fn()
+        if tail is not None:
+            tail()  # host-side join of side-stream work: e1 is recorded, and reached, after it
         e1.record(stream)
         sol.sync()
         torch.cuda.synchronize()
@@ -368,9 +370,37 @@ def run_b200(args):
         n_e2e = max(1, min(args.steps, 5))
         ms2 = timed(e2e_step, n_e2e)
         bytes_dir = 3 * ctx.Np * ctx.K * 8
-        e2e = {"value": 3.0 * ctx.Np * K_global * nst * OUTPUT_INTERVAL * n_e2e / (ms2 * 1e-3), "unit": UNIT,
-               "h2d_bytes_per_step": bytes_dir, "d2h_bytes_per_step": bytes_dir, "steps": n_e2e,
-               "api": "bdg_sw2d_set_state (pinned host) -> %s -> bdg_sw2d_get_state" % ("bdg_sw2d_step_ssprk2" if rk2 else "bdg_sw2d_step")}
+        stepper = "bdg_sw2d_step_ssprk2" if rk2 else "bdg_sw2d_step"
+        serial = 3.0 * ctx.Np * K_global * nst * OUTPUT_INTERVAL * n_e2e / (ms2 * 1e-3)
+        # The same batches through the streaming calls: every step still uploads its own input from pinned host memory
+        # and downloads its own result, but the upload of step i+1 and the download of step i-1 overlap the launches
+        # of step i (both PCIe directions + the SMs busy at once).  The first upload and the last download are exposed.
+        dst2 = [dst, [torch.empty(h.shape, dtype=torch.float64).pin_memory().numpy() for _ in range(3)]]
+        n_pipe = max(2, min(args.steps, 10))
+        it = {"i": 0, "n": 0}
+
+        def pipe_step():
+            i = it["i"]
+            it["i"] += 1
+            if i == 0:
+                sol.stage_state(src[0], src[1], src[2])
+            sol.commit_state()
+            if i + 1 < it["n"]:
+                sol.stage_state(src[0], src[1], src[2])
+            advance(OUTPUT_INTERVAL, dt, sync=False)
+            sol.get_state_async(dst2[i & 1])
+
+        it.update(i=0, n=2)
+        timed(pipe_step, 2, tail=sol.get_state_wait)  # warm-up: allocates the streaming buffers
+        it.update(i=0, n=n_pipe)
+        ms3 = timed(pipe_step, n_pipe, tail=sol.get_state_wait)
+        piped = 3.0 * ctx.Np * K_global * nst * OUTPUT_INTERVAL * n_pipe / (ms3 * 1e-3)
+        same = all(np.array_equal(a, b) for a, b in zip(dst2[0], dst2[1])) and np.array_equal(dst2[0][0], dst[0])
+        e2e = {"value": piped, "unit": UNIT, "h2d_bytes_per_step": bytes_dir, "d2h_bytes_per_step": bytes_dir, "steps": n_pipe,
+               "api": "per step: bdg_sw2d_commit_state (input staged by bdg_sw2d_stage_state from pinned host) -> %s -> bdg_sw2d_get_state_async; "
+                      "copies of neighbouring steps overlap the launches; joined by bdg_sw2d_get_state_wait inside the timed region" % stepper,
+               "serial": {"value": serial, "steps": n_e2e, "api": "bdg_sw2d_set_state (pinned host) -> %s -> bdg_sw2d_get_state, nothing overlapped" % stepper},
+               "results_identical_to_serial": bool(same)}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

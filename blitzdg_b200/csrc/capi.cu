@@ -166,10 +166,14 @@ extern "C" void bdg_sw2d_destroy(bdg_sw2d *s) {
   fused_release(s);
   void *ptrs[] = {s->q[0], s->q[1], s->res, s->rhs, s->sflux, s->d_Dr, s->d_Ds, s->d_Lift, s->d_Filt, s->d_rx, s->d_sx,
                   s->d_ry, s->d_sy, s->d_nx, s->d_ny, s->d_Fscale, s->d_aff, s->d_H, s->d_Hx, s->d_Hy, s->d_vmapP,
-                  s->d_fmask, s->d_bctag, s->d_facetag, s->d_scal, s->d_send_nodes, s->d_sendbuf, s->d_perm, s->d_vfrag, s->d_Dq, s->d_sponge, s->d_IM, s->d_out};
+                  s->d_fmask, s->d_bctag, s->d_facetag, s->d_scal, s->d_send_nodes, s->d_sendbuf, s->d_perm, s->d_vfrag, s->d_Dq, s->d_sponge, s->d_IM, s->d_out, s->in_raw, s->dl_raw};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   free(s->h_nbr); free(s->h_send_off); free(s->h_recv_off);
+  for (cudaEvent_t ev : {s->ev_in_done, s->ev_in_free, s->ev_dl_conv, s->ev_dl_done})
+    if (ev) cudaEventDestroy(ev);
+  if (s->in_stream) cudaStreamDestroy(s->in_stream);
+  if (s->dl_stream) cudaStreamDestroy(s->dl_stream);
   if (s->ev_out_state) cudaEventDestroy(s->ev_out_state);
   if (s->ev_out_kernel) cudaEventDestroy(s->ev_out_kernel);
   if (s->ev_out_done) cudaEventDestroy(s->ev_out_done);
@@ -503,6 +507,99 @@ extern "C" int bdg_sw2d_get_state(bdg_sw2d *s, double *h, double *hu, double *hv
     CU(cudaStreamSynchronize(s->stream));
     *t = s->t;
   }
+  return BDG_OK;
+}
+
+// ---- streaming interface: batches of independent states (ensemble members, parameter sweeps, restarts) -----------
+// The upload of the next state and the download of the previous result run on their own streams (both directions
+// of the PCIe link at once) while the steps of the current state occupy the SMs:
+//   stage_state(i+1) | commit_state(i), step(i) ... | get_state_async(i-1)
+// The layout conversions run on the main stream (they are HBM-speed and short), only the raw copies are forked.
+static int streaming_setup(bdg_sw2d *s) {
+  if (s->in_stream) return BDG_OK;
+  int rc;
+  if ((rc = dev_alloc(s, &s->in_raw, 3 * s->nT))) return rc;
+  if ((rc = dev_alloc(s, &s->dl_raw, 3 * s->nT))) return rc;
+  CU(cudaStreamCreateWithFlags(&s->in_stream, cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&s->dl_stream, cudaStreamNonBlocking));
+  for (cudaEvent_t *ev : {&s->ev_in_done, &s->ev_in_free, &s->ev_dl_conv, &s->ev_dl_done}) CU(cudaEventCreateWithFlags(ev, cudaEventDisableTiming));
+  return BDG_OK;
+}
+
+// Starts the upload of a state that bdg_sw2d_commit_state will make the live one.  The host arrays must stay valid
+// (and should be pinned) until commit_state has been called and the handle synchronised or stepped.
+extern "C" int bdg_sw2d_stage_state(bdg_sw2d *s, const double *h, const double *hu, const double *hv, double t) {
+  if (!s || !h || !hu || !hv) return BDG_E_INVALID;
+  CU(cudaSetDevice(s->device));
+  int rc = streaming_setup(s);
+  if (rc) return rc;
+  if (s->staged) return fail(s, BDG_E_INVALID, "bdg_sw2d_stage_state: a staged state is waiting for bdg_sw2d_commit_state");
+  CU(cudaStreamWaitEvent(s->in_stream, s->ev_in_free, 0));  // the previous commit has consumed in_raw (no-op the first time)
+  const double *src[3] = {h, hu, hv};
+  for (int c = 0; c < 3; ++c) CU(cudaMemcpyAsync(s->in_raw + c * s->nT, src[c], sizeof(double) * s->nT, cudaMemcpyHostToDevice, s->in_stream));
+  CU(cudaEventRecord(s->ev_in_done, s->in_stream));
+  s->staged = 1;
+  s->staged_t = t;
+  return BDG_OK;
+}
+
+// Stream-ordered bdg_sw2d_set_state of the staged arrays: everything enqueued later sees the new state.
+extern "C" int bdg_sw2d_commit_state(bdg_sw2d *s) {
+  if (!s) return BDG_E_INVALID;
+  if (!s->staged) return fail(s, BDG_E_INVALID, "bdg_sw2d_commit_state without bdg_sw2d_stage_state");
+  CU(cudaSetDevice(s->device));
+  if (s->put_pending) {
+    CU(cudaStreamSynchronize(s->comm_stream));
+    s->put_pending = 0;
+  }
+  CU(cudaStreamWaitEvent(s->stream, s->ev_in_done, 0));
+  double *q = s->q[s->cur];
+  const int R = s->v.Np, KB = tile_kb(R);
+  const long long K = s->v.K;
+  for (int c = 0; c < 3; ++c) {
+    k_rowmajor_to_elem<<<(unsigned)((K + KB - 1) / KB), 256, sizeof(double) * R * (KB + 1), s->stream>>>(s->in_raw + c * s->nT, q + c * s->v.stride, R, K, KB, s->d_perm);
+    s->launches++;
+  }
+  CU(cudaGetLastError());
+  CU(cudaEventRecord(s->ev_in_free, s->stream));
+  CU(cudaMemsetAsync(s->res, 0, sizeof(double) * 3 * s->v.stride, s->stream));
+  s->t = s->staged_t;
+  s->staged = 0;
+  s->ghost_valid = 0;
+  CU(cudaMemcpyAsync(s->d_scal + S_T, &s->t, sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  return BDG_OK;
+}
+
+// Snapshot of the live state behind everything enqueued so far; the copies into h, hu, hv ([Np][K], pinned) run on a
+// side stream while later work proceeds.  bdg_sw2d_get_state_wait blocks until they have arrived.
+extern "C" int bdg_sw2d_get_state_async(bdg_sw2d *s, double *h, double *hu, double *hv) {
+  if (!s || !h || !hu || !hv) return BDG_E_INVALID;
+  CU(cudaSetDevice(s->device));
+  int rc = streaming_setup(s);
+  if (rc) return rc;
+  if (s->dl_pending) CU(cudaStreamWaitEvent(s->stream, s->ev_dl_done, 0));  // the previous snapshot has left dl_raw
+  const double *q = s->q[s->cur];
+  const int R = s->v.Np, KB = tile_kb(R);
+  const long long K = s->v.K;
+  for (int c = 0; c < 3; ++c) {
+    k_elem_to_rowmajor<<<(unsigned)((K + KB - 1) / KB), 256, sizeof(double) * R * (KB + 1), s->stream>>>(q + c * s->v.stride, s->dl_raw + c * s->nT, R, K, KB, s->d_perm);
+    s->launches++;
+  }
+  CU(cudaGetLastError());
+  CU(cudaEventRecord(s->ev_dl_conv, s->stream));
+  CU(cudaStreamWaitEvent(s->dl_stream, s->ev_dl_conv, 0));
+  double *dst[3] = {h, hu, hv};
+  for (int c = 0; c < 3; ++c) CU(cudaMemcpyAsync(dst[c], s->dl_raw + c * s->nT, sizeof(double) * s->nT, cudaMemcpyDeviceToHost, s->dl_stream));
+  CU(cudaEventRecord(s->ev_dl_done, s->dl_stream));
+  s->dl_pending = 1;
+  return BDG_OK;
+}
+
+extern "C" int bdg_sw2d_get_state_wait(bdg_sw2d *s) {
+  if (!s) return BDG_E_INVALID;
+  if (!s->dl_pending) return BDG_OK;
+  CU(cudaSetDevice(s->device));
+  CU(cudaEventSynchronize(s->ev_dl_done));
   return BDG_OK;
 }
 

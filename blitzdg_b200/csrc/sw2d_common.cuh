@@ -111,6 +111,12 @@ struct bdg_sw2d {
   int out_n;
   cudaStream_t out_stream;
   cudaEvent_t ev_out_state, ev_out_kernel, ev_out_done;
+  // streaming interface (capi.cu: stage_state / commit_state / get_state_async): raw row-major planes [3][Np*K]
+  double *in_raw, *dl_raw;
+  cudaStream_t in_stream, dl_stream;
+  cudaEvent_t ev_in_done, ev_in_free, ev_dl_conv, ev_dl_done;
+  int staged, dl_pending;
+  double staged_t;
   int64_t launches;
   char err[512];
 };

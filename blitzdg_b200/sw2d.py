@@ -105,6 +105,25 @@ class SW2dSolver:
         self._ck(self.lib.bdg_sw2d_get_state(self.h, _dp(h), _dp(hu), _dp(hv), C.byref(t)))
         return h, hu, hv, t.value
 
+    # streaming variants (batches of independent states): copies overlap the steps of the current state
+    def stage_state(self, h, hu, hv, t=0.0):
+        """h, hu, hv must be C-contiguous float64 [Np][K] (pinned for real overlap) and stay alive until commit_state ran."""
+        for a in (h, hu, hv):
+            assert a.dtype == np.float64 and a.flags.c_contiguous and a.shape == self.shape
+        self._staged = (h, hu, hv)
+        self._ck(self.lib.bdg_sw2d_stage_state(self.h, _dp(h), _dp(hu), _dp(hv), float(t)))
+
+    def commit_state(self):
+        self._ck(self.lib.bdg_sw2d_commit_state(self.h))
+
+    def get_state_async(self, out):
+        for a in out:
+            assert a.dtype == np.float64 and a.flags.c_contiguous and a.shape == self.shape
+        self._ck(self.lib.bdg_sw2d_get_state_async(self.h, _dp(out[0]), _dp(out[1]), _dp(out[2])))
+
+    def get_state_wait(self):
+        self._ck(self.lib.bdg_sw2d_get_state_wait(self.h))
+
     # hot path ------------------------------------------------------------------------------------
     def computeRHS(self):
         """sw2d::computeRHS on the current device state; returns (RHS1, RHS2, RHS3) as [Np][K]."""

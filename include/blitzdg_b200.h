@@ -99,6 +99,17 @@ int bdg_sw2d_set_bathymetry(bdg_sw2d *s, const double *H, const double *Hx, cons
 int bdg_sw2d_set_state(bdg_sw2d *s, const double *h, const double *hu, const double *hv, double t);
 int bdg_sw2d_get_state(bdg_sw2d *s, double *h, double *hu, double *hv, double *t);
 
+/* Streaming variants for batches of independent states (ensemble members, parameter sweeps): the upload of the next
+ * state and the download of the previous result use both directions of the PCIe link while the steps of the
+ * current state run.  stage_state starts the upload (host arrays pinned and valid until the commit has executed);
+ * commit_state is a stream-ordered set_state of the staged arrays; get_state_async snapshots the live state behind
+ * everything enqueued so far and copies it out on a side stream; get_state_wait blocks until it has arrived.
+ *     stage(0); for i: commit(); stage(i+1); step(...); get_state_async(out[i%2]); ...; get_state_wait();          */
+int bdg_sw2d_stage_state(bdg_sw2d *s, const double *h, const double *hu, const double *hv, double t);
+int bdg_sw2d_commit_state(bdg_sw2d *s);
+int bdg_sw2d_get_state_async(bdg_sw2d *s, double *h, double *hu, double *hv);
+int bdg_sw2d_get_state_wait(bdg_sw2d *s);
+
 /* --- the hot path ------------------------------------------------------------------------- */
 /* one evaluation of sw2d::computeRHS on the current state at the current time; host out [Np][K] */
 int bdg_sw2d_rhs(bdg_sw2d *s, double *RHS1, double *RHS2, double *RHS3);

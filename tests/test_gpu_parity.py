@@ -272,3 +272,46 @@ def test_full_size_properties_1M_triangles():
         for a, b in zip(Ra, Rb):
             assert relerr(a, b) < 5e-11
     sol.close()
+
+
+def test_streaming_state_calls_equal_serial_calls():
+    """stage_state / commit_state / get_state_async / get_state_wait: a batch of independent states pushed through the
+    overlapped calls gives bitwise what set_state -> step -> get_state gives, in order; misuse is an error."""
+    import torch
+
+    ctx = provision(structured_mesh("tri", 48, 20), 4).get_DGContext()
+    _, h, hu, hv = _state(ctx, seed=1, amp=0.1)
+    sol = _solver(ctx)
+    sol.set_state(h, hu, hv)
+    dt = 0.5 * sol.computeTimeStep()
+    batch = []
+    for i in range(4):
+        rng = np.random.default_rng(100 + i)
+        batch.append([np.ascontiguousarray(a) for a in (h + 0.01 * i, 0.1 * rng.standard_normal(h.shape), 0.1 * rng.standard_normal(h.shape))])
+    want = []
+    for b in batch:
+        sol.set_state(*b, t=1.5)
+        sol.step(7, dt)
+        want.append(sol.get_state())
+    pin = lambda: [torch.empty(h.shape, dtype=torch.float64).pin_memory().numpy() for _ in range(3)]
+    src, out = [pin() for _ in batch], [pin() for _ in batch]
+    for s_, b in zip(src, batch):
+        for a, c in zip(s_, b):
+            a[...] = c
+    with pytest.raises(RuntimeError):
+        sol.commit_state()
+    sol.stage_state(*src[0], t=1.5)
+    with pytest.raises(RuntimeError):
+        sol.stage_state(*src[1], t=1.5)
+    for i in range(len(batch)):
+        sol.commit_state()
+        if i + 1 < len(batch):
+            sol.stage_state(*src[i + 1], t=1.5)
+        sol.step(7, dt, sync=False)
+        sol.get_state_async(out[i])
+    sol.get_state_wait()
+    for i in range(len(batch)):
+        for c in range(3):
+            assert np.array_equal(out[i][c], want[i][c]), (i, c)
+    assert sol.get_state()[3] == want[-1][3]
+    sol.close()
