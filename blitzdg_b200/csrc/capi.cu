@@ -341,6 +341,14 @@ static int create_impl(bdg_sw2d *s, const bdg_dgcontext2d *c, const bdg_sw2d_par
       }
     if (ok) {
       s->is_affine = 1;
+      // The fused kernel wants the face triple as (nx, ny, 1) * Fscale/2: the 1/2 of the flux jump (main.cpp:416-421) and
+      // the Fscale of the surface term (:451-458) are folded into the normal once, here, instead of per face node per stage.
+      for (long long k = 0; k < K; ++k)
+        for (int f = 0; f < Nf; ++f) {
+          double *t3 = &aff[k * W + 4 + 3 * f];
+          const double hfs = 0.5 * t3[2];
+          t3[0] *= hfs; t3[1] *= hfs; t3[2] = hfs;
+        }
       if (renum) {
         std::vector<double> a2(aff.size());
         for (long long k = 0; k < K; ++k) memcpy(&a2[k * W], &aff[(size_t)perm[k] * W], sizeof(double) * W);

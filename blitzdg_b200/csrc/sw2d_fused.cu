@@ -46,7 +46,7 @@ namespace {
 constexpr int kWarps = 4;
 constexpr int kThreads = kWarps * 32;
 constexpr int kTile = kWarps * 8;  // elements per CTA tile
-constexpr int kAW = 13;            // doubles per element in v.aff: rx,sx,ry,sy,(nx,ny,Fscale)x3
+constexpr int kAW = 13;            // doubles per element in v.aff: rx,sx,ry,sy,(nx*c,ny*c,c)x3 with c = Fscale/2 (folded at create)
 constexpr int kGI = 5;             // ghost indices a thread can carry: Gmax <= kGI*kThreads
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -119,9 +119,8 @@ __device__ __forceinline__ double fsqrt(double x) {
   double hh = 0.5 * r, s = x * r;
   double e = fma(-hh, s, 0.5);
   s = fma(s, e, s);
-  hh = fma(hh, e, hh);
-  e = fma(-s, s, x);  // seed error d -> ~1.5 d^2 after the coupled step -> O(d^4) after this correction (d <= 2^-20)
-  return fma(e, hh, s);
+  e = fma(-s, s, x);  // seed error d -> ~1.5 d^2 after the coupled step -> O(d^3) after this correction (d <= 2^-20):
+  return fma(e, hh, s);  // the correction term is already ~d^2 small, so the unrefined 1/(2 sqrt) (relative error d) serves
 }
 
 #ifdef BDG_PHASEPROF
@@ -307,7 +306,8 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
         const double spdM = sFl[3 * PS + m];
         if (decltype(with_wall)::value && ((wallmask >> kb) & 1u)) {
           double a0, a1, a2, a3, a4;
-          wall_trace(af[4 + 3 * f], af[5 + 3 * f], sQ[m], sQ[PS + m], sQ[2 * PS + m], a0, a1, a2, a3, a4, spdP);
+          const double ih = frcp(af[6 + 3 * f]);  // unit normal back from the folded one (walls are rare)
+          wall_trace(af[4 + 3 * f] * ih, af[5 + 3 * f] * ih, sQ[m], sQ[PS + m], sQ[2 * PS + m], a0, a1, a2, a3, a4, spdP);
         }
         const double sp = dmax(spdM, spdP);
         if (fixed_face) {  // the only position of this thread on face kb so far
@@ -336,8 +336,8 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   for (int kb = 0; kb < NFB; ++kb) {
     const int f = (C::FACE_BLOCKS && kb < 3) ? kb : (fm[kb] >> 16) & 15;
     const int m = eo + (fm[kb] & 0xffff), r = word[kb] & 0xffffu;
-    const double nx = af[4 + 3 * f], ny = af[5 + 3 * f], hfs = 0.5 * af[6 + 3 * f];
-    const double l = f == 0 ? lam0 : (f == 1 ? lam1 : lam2);
+    const double nx = af[4 + 3 * f], ny = af[5 + 3 * f], hfs = af[6 + 3 * f];  // (nx, ny, 1) * Fscale/2
+    const double l = hfs * (f == 0 ? lam0 : (f == 1 ? lam1 : lam2));
     const double hM = sQ[m], huM = sQ[PS + m], hvM = sQ[2 * PS + m];
     const double F2M = sFl[m], G2M = sFl[PS + m], G3M = sFl[2 * PS + m];
     double hP = sQ[r], huP = sQ[PS + r], hvP = sQ[2 * PS + r];
@@ -345,12 +345,13 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
     if (decltype(with_wall)::value && ((wallmask >> kb) & 1u)) {
       double spd_unused;
       hP = hM;
-      wall_trace(nx, ny, hM, huM, hvM, huP, hvP, F2P, G2P, G3P, spd_unused);
+      const double ih = frcp(hfs);
+      wall_trace(nx * ih, ny * ih, hM, huM, hvM, huP, hvP, F2P, G2P, G3P, spd_unused);
     }
     const double dh = hM - hP, dhu = huM - huP, dhv = hvM - hvP, dG2 = G2M - G2P;
-    sfl[kb][0] = hfs * fma(-l, dh, fma(dhu, nx, dhv * ny));
-    sfl[kb][1] = hfs * fma(-l, dhu, fma(F2M - F2P, nx, dG2 * ny));
-    sfl[kb][2] = hfs * fma(-l, dhv, fma(dG2, nx, (G3M - G3P) * ny));
+    sfl[kb][0] = fma(-l, dh, fma(dhu, nx, dhv * ny));
+    sfl[kb][1] = fma(-l, dhu, fma(F2M - F2P, nx, dG2 * ny));
+    sfl[kb][2] = fma(-l, dhv, fma(dG2, nx, (G3M - G3P) * ny));
   }
   };
   if (any_wall) pass_b(std::true_type{}); else pass_b(std::false_type{});
