@@ -1006,6 +1006,21 @@ extern "C" int bdg_sw2d_check(bdg_sw2d *s, double *eta_max) {
   return BDG_OK;
 }
 
+// positivityPreservingLimiter2D of the Python drivers (reference swhelpers/limiters.py:3-21) on the live state
+extern "C" int bdg_sw2d_limit_positivity(bdg_sw2d *s) {
+  if (!s) return BDG_E_INVALID;
+  if (s->v.Np > 64) return fail(s, BDG_E_UNSUPPORTED, "positivity limiter: Np = %d > 64", s->v.Np);
+  CU(cudaSetDevice(s->device));
+  if (s->put_pending) {
+    CU(cudaStreamWaitEvent(s->stream, s->ev_recv, 0));
+    s->put_pending = 0;
+  }
+  cudaError_t e = launch_positivity_limiter(s, s->q[s->cur]);
+  if (e != cudaSuccess) return fail(s, BDG_E_CUDA, "limiter: %s", cudaGetErrorString(e));
+  s->ghost_valid = 0;  // neighbours hold traces of the unlimited state
+  return BDG_OK;
+}
+
 // ======================================================================================== output
 // SURVEY.md 8f rank 2 (sw2d_output.cu).  interp [n_out][Np] row-major: IM of splitElements (or any other interpolation).
 extern "C" int bdg_sw2d_set_output(bdg_sw2d *s, const double *interp, int32_t n_out) {

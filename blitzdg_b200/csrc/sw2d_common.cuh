@@ -133,6 +133,7 @@ cudaError_t launch_dt_finalize(bdg_sw2d *s);
 cudaError_t launch_advance_time(bdg_sw2d *s);
 cudaError_t launch_check(bdg_sw2d *s, const double *q);
 cudaError_t launch_pack(bdg_sw2d *s, const double *q, int with_H);
+cudaError_t launch_positivity_limiter(bdg_sw2d *s, double *q);  // swhelpers/limiters.py:3-21 on the live state, in place
 cudaError_t launch_output_fields(bdg_sw2d *s, const double *q, cudaStream_t stream);  // eta, u, v interpolated into s->d_out
 cudaError_t launch_put(bdg_sw2d *s, const double *q, int buf, unsigned long long epoch, int side);
 cudaError_t launch_wait_epoch(bdg_sw2d *s, unsigned long long epoch);

@@ -51,7 +51,54 @@ __global__ void __launch_bounds__(kOutThreads) k_output_fields(Sw2dView v, const
   }
 }
 
+// Positivity-preserving limiter of the Python drivers (swhelpers/limiters.py:3-21): per element
+// theta = min(1, mean(h) / (mean(h) - max(min(h), 1e-3) + 1e-4)); every field is pulled towards its element mean,
+// q = mean(q) + theta*(q - mean(q)).  One warp per element (Np <= 64 nodes: two per lane), shuffles for min and sums.
+__global__ void __launch_bounds__(256) k_positivity_limiter(Sw2dView v, double *__restrict__ q) {
+  const int lane = threadIdx.x & 31, Np = v.Np;
+  const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  const double inv = 1.0 / Np;
+  for (long long k = warp; k < v.K; k += nwarps) {
+    const long long m0 = k * Np;
+    const bool a = lane < Np, b = lane + 32 < Np;
+    double x[3][2], sum[3], hmin = 1e300;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      x[i][0] = a ? q[i * v.stride + m0 + lane] : 0.0;
+      x[i][1] = b ? q[i * v.stride + m0 + lane + 32] : 0.0;
+      sum[i] = x[i][0] + x[i][1];
+    }
+    if (a) hmin = x[0][0];
+    if (b) hmin = fmin(hmin, x[0][1]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      hmin = fmin(hmin, __shfl_xor_sync(0xffffffffu, hmin, o));
+#pragma unroll
+      for (int i = 0; i < 3; ++i) sum[i] += __shfl_xor_sync(0xffffffffu, sum[i], o);
+    }
+    hmin = fmax(hmin, 1e-3);
+    const double hmean = sum[0] * inv;
+    const double theta = fmin(1.0, hmean / (hmean - hmin + 1e-4));
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const double mean = sum[i] * inv;
+      if (a) q[i * v.stride + m0 + lane] = mean + theta * (x[i][0] - mean);
+      if (b) q[i * v.stride + m0 + lane + 32] = mean + theta * (x[i][1] - mean);
+    }
+  }
+}
+
 }  // namespace
+
+cudaError_t launch_positivity_limiter(bdg_sw2d *s, double *q) {
+  if (s->v.Np > 64) return cudaErrorInvalidValue;
+  const long long warps = s->v.K;
+  long long blocks = (warps + 7) / 8;
+  if (blocks > 148 * 32) blocks = 148 * 32;
+  k_positivity_limiter<<<(unsigned)blocks, 256, 0, s->stream>>>(s->v, q);
+  s->launches++;
+  return cudaGetLastError();
+}
 
 cudaError_t launch_output_fields(bdg_sw2d *s, const double *q, cudaStream_t stream) {
   const int Np = s->v.Np, n_out = s->out_n;

@@ -169,6 +169,10 @@ class SW2dSolver:
     def output_wait(self):
         self._ck(self.lib.bdg_sw2d_output_wait(self.h))
 
+    def positivityPreservingLimiter2D(self):
+        """swhelpers/limiters.py:3-21 on the device state, in place (the Python drivers call it after a stage)."""
+        self._ck(self.lib.bdg_sw2d_limit_positivity(self.h))
+
     def sync(self):
         self._ck(self.lib.bdg_sw2d_sync(self.h))
 

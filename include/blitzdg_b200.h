@@ -132,6 +132,11 @@ int bdg_sw2d_step_ssprk2(bdg_sw2d *s, int32_t nsteps, double dt);
  * => BDG_E_UNSTABLE.  eta_max may be NULL. */
 int bdg_sw2d_check(bdg_sw2d *s, double *eta_max);
 
+/* positivityPreservingLimiter2D of the Python drivers (reference swhelpers/limiters.py:3-21) applied
+ * to the live state in place: per element theta = min(1, mean(h)/(mean(h) - max(min(h),1e-3) + 1e-4)) and
+ * q = mean(q) + theta*(q - mean(q)) for h, hu, hv (arithmetic node means).  Stream-ordered like bdg_sw2d_step. */
+int bdg_sw2d_limit_positivity(bdg_sw2d *s);
+
 /* --- output path ---------------------------------------------------------------------------
  * Every outputInterval steps the drivers derive eta = h - H, u = hu/h, v = hv/h (reference src/sw2d/main.cpp:199-210)
  * and VtkOutputter::writeFieldToFile (reference include/VtkOutputter.hpp:48-101) interpolates each to the equispaced

@@ -74,3 +74,18 @@ def insert_all_cells(x, y, field):
 
 def derived_fields(h, hu, hv, H):
     return {"eta": h - H, "u": hu / h, "v": hv / h}
+
+
+def positivity_limiter(h, hu, hv):
+    """Restatement of swhelpers/limiters.py:3-21, element by element: theta from the element's mean and minimum depth
+    (minimum floored at 1e-3, theta capped at 1), then every field contracted towards its element mean."""
+    Np, K = h.shape
+    out = [np.empty_like(h), np.empty_like(h), np.empty_like(h)]
+    for k in range(K):
+        hmin = max(h[:, k].min(), 1e-3)
+        hmean = h[:, k].mean()
+        theta = min(hmean / (hmean - hmin + 1e-4), 1.0)
+        for o, f in zip(out, (h, hu, hv)):
+            mean = f[:, k].mean()
+            o[:, k] = mean + theta * (f[:, k] - mean)
+    return out

@@ -220,3 +220,46 @@ def test_ssprk2_thread_per_node_kernels():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "launches" in r.stdout, r.stdout + r.stderr
+
+
+# ---- positivity limiter of the Python drivers (swhelpers/limiters.py:3-21) --------------------
+def test_oracle_limiter_properties(coarse_box_mesh):
+    """What the reference function does as written: the floor `hmin[hmin < 1e-3] = 1e-3` makes theta >= 1 (clipped to 1,
+    i.e. no limiting) whenever the element mean exceeds ~9e-4; only nearly dry elements are contracted.  Element means
+    are always kept.  The device kernel reproduces exactly this (test_device_limiter_matches_oracle)."""
+    from oracle.output_numpy import positivity_limiter
+
+    ctx = _ctx(coarse_box_mesh, 4, filt=False)
+    rng = np.random.default_rng(0)
+    h = 0.05 + 0.06 * rng.standard_normal(ctx.x.shape)
+    h[:, 1::2] = 5e-4 + 2e-4 * rng.standard_normal((ctx.Np, h[:, 1::2].shape[1]))  # nearly dry elements
+    hu, hv = rng.standard_normal(h.shape), rng.standard_normal(h.shape)
+    a, b, c = positivity_limiter(h, hu, hv)
+    wet = h.mean(axis=0) > 1e-3
+    assert wet.any() and (~wet).any()
+    assert np.abs(a[:, wet] - h[:, wet]).max() < 1e-15 and np.abs(b[:, wet] - hu[:, wet]).max() < 1e-14
+    assert np.abs(a[:, ~wet] - h[:, ~wet]).max() > 1e-5  # theta != 1 there
+    for x, y in ((a, h), (b, hu), (c, hv)):
+        assert np.abs(x.mean(axis=0) - y.mean(axis=0)).max() < 1e-13
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("quad,N", [(False, 4), (False, 8), (True, 3), (True, 6)])
+def test_device_limiter_matches_oracle(coarse_box_mesh, coarse_quads_mesh, quad, N):
+    from oracle.output_numpy import positivity_limiter
+
+    ctx = _ctx(coarse_quads_mesh if quad else coarse_box_mesh, N, quad, filt=False)
+    rng = np.random.default_rng(N)
+    h = 0.05 + 0.06 * rng.standard_normal(ctx.x.shape)
+    h[:, ::3] += 1.0
+    h[:, 1::3] = 5e-4 + 2e-4 * rng.standard_normal((ctx.Np, h[:, 1::3].shape[1]))  # nearly dry: theta != 1
+    hu, hv = rng.standard_normal(h.shape), rng.standard_normal(h.shape)
+    want = positivity_limiter(h, hu, hv)
+    sol = _solver(ctx)
+    sol.set_state(h, hu, hv)
+    sol.positivityPreservingLimiter2D()
+    got = sol.get_state()
+    sol.close()
+    assert np.abs(want[0] - h).max() > 1e-5
+    for g, w in zip(got[:3], want):
+        assert np.abs(g - w).max() <= 1e-12 * max(np.abs(w).max(), 1.0)
