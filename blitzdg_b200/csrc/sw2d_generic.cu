@@ -17,6 +17,29 @@ struct Trace {
   double hM, huM, hvM, hP, huP, hvP, nx, ny;
 };
 
+// 1/x by MUFU seed + two Newton steps (x = 0 gives NaN like the reference's 0/0)
+__device__ __forceinline__ double frcp(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  double e = fma(-x, r, 1.0);
+  r = fma(r, e, r);
+  e = fma(-x, r, 1.0);
+  return fma(r, e, r);
+}
+
+// sqrt(x), x >= 0: coupled Newton on (sqrt, 1/(2 sqrt)) from the MUFU rsqrt seed + one correction (as in sw2d_fused.cu);
+// x = 0 -> 0, NaN -> NaN.  The library sqrt/divide sequences cost 2-3x the fp64-pipe slots of these.
+__device__ __forceinline__ double fsqrt(double x) {
+  double r;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  if (x == 0.0) r = 0.0;  // rsqrt(0) = inf would turn the products into NaN
+  double hh = 0.5 * r, s = x * r;
+  double e = fma(-hh, s, 0.5);
+  s = fma(s, e, s);
+  e = fma(-s, s, x);
+  return fma(e, hh, s);
+}
+
 // A1-A4 of Appendix A: gather, wall / open BC, star states for face-node slot sl of element k
 __device__ __forceinline__ Trace load_trace(const Sw2dView &v, const double *__restrict__ q, int k, int sl, double t) {
   const long long i = (long long)k * v.Nfn + sl;
@@ -43,17 +66,21 @@ __device__ __forceinline__ Trace load_trace(const Sw2dView &v, const double *__r
     }
     const double bM = -HM, bP = -HP, bmax = fmax(bP, bM);  // main.cpp:359-368
     const double hMs = fmax(0.0, T.hM + bM - bmax), hPs = fmax(0.0, T.hP + bP - bmax);
-    T.huM = hMs * (T.huM / hMs); T.hvM = hMs * (T.hvM / hMs);
-    T.huP = hPs * (T.huP / hPs); T.hvP = hPs * (T.hvP / hPs);
+    // main.cpp:366-368: hu = h* (hu/h) is evaluated AFTER h = h* (SURVEY.md a5), an identity up to one rounding --
+    // except on a dry trace (h* = 0), where 0*(hu/0) is NaN and trips the blow-up guard; four divides saved.
+    const double nan = __longlong_as_double(0x7ff8000000000000LL);
+    if (!(hMs > 0.0)) T.huM = T.hvM = nan;
+    if (!(hPs > 0.0)) T.huP = T.hvP = nan;
     T.hM = hMs; T.hP = hPs;
   }
   return T;
 }
 
 __device__ __forceinline__ double trace_speed(const Trace &T, double g) {  // A7
-  const double uM = T.huM / T.hM, vM = T.hvM / T.hM, uP = T.huP / T.hP, vP = T.hvP / T.hP;
-  const double sM = sqrt(uM * uM + vM * vM) + sqrt(g * T.hM);
-  const double sP = sqrt(uP * uP + vP * vP) + sqrt(g * T.hP);
+  const double rM = frcp(T.hM), rP = frcp(T.hP);
+  const double uM = T.huM * rM, vM = T.hvM * rM, uP = T.huP * rP, vP = T.hvP * rP;
+  const double sM = fsqrt(uM * uM + vM * vM) + fsqrt(g * T.hM);
+  const double sP = fsqrt(uP * uP + vP * vP) + fsqrt(g * T.hP);
   return sM > sP ? sM : sP;
 }
 
@@ -135,16 +162,6 @@ __global__ void k_face(Sw2dView v, const double *__restrict__ q, double *__restr
   }
 }
 
-// 1/x by MUFU seed + two Newton steps (x = 0 gives NaN like the reference's 0/0)
-__device__ __forceinline__ double frcp(double x) {
-  double r;
-  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
-  double e = fma(-x, r, 1.0);
-  r = fma(r, e, r);
-  e = fma(-x, r, 1.0);
-  return fma(r, e, r);
-}
-
 // A5-A8, one thread per face NODE (coalesced trace-map / geometry reads and sflux writes; every trace is loaded
 // once): wave speeds go through shared memory for the per-face maximum (sw2d-simple main.cpp:305-312).
 // EB elements per CTA, thread = e*Nfn + slot.
@@ -163,7 +180,7 @@ __global__ void k_face_nodes(Sw2dView v, const double *__restrict__ q, double *_
     rM = frcp(T.hM);
     rP = frcp(T.hP);
     const double uM = T.huM * rM, vM = T.hvM * rM, uP = T.huP * rP, vP = T.hvP * rP;
-    const double sM = sqrt(uM * uM + vM * vM) + sqrt(g * T.hM), sP = sqrt(uP * uP + vP * vP) + sqrt(g * T.hP);
+    const double sM = fsqrt(uM * uM + vM * vM) + fsqrt(g * T.hM), sP = fsqrt(uP * uP + vP * vP) + fsqrt(g * T.hP);
     sspd[tid] = sM > sP ? sM : sP;
   }
   __syncthreads();

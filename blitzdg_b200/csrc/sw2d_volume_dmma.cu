@@ -96,7 +96,7 @@ __device__ __forceinline__ void stage_epilogue(const Sw2dView &v, const VolArgs 
     const bool ok0 = n < Np && kbase + 2 * t < v.K, ok1 = n < Np && kbase + 2 * t + 1 < v.K;
     const long long m0 = (kbase + 2 * t) * Np + n, m1 = m0 + Np;
     // all loads of the row block first (the stores below may alias them as far as the compiler knows)
-    double qo[2][3], ro[2][3], qd[2][3], hx[2] = {0.0, 0.0}, hy[2] = {0.0, 0.0}, sg[2] = {0.0, 0.0};
+    double qo[2][3], ro[2][3], hx[2] = {0.0, 0.0}, hy[2] = {0.0, 0.0};
 #pragma unroll
     for (int cc = 0; cc < 2; ++cc) {
       const bool ok = cc ? ok1 : ok0;
@@ -105,10 +105,8 @@ __device__ __forceinline__ void stage_epilogue(const Sw2dView &v, const VolArgs 
       for (int i = 0; i < 3; ++i) {
         qo[cc][i] = (ok && (p.mode >= 1 || v.full)) ? q[i * v.stride + m] : 1.0;
         ro[cc][i] = (ok && p.mode == 1 && p.a != 0.0) ? p.res[i * v.stride + m] : 0.0;
-        qd[cc][i] = (ok && p.mode == 3) ? p.qdst[i * v.stride + m] : 0.0;
       }
       if (ok && v.full) { hx[cc] = v.Hx[m]; hy[cc] = v.Hy[m]; }
-      if (ok && p.mode >= 2 && v.sponge) sg[cc] = v.sponge[m];
     }
 #pragma unroll
     for (int cc = 0; cc < 2; ++cc) {
@@ -128,8 +126,14 @@ __device__ __forceinline__ void stage_epilogue(const Sw2dView &v, const VolArgs 
             p.out[(long long)i * Np * v.K + m] = rr[i];
           } else {
             const double sres = fma(p.a, ro[cc][i], dt * rr[i]);  // a = 0 in modes 2, 3
-            if (p.mode == 1) p.res[i * v.stride + m] = sres;
-            p.qdst[i * v.stride + m] = stepper_value(p.mode, p.b, sres, qo[cc][i], qd[cc][i], i, sg[cc]);
+            if (p.mode == 1) {
+              p.res[i * v.stride + m] = sres;
+              p.q[i * v.stride + m] = fma(p.b, sres, qo[cc][i]);
+            } else {  // SSP-RK2 forms: their extra operands are loaded here, not up front (keeps the LSERK4 path's registers)
+              const double qold = p.mode == 3 ? p.qdst[i * v.stride + m] : 0.0;
+              const double sig = (i > 0 && v.sponge) ? __ldg(v.sponge + m) : 0.0;
+              p.qdst[i * v.stride + m] = stepper_value(p.mode, p.b, sres, qo[cc][i], qold, i, sig);
+            }
           }
         }
       }
