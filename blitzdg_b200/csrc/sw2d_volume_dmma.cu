@@ -141,8 +141,11 @@ __device__ __forceinline__ void stage_epilogue(const Sw2dView &v, const VolArgs 
   }
 }
 
+#ifndef BDG_VOL_MINB_SMALL
+#define BDG_VOL_MINB_SMALL 5  // N <= 4 affine: 96 registers, 5 CTAs/SM measured +1 % over 3 (tools/vol_occupancy_sweep.sh)
+#endif
 template <int MB, bool AFFINE>
-__global__ void __launch_bounds__(kVW * 32, 3) k_volume_dmma(Sw2dView v, VolArgs p) {
+__global__ void __launch_bounds__(kVW * 32, (MB <= 2 && AFFINE) ? BDG_VOL_MINB_SMALL : 3) k_volume_dmma(Sw2dView v, VolArgs p) {
   extern __shared__ __align__(16) double sA[];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int c = lane >> 2, t = lane & 3, gr = lane >> 2;
