@@ -44,6 +44,8 @@ def parse():
                     help="ssprk2 = the src/sw2d driver loop (SURVEY.md 8f rank 1): with --mode full the top edge becomes an open "
                          "boundary with tide, sloping 150-200 m bathymetry and a sponge behind the open boundary")
     ap.add_argument("--block", default="", help="element order: '' = cell-major, 'BXxBY' = blocks of BX x BY cells (locality study)")
+    ap.add_argument("--shuffle", type=int, default=None, help="seed: random element / vertex numbering (unstructured-numbering study)")
+    ap.add_argument("--jitter", type=float, default=0.0, help="interior vertex jitter in cell widths")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -115,7 +117,7 @@ def build_problem(args, rank, world):
     from blitzdg_b200.synthetic import provision, structured_mesh
 
     block = tuple(int(x) for x in args.block.split("x")) if args.block else None
-    mesh = structured_mesh(args.shape, args.nx, args.ny * world, block=block)
+    mesh = structured_mesh(args.shape, args.nx, args.ny * world, jitter=args.jitter, block=block, shuffle=args.shuffle)
     if world == 1:
         ctx = provision(mesh, args.order).get_DGContext()
         halo = None

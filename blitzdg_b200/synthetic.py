@@ -54,8 +54,24 @@ def structured_arrays(shape, nx, ny, jitter=0.0, x0=-1.0, x1=1.0, y0=-1.0, y1=1.
     return etov, vert
 
 
-def structured_mesh(shape, nx, ny, jitter=0.0, block=None):
+def shuffle_numbering(etov, vert, seed):
+    """Random element order, vertex numbering and starting vertex per element (orientation kept): what an unstructured
+    mesh generator's output looks like to the setup code and to the device element order."""
+    rng = np.random.default_rng(seed)
+    K, Nf = etov.shape
+    vperm = rng.permutation(len(vert))  # new id of old vertex
+    inv = np.empty_like(vperm)
+    inv[vperm] = np.arange(len(vert))
+    etov = vperm[etov]
+    rot = rng.integers(0, Nf, K)
+    etov = np.take_along_axis(etov, (np.arange(Nf)[None, :] + rot[:, None]) % Nf, axis=1)
+    return np.ascontiguousarray(etov[rng.permutation(K)]), np.ascontiguousarray(vert[inv])
+
+
+def structured_mesh(shape, nx, ny, jitter=0.0, block=None, shuffle=None):
     etov, vert = structured_arrays(shape, nx, ny, jitter, block=block)
+    if shuffle is not None:
+        etov, vert = shuffle_numbering(etov, vert, shuffle)
     m = MeshManager()
     m.buildMesh(etov, vert)
     return m

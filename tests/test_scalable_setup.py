@@ -6,27 +6,13 @@ import time
 import numpy as np
 import pytest
 
-from blitzdg_b200 import MeshManager
-from blitzdg_b200.synthetic import provision, structured_arrays
+from blitzdg_b200.synthetic import provision, structured_mesh
 
 
 def shuffled_mesh(shape, nx, ny, jitter, seed):
-    """Structured cells with jittered interior vertices, then elements, vertices and each element's starting
-    vertex permuted at random (orientation kept): nothing of the generator's regularity is left in the numbering."""
-    etov, vert = structured_arrays(shape, nx, ny, jitter)
-    rng = np.random.default_rng(seed)
-    K, Nf = etov.shape
-    vperm = rng.permutation(len(vert))  # new id of old vertex
-    inv = np.empty_like(vperm)
-    inv[vperm] = np.arange(len(vert))
-    etov = vperm[etov]
-    vert = vert[inv]
-    rot = rng.integers(0, Nf, K)
-    etov = np.take_along_axis(etov, (np.arange(Nf)[None, :] + rot[:, None]) % Nf, axis=1)
-    etov = etov[rng.permutation(K)]
-    m = MeshManager()
-    m.buildMesh(np.ascontiguousarray(etov), np.ascontiguousarray(vert))
-    return m
+    """Structured cells with jittered interior vertices and a random numbering (synthetic.shuffle_numbering): nothing
+    of the generator's regularity is left."""
+    return structured_mesh(shape, nx, ny, jitter, shuffle=seed)
 
 
 @pytest.mark.parametrize("shape,N,nx,ny", [("tri", 3, 9, 7), ("quad", 2, 8, 5)])
