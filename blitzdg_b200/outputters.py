@@ -147,12 +147,63 @@ class DeviceOutput:
         self._pin = [[torch.empty((self.n_out, K), dtype=torch.float64).pin_memory() for _ in range(3)] for _ in range(2)]
         self._cur = 0
         self._pending = None
+        self._writer = None
 
     def begin(self, tstep):
+        if self._writer is not None:
+            self._busy[self._cur].wait()  # the writer thread has finished with the buffer set about to be reused
         bufs = [t.numpy() for t in self._pin[self._cur]]
         self.sol.output_begin(*bufs)
         self._pending = (tstep, bufs)
+        if self._writer is not None:
+            self._busy[self._cur].clear()
+            self._queue.put((self._cur, tstep, bufs))
         self._cur ^= 1
+
+    # ---- optional writer thread: files are written while the time loop keeps running -------------------------------
+    def start_writer(self):
+        """After this, every begin() is followed -- on a background thread -- by the wait for its copies and the file
+        writes; the caller only steps and calls begin().  finish() drains the queue and returns the file names."""
+        import queue
+        import threading
+
+        self._queue = queue.Queue()
+        self._busy = [threading.Event(), threading.Event()]
+        for e in self._busy:
+            e.set()
+        self.written, self.writer_error = [], None
+
+        def run():
+            while True:
+                item = self._queue.get()
+                if item is None:
+                    return
+                slot, tstep, bufs = item
+                try:
+                    # waits for the copies of the LATEST begin(); copies complete in stream order, so this snapshot's
+                    # have arrived too.  output_wait only synchronises on an event: safe beside the stepping thread.
+                    self.sol.output_wait()
+                    for name, a in zip(("eta", "u", "v"), bufs):
+                        fn = os.path.join(self.directory, "%s%07d.vtu" % (name, int(tstep)))
+                        write_vtu(fn, self.x, self.y, self._corners(a), name, self.fmt)
+                        self.written.append(fn)
+                except Exception as exc:  # surfaced by finish()
+                    self.writer_error = exc
+                finally:
+                    self._busy[slot].set()
+
+        self._writer = threading.Thread(target=run, daemon=True)
+        self._writer.start()
+
+    def finish(self):
+        if self._writer is None:
+            return []
+        self._queue.put(None)
+        self._writer.join()
+        self._writer = None
+        if self.writer_error is not None:
+            raise self.writer_error
+        return self.written
 
     def fields(self):
         """Waits for the snapshot of the last begin(); returns tstep, {"eta","u","v"} as [n_out][K] interpolated arrays."""

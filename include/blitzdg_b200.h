@@ -145,7 +145,8 @@ int bdg_sw2d_limit_positivity(bdg_sw2d *s);
  * output_begin: enqueues the derivation + the three interpolations of the live state and the copies of the results
  * into eta, u, v (host, [n_out][K] row-major, any may be NULL; pinned memory keeps the copies asynchronous) on a side
  * stream: later bdg_sw2d_step calls only wait for the interpolation kernel, not for the copies.
- * output_wait: blocks until the host arrays of the last output_begin are complete. */
+ * output_wait: blocks until the host arrays of the last output_begin are complete; it only waits on an event and may
+ * be called from a second (writer) thread while the owning thread keeps stepping. */
 int bdg_sw2d_set_output(bdg_sw2d *s, const double *interp, int32_t n_out);
 int bdg_sw2d_output_begin(bdg_sw2d *s, double *eta, double *u, double *v);
 int bdg_sw2d_output_wait(bdg_sw2d *s);
