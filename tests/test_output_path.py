@@ -113,7 +113,6 @@ def test_device_output_matches_host_path(tmp_path, shape, N, nx, ny, jit, bathy)
     sol.step(5, dt, sync=False)
     dev.begin(5)            # snapshot after 5 steps ...
     sol.step(5, dt, sync=False)   # ... while the next interval is already running
-    s5 = None
     t, flds = dev.fields()
     snap = {k: v.copy() for k, v in flds.items()}
     names = dev.write()
