@@ -45,3 +45,24 @@ def test_struct_layout_matches_c():
     assert ctypes.sizeof(capi.bdg_sw2d_params) == 4 * 8 + 4 * 4 + 3 * 8
     assert ctypes.sizeof(capi.bdg_dgcontext2d) == 24 + 13 * 8 + 9 * 8 + 9 * 4 + 4
     assert ctypes.sizeof(capi.bdg_halo) == 16 + 4 * 8 + 8
+
+
+def test_null_handle_is_rejected_by_every_entry_point():
+    """The reference-facing calls validate their handle before touching CUDA (BDG_E_INVALID, no crash, no GPU needed)."""
+    lib = capi.load()
+    nul = ctypes.c_void_p()
+    dp = ctypes.POINTER(ctypes.c_double)()
+    calls = {
+        "bdg_sw2d_set_bathymetry": (nul, dp, dp, dp), "bdg_sw2d_set_state": (nul, dp, dp, dp, 0.0),
+        "bdg_sw2d_get_state": (nul, dp, dp, dp, dp), "bdg_sw2d_rhs": (nul, dp, dp, dp), "bdg_sw2d_timestep": (nul, dp),
+        "bdg_sw2d_step": (nul, 1, 0.1), "bdg_sw2d_step_ssprk2": (nul, 1, 0.1), "bdg_sw2d_sync": (nul,), "bdg_sw2d_check": (nul, dp),
+        "bdg_sw2d_set_sponge": (nul, dp), "bdg_sw2d_set_output": (nul, dp, 3), "bdg_sw2d_output_begin": (nul, dp, dp, dp),
+        "bdg_sw2d_output_wait": (nul,), "bdg_sw2d_limit_positivity": (nul,), "bdg_sw2d_stage_state": (nul, dp, dp, dp, 0.0),
+        "bdg_sw2d_commit_state": (nul,), "bdg_sw2d_get_state_async": (nul, dp, dp, dp), "bdg_sw2d_get_state_wait": (nul,),
+        "bdg_sw2d_set_variant": (nul, 1), "bdg_sw2d_comm_init": (nul, nul), "bdg_sw2d_halo_pack_to_host": (nul, dp),
+        "bdg_sw2d_halo_set_ghosts": (nul, dp),
+    }
+    for name, args in calls.items():
+        assert getattr(lib, name)(*args) == capi.BDG_E_INVALID, name
+    assert lib.bdg_sw2d_launch_count(nul) == 0 and lib.bdg_sw2d_get_variant(nul) == -1
+    lib.bdg_sw2d_destroy(nul)  # no-op
