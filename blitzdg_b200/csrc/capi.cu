@@ -139,7 +139,7 @@ int dev_upload(bdg_sw2d *s, T **p, const T *host, size_t n) {
 }  // namespace
 
 // ====================================================================================== lifetime
-extern "C" int bdg_version(void) { return 101; }
+extern "C" int bdg_version(void) { return 102; }
 
 extern "C" int bdg_element_order(const int32_t *vmapP, int32_t Np, int32_t Nfp, int32_t Nfaces, int32_t K, int32_t n_interior,
                                  int32_t *perm_out) {
