@@ -65,7 +65,7 @@ class ClockSampler:
     """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
 
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,enforced.power.limit")
 
     def __init__(self, gpu):
         self.gpu = gpu
@@ -89,20 +89,25 @@ class ClockSampler:
         self.f.flush()
         rows = [r.strip().split(", ") for r in open(self.f.name) if r.strip()]
         os.unlink(self.f.name)
-        sm, mx, reasons, pw = [], None, set(), []
+        sm, mx, reasons, pw, plim = [], None, set(), [], None
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in rows:
             try:
                 sm.append(float(r[1]))
                 mx = float(r[2])
-                pw.append(float(r[3]))
                 for nm, val in zip(names, r[4:8]):
                     if val.strip().lower().startswith("active"):
                         reasons.add(nm)
             except Exception:
                 continue
+            try:  # board power is informative only: never let it cost the clocks line
+                pw.append(float(r[3]))
+                plim = float(r[8])
+            except Exception:
+                pass
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm),
-                "power_w": float(np.median(pw)) if pw else None}
+                "power_w": float(np.median(pw)) if pw else None, "power_max_w": float(np.max(pw)) if pw else None,
+                "power_limit_w": plim}
 
 
 def dist_env():
