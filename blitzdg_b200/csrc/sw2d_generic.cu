@@ -41,6 +41,8 @@ __device__ __forceinline__ double fsqrt(double x) {
 }
 
 // A1-A4 of Appendix A: gather, wall / open BC, star states for face-node slot sl of element k
+// NEED_N = false (speed-only callers): the normal is fetched for wall nodes only, 16 B per face node less.
+template <bool NEED_N = true>
 __device__ __forceinline__ Trace load_trace(const Sw2dView &v, const double *__restrict__ q, int k, int sl, double t) {
   const long long i = (long long)k * v.Nfn + sl;
   const long long mM = (long long)k * v.Np + v.fmask[sl];
@@ -49,8 +51,8 @@ __device__ __forceinline__ Trace load_trace(const Sw2dView &v, const double *__r
   Trace T;
   T.hM = h[mM]; T.huM = hu[mM]; T.hvM = hv[mM];
   T.hP = h[mP]; T.huP = hu[mP]; T.hvP = hv[mP];
-  T.nx = v.nx[i]; T.ny = v.ny[i];
   const int tag = v.bctag[i];
+  if (NEED_N || tag == 3) { T.nx = v.nx[i]; T.ny = v.ny[i]; } else { T.nx = T.ny = 0.0; }
   if (tag == 3) {  // Wall: reflect the normal momentum (main.cpp:340-345)
     if (v.full) T.hP = T.hM;
     const double d = T.huM * T.nx + T.hvM * T.ny;
@@ -114,9 +116,29 @@ __global__ void k_speed(Sw2dView v, const double *__restrict__ q, int slot) {
   const long long nF = (long long)v.Nfn * v.K;
   const double t = v.scal[S_T];
   double m = 0.0;
+#pragma unroll 4  // independent iterations: four dependent gather chains (vmapP -> H, fmask -> q) in flight per thread
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nF; i += (long long)gridDim.x * blockDim.x) {
-    Trace T = load_trace(v, q, (int)(i / v.Nfn), (int)(i % v.Nfn), t);
-    double s = trace_speed(T, v.g);
+    // The '+' side of an interior face node is the '-' side of the neighbour's (same pair of values, same star states),
+    // which that neighbour's thread -- or the neighbour rank, before the all-reduce -- evaluates: only BC faces need
+    // both sides here.  Halves the gathers and the sqrt/reciprocal work of this launch.
+    const unsigned iu = (unsigned)i;  // Nfn*K < 2^31: 32-bit division, not the 64-bit software routine
+    const int k = (int)(iu / (unsigned)v.Nfn), sl = (int)(iu - (unsigned)k * (unsigned)v.Nfn);
+    double s;
+    if (v.bctag[i] != 0) {
+      Trace T = load_trace<false>(v, q, k, sl, t);
+      s = trace_speed(T, v.g);
+    } else {
+      const long long mM = (long long)k * v.Np + v.fmask[sl];
+      double hM = q[mM];
+      double huM = q[v.stride + mM], hvM = q[2 * v.stride + mM];
+      if (v.full) {  // star state of the '-' side (main.cpp:359-368), as in load_trace
+        const double bM = -v.H[mM], bP = -v.H[v.vmapP[i]];
+        hM = fmax(0.0, hM + bM - fmax(bP, bM));
+        if (!(hM > 0.0)) huM = hvM = __longlong_as_double(0x7ff8000000000000LL);
+      }
+      const double r = frcp(hM), uM = huM * r, vM = hvM * r;
+      s = fsqrt(uM * uM + vM * vM) + fsqrt(v.g * hM);
+    }
     m = (__double_as_longlong(s) > __double_as_longlong(m)) ? s : m;
   }
   m = block_max(m);

@@ -86,7 +86,9 @@ __device__ __forceinline__ void finish_node(const Sw2dView &v, const VolArgs &p,
 
 // Epilogue in the C-fragment layout (row n = 8*rb + lane/4, columns = elements kbase + 2*(lane%4) + {0,1}):
 // acc = RHS_i without sources -> sources (full mode, A11) -> out (mode 0) / LSERK4 stage update in place (mode 1).
-template <int MB>
+// RK2 instances (modes 2, 3) also batch the destination's old values and the sponge; they are separate kernel
+// instantiations so that the LSERK4 instances keep their register budget.
+template <int MB, bool RK2>
 __device__ __forceinline__ void stage_epilogue(const Sw2dView &v, const VolArgs &p, double (&acc)[3][MB][2], long long kbase, int lane, double dt) {
   const int gr = lane >> 2, t = lane & 3, Np = v.Np;
   const double *q = p.q;
@@ -97,6 +99,7 @@ __device__ __forceinline__ void stage_epilogue(const Sw2dView &v, const VolArgs 
     const long long m0 = (kbase + 2 * t) * Np + n, m1 = m0 + Np;
     // all loads of the row block first (the stores below may alias them as far as the compiler knows)
     double qo[2][3], ro[2][3], hx[2] = {0.0, 0.0}, hy[2] = {0.0, 0.0};
+    double qd[RK2 ? 2 : 1][3], sg[2] = {0.0, 0.0};
 #pragma unroll
     for (int cc = 0; cc < 2; ++cc) {
       const bool ok = cc ? ok1 : ok0;
@@ -104,9 +107,11 @@ __device__ __forceinline__ void stage_epilogue(const Sw2dView &v, const VolArgs 
 #pragma unroll
       for (int i = 0; i < 3; ++i) {
         qo[cc][i] = (ok && (p.mode >= 1 || v.full)) ? q[i * v.stride + m] : 1.0;
-        ro[cc][i] = (ok && p.mode == 1 && p.a != 0.0) ? p.res[i * v.stride + m] : 0.0;
+        ro[cc][i] = (!RK2 && ok && p.mode == 1 && p.a != 0.0) ? p.res[i * v.stride + m] : 0.0;
+        if (RK2) qd[cc][i] = (ok && p.mode == 3) ? p.qdst[i * v.stride + m] : 0.0;
       }
       if (ok && v.full) { hx[cc] = v.Hx[m]; hy[cc] = v.Hy[m]; }
+      if (RK2 && ok && v.sponge) sg[cc] = __ldg(v.sponge + m);
     }
 #pragma unroll
     for (int cc = 0; cc < 2; ++cc) {
@@ -126,13 +131,11 @@ __device__ __forceinline__ void stage_epilogue(const Sw2dView &v, const VolArgs 
             p.out[(long long)i * Np * v.K + m] = rr[i];
           } else {
             const double sres = fma(p.a, ro[cc][i], dt * rr[i]);  // a = 0 in modes 2, 3
-            if (p.mode == 1) {
+            if (!RK2) {
               p.res[i * v.stride + m] = sres;
               p.q[i * v.stride + m] = fma(p.b, sres, qo[cc][i]);
-            } else {  // SSP-RK2 forms: their extra operands are loaded here, not up front (keeps the LSERK4 path's registers)
-              const double qold = p.mode == 3 ? p.qdst[i * v.stride + m] : 0.0;
-              const double sig = (i > 0 && v.sponge) ? __ldg(v.sponge + m) : 0.0;
-              p.qdst[i * v.stride + m] = stepper_value(p.mode, p.b, sres, qo[cc][i], qold, i, sig);
+            } else {  // SSP-RK2 forms (stepper_value, sw2d_common.cuh)
+              p.qdst[i * v.stride + m] = stepper_value(p.mode, p.b, sres, qo[cc][i], qd[RK2 ? cc : 0][i], i, sg[cc]);
             }
           }
         }
@@ -144,7 +147,7 @@ __device__ __forceinline__ void stage_epilogue(const Sw2dView &v, const VolArgs 
 #ifndef BDG_VOL_MINB_SMALL
 #define BDG_VOL_MINB_SMALL 5  // N <= 4 affine: 96 registers, 5 CTAs/SM measured +1 % over 3 (tools/vol_occupancy_sweep.sh)
 #endif
-template <int MB, bool AFFINE>
+template <int MB, bool AFFINE, bool RK2>
 __global__ void __launch_bounds__(kVW * 32, (MB <= 2 && AFFINE) ? BDG_VOL_MINB_SMALL : 3) k_volume_dmma(Sw2dView v, VolArgs p) {
   extern __shared__ __align__(16) double sA[];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -202,7 +205,7 @@ __global__ void __launch_bounds__(kVW * 32, (MB <= 2 && AFFINE) ? BDG_VOL_MINB_S
         }
       }
       __syncwarp();  // every lane's state loads of these 8 elements precede the in-place update
-      stage_epilogue<MB>(v, p, acc, kbase, lane, dt);
+      stage_epilogue<MB, RK2>(v, p, acc, kbase, lane, dt);
     } else {
       // per-node metrics: one field at a time; C = {Dr X, Ds X, Dr Y, Ds Y, LIFT s} with X,Y = (F_i, G_i)
 #pragma unroll 1
@@ -282,7 +285,7 @@ __global__ void __launch_bounds__(kVW * 32, (MB <= 2 && AFFINE) ? BDG_VOL_MINB_S
 // same register serves both.  The warp stages an element's nodal fluxes in shared memory (every flux evaluated once),
 // combines the four products with the nodal rx, sx, ry, sy, parks the volume RHS of its 8 elements in shared memory
 // and then runs the dense LIFT contraction across the 8 elements (columns = elements) from there.
-template <int MB>
+template <int MB, bool RK2>
 __global__ void __launch_bounds__(kVW * 32, 3) k_volume_quad_sf(Sw2dView v, VolArgs p) {
   extern __shared__ __align__(16) double sm[];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -374,17 +377,18 @@ __global__ void __launch_bounds__(kVW * 32, 3) k_volume_quad_sf(Sw2dView v, VolA
       }
     }
     __syncwarp();
-    stage_epilogue<MB>(v, p, acc, kbase, lane, dt);
+    stage_epilogue<MB, RK2>(v, p, acc, kbase, lane, dt);
     __syncwarp();
   }
 }
 
 template <int MB>
 cudaError_t launch_mb(bdg_sw2d *s, const VolArgs &a, size_t smem) {
-  static int ctas[16][2] = {};
-  static size_t smem_set[16][2] = {};
-  const int dev = s->device & 15, aff = s->is_affine ? 1 : 0;
-  auto kern = aff ? k_volume_dmma<MB, true> : k_volume_dmma<MB, false>;
+  static int ctas[16][4] = {};
+  static size_t smem_set[16][4] = {};
+  const int dev = s->device & 15, aff = (s->is_affine ? 1 : 0) + (a.mode >= 2 ? 2 : 0);
+  auto kern = a.mode >= 2 ? (s->is_affine ? k_volume_dmma<MB, true, true> : k_volume_dmma<MB, false, true>)
+                          : (s->is_affine ? k_volume_dmma<MB, true, false> : k_volume_dmma<MB, false, false>);
   if (smem != smem_set[dev][aff]) {  // one instance serves every order with this row-block count: the operator size varies
     cudaError_t e;
     if ((e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
@@ -404,23 +408,24 @@ cudaError_t launch_mb(bdg_sw2d *s, const VolArgs &a, size_t smem) {
 
 template <int MB>
 cudaError_t launch_quad(bdg_sw2d *s, const VolArgs &a) {
-  static int ctas[16] = {};
-  static size_t smem_set[16] = {};
-  const int dev = s->device & 15;
+  static int ctas[16][2] = {};
+  static size_t smem_set[16][2] = {};
+  const int dev = s->device & 15, rk = a.mode >= 2 ? 1 : 0;
+  auto kern = rk ? k_volume_quad_sf<MB, true> : k_volume_quad_sf<MB, false>;
   const size_t smem = sizeof(double) * ((size_t)MB * a.NFB * 32 + (size_t)kVW * (5 * 64 + 3 * 8 * MB * 8));
-  if (smem != smem_set[dev]) {
+  if (smem != smem_set[dev][rk]) {
     cudaError_t e;
-    if ((e = cudaFuncSetAttribute(k_volume_quad_sf<MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas[dev], k_volume_quad_sf<MB>, kVW * 32, smem)) != cudaSuccess) return e;
-    if (ctas[dev] < 1) return cudaErrorLaunchOutOfResources;
-    smem_set[dev] = smem;
+    if ((e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas[dev][rk], kern, kVW * 32, smem)) != cudaSuccess) return e;
+    if (ctas[dev][rk] < 1) return cudaErrorLaunchOutOfResources;
+    smem_set[dev][rk] = smem;
   }
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device);
-  int grid = sms * ctas[dev];
+  int grid = sms * ctas[dev][rk];
   const int need = (a.ngroups + kVW - 1) / kVW;
   if (grid > need) grid = need;
-  k_volume_quad_sf<MB><<<grid, kVW * 32, smem, s->stream>>>(s->v, a);
+  kern<<<grid, kVW * 32, smem, s->stream>>>(s->v, a);
   s->launches++;
   return cudaGetLastError();
 }
