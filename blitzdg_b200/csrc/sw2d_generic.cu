@@ -116,7 +116,7 @@ __global__ void k_speed(Sw2dView v, const double *__restrict__ q, int slot) {
   const long long nF = (long long)v.Nfn * v.K;
   const double t = v.scal[S_T];
   double m = 0.0;
-#pragma unroll 4  // independent iterations: four dependent gather chains (vmapP -> H, fmask -> q) in flight per thread
+  // (unrolling this loop for more gathers in flight costs occupancy and was slower: 236 vs 186 us)
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nF; i += (long long)gridDim.x * blockDim.x) {
     // The '+' side of an interior face node is the '-' side of the neighbour's (same pair of values, same star states),
     // which that neighbour's thread -- or the neighbour rank, before the all-reduce -- evaluates: only BC faces need
