@@ -5,12 +5,17 @@
  * non-FMA dot products).  It is the parity checker for tests/, __graft_entry__.smoke() and the
  * cpu_baseline / --impl reference legs of bench.py; the product path never links or calls it.
  *
- * PARITY PINNING: the reference's own specs hold no golden vector for computeRHS or any
- * time step ("parity unpinned" for the RHS); what they do pin -- every input
- * array of the path and the fullToVector/applyIndexMap semantics -- is checked in
- * tests/test_setup_golden.py and tests/test_oracle.py.  The RHS restatement is pinned by
- * transcription + an independent NumPy transcription of the reference's Python drivers
- * (oracle/sw2d_numpy.py) + the self-checks of SURVEY.md §8c.
+ * PARITY PINNING: the reference's C++ specs hold no golden vector for computeRHS or any time
+ * step; what they do pin -- every input array of the path and the
+ * fullToVector/applyIndexMap semantics -- is checked in tests/test_setup_golden.py and
+ * tests/test_oracle.py.  The RHS itself is pinned against outputs of the reference's own
+ * Python RHS functions run in the build container (sw2dquads.py:10-123, swhelpers/rhs.py:178-311,
+ * swhelpers/limiters.py:3-21 executed unmodified by tests/golden/make_python_reference_vectors.py;
+ * fixture tests/golden/python_reference_rhs.npz; tests/test_python_reference_golden.py):
+ * per-face LF, wall BC, Coriolis/drag/bed-slope sources, tri N=4,7 and quad N=3,6, to 1e-12.
+ * The lines only the C++ src/sw2d driver has (global LF maximum, star states, Out BC with tide,
+ * SSP-RK2 + sponge) have no runnable reference here and stay pinned by transcription, the second
+ * NumPy derivation (oracle/sw2d_numpy.py) and the self-checks of SURVEY.md §8c.
  *
  * Followed sources (reference = WQCG/blitzdg @ d61b584):
  *   full RHS     src/sw2d/main.cpp:279-484        dt   src/sw2d/main.cpp:253-277
