@@ -94,6 +94,31 @@ def main():
         for nm, a in zip(("h", "hu", "hv", "RHS1", "RHS2", "RHS3"), (h, hu, hv) + tuple(R)):
             out["sw2dquads_%s_%s" % (tag, nm)] = np.ascontiguousarray(a)
 
+    # 1000 LSERK4 steps driven by the reference's RHS function: stage idiom of /root/reference/advec1d.py:80-88
+    # (`resRK = rk4a[stg]*resRK + dt*RHS; u += rk4b[stg]*resRK`), coefficients of include/LSERK4.hpp:17-27 (host mirror,
+    # pinned in tests/test_oracle.py), each of h, hu, hv updated like advec1d's u; fixed dt = 2e-3 (CFL dt here ~3.7e-3).
+    from blitzdg_b200 import LSERK4
+
+    for tag, msh, quad, N in (("tri4", "coarse_box.msh", False, 4), ("quad3", "coarse_box_quads.msh", True, 3)):
+        mm = MeshManager()
+        mm.readMesh(os.path.join(HERE, msh))
+        ctx = (QuadNodesProvisioner if quad else TriangleNodesProvisioner)(N, mm).get_DGContext()
+        view = py_view(ctx)
+        H = np.full_like(ctx.x, 10.0)
+        q = [a.copy() for a in state(ctx, H)]
+        res = [np.zeros_like(a) for a in q]
+        dt = 2e-3
+        for _ in range(1000):
+            for stg in range(5):
+                R = quads_rhs(q[0], q[1], q[2], g, H, view)
+                for c in range(3):
+                    res[c] = LSERK4.rk4a[stg] * res[c] + dt * R[c]
+                    q[c] += LSERK4.rk4b[stg] * res[c]
+        out["lserk4_1000_%s_dt" % tag] = np.array(dt)
+        for nm, a in zip(("h", "hu", "hv"), q):
+            assert np.isfinite(a).all()
+            out["lserk4_1000_%s_%s" % (tag, nm)] = np.ascontiguousarray(a)
+
     # swhelpers/rhs.py on triangles with a sloping bed; z = -H so zx = -Hx.
     mm = MeshManager()
     mm.readMesh(os.path.join(HERE, "coarse_box.msh"))

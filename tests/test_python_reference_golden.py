@@ -16,6 +16,8 @@ from blitzdg_b200 import MeshManager, QuadNodesProvisioner, TriangleNodesProvisi
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 RHS_TOL = 1e-12
+STEP_TOL = 1e-10  # BASELINE.json: after 1000 LSERK4 steps
+STEP_CASES = [("tri4", "coarse_box.msh", False, 4), ("quad3", "coarse_box_quads.msh", True, 3)]
 G = 9.81
 F_COR = 1.0070e-4
 CASES = [("tri4", "coarse_box.msh", False, 4), ("tri7", "coarse_box.msh", False, 7),
@@ -92,6 +94,17 @@ def test_oracle_matches_swhelpers_rhs_with_sources(ref, tag, CD):
         assert relerr(R[c], want[c]) < RHS_TOL, c
 
 
+@pytest.mark.parametrize("tag,msh,quad,N", STEP_CASES)
+def test_oracle_matches_1000_lserk4_steps_of_reference_rhs(ref, tag, msh, quad, N):
+    """The fixture's loop is advec1d.py:80-88's stage idiom around the reference's sw2dquads RHS function."""
+    ctx = _ctx(msh, quad, N)
+    h, hu, hv = (ref["sw2dquads_%s_%s" % (tag, n)].copy() for n in ("h", "hu", "hv"))
+    res = [np.zeros_like(h) for _ in range(3)]
+    _oracle(ctx, lf_mode=0, sources=0).step(h, hu, hv, res, 1000, float(ref["lserk4_1000_%s_dt" % tag]))
+    for a, n in zip((h, hu, hv), ("h", "hu", "hv")):
+        assert relerr(a, ref["lserk4_1000_%s_%s" % (tag, n)]) < STEP_TOL, n
+
+
 def test_limiter_restatement_matches_reference_function(ref):
     from oracle.output_numpy import positivity_limiter
 
@@ -119,6 +132,28 @@ def test_cuda_matches_sw2dquads_rhs(ref, tag, msh, quad, N):
         R = sol.computeRHS()
         for c in range(3):
             assert relerr(R[c], ref["sw2dquads_%s_RHS%d" % (tag, c + 1)]) < RHS_TOL, (var, c)
+    sol.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag,msh,quad,N", STEP_CASES)
+def test_cuda_matches_1000_lserk4_steps_of_reference_rhs(ref, tag, msh, quad, N):
+    ctx = _ctx(msh, quad, N)
+    h, hu, hv = (ref["sw2dquads_%s_%s" % (tag, n)] for n in ("h", "hu", "hv"))
+    sol = _solver(ctx)
+    variants = [1]
+    try:
+        sol.set_variant(2)
+        variants.append(2)
+    except RuntimeError:
+        pass
+    for var in variants:
+        sol.set_variant(var)
+        sol.set_state(h, hu, hv)
+        sol.step(1000, float(ref["lserk4_1000_%s_dt" % tag]))
+        out = sol.get_state()
+        for a, n in zip(out[:3], ("h", "hu", "hv")):
+            assert relerr(a, ref["lserk4_1000_%s_%s" % (tag, n)]) < STEP_TOL, (var, n)
     sol.close()
 
 
