@@ -127,9 +127,11 @@ def main():
     Hx, Hy = np.full_like(H, 0.5), np.full_like(H, 0.25)
     h, hu, hv = state(ctx, H)
     f = 1.0070e-4
+    hN = h * (0.5 + 0.1 * np.sin(2 * ctx.x + ctx.y))  # tracer of the 4th equation (RHS1-3 do not see it)
+    out["swhelpers_hN"] = np.ascontiguousarray(hN)
     for tag, CD in (("cd0", 0.0), ("cd", 2.5e-3)):
-        R = helpers_rhs(h, hu, hv, h.copy(), -Hx, -Hy, g, H, f, CD, py_view(ctx), ctx.vmapM, ctx.vmapP)
-        for nm, a in zip(("RHS1", "RHS2", "RHS3"), R[:3]):
+        R = helpers_rhs(h, hu, hv, hN, -Hx, -Hy, g, H, f, CD, py_view(ctx), ctx.vmapM, ctx.vmapP)
+        for nm, a in zip(("RHS1", "RHS2", "RHS3", "RHS4"), R):
             out["swhelpers_%s_%s" % (tag, nm)] = np.ascontiguousarray(a)
     for nm, a in zip(("h", "hu", "hv", "H"), (h, hu, hv, H)):
         out["swhelpers_" + nm] = np.ascontiguousarray(a)
