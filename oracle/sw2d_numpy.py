@@ -20,7 +20,9 @@ def fluxes(h, hu, hv, g):
 
 def compute_rhs(ctx, h, hu, hv, g=9.81, lf_mode=0, sources=False, H=None, Hx=None, Hy=None,
                 CD=2.5e-3, f=1.0070e-4, t=0.0, tide_amp=3.0, tide_period=3600 * 12.42, tide_ramp=0.15 / 3600,
-                use_filter=False):
+                use_filter=False, hN=None):
+    """hN: optional tracer of the Python drivers' 4th equation (swhelpers/flux.py:18-20, swhelpers/rhs.py:206-296):
+    F4 = hN*u, G4 = hN*v, same LF speed; a fourth array is then returned."""
     Nfp, Nf, K = ctx.Nfp, ctx.Nfaces, ctx.K
     vM, vP = ctx.vmapM, ctx.vmapP
     flat = lambda a: a.flatten("F")
@@ -64,8 +66,16 @@ def compute_rhs(ctx, h, hu, hv, g=9.81, lf_mode=0, sources=False, H=None, Hx=Non
     dF = [0.5 * ((F1M - F1P) * nx + (G1M - G1P) * ny - lam * dh),
           0.5 * ((F2M - F2P) * nx + (G2M - G2P) * ny - lam * dhu),
           0.5 * ((F3M - F3P) * nx + (G3M - G3P) * ny - lam * dhv)]
+    Fs, Gs = [F1, F2, F3], [G1, G2, G3]
+    if hN is not None:
+        hNM, hNP = flat(hN)[vM], flat(hN)[vP]
+        F4M, G4M = hNM * (huM / hM), hNM * (hvM / hM)
+        F4P, G4P = hNP * (huP / hP), hNP * (hvP / hP)
+        dF.append(0.5 * ((F4M - F4P) * nx + (G4M - G4P) * ny - lam * (hNM - hNP)))
+        Fs.append(hN * (hu / h))
+        Gs.append(hN * (hv / h))
     out = []
-    for Fc, Gc, dFc in zip((F1, F2, F3), (G1, G2, G3), dF):
+    for Fc, Gc, dFc in zip(Fs, Gs, dF):
         R = -(ctx.rx * (ctx.Dr @ Fc) + ctx.sx * (ctx.Ds @ Fc))
         R += -(ctx.ry * (ctx.Dr @ Gc) + ctx.sy * (ctx.Ds @ Gc))
         R += ctx.Lift @ (ctx.Fscale * dFc.reshape((Nfp * Nf, K), order="F"))

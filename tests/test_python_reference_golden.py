@@ -105,6 +105,20 @@ def test_oracle_matches_1000_lserk4_steps_of_reference_rhs(ref, tag, msh, quad, 
         assert relerr(a, ref["lserk4_1000_%s_%s" % (tag, n)]) < STEP_TOL, n
 
 
+def test_numpy_transcription_matches_tracer_equation(ref):
+    """4th (tracer) equation of swhelpers/rhs.py -- SURVEY.md §8f rank 4; no kernel yet, the second derivation is held to
+    the reference's output so the kernel can be built against both."""
+    from oracle import sw2d_numpy
+
+    ctx = _ctx("coarse_box.msh", False, 4)
+    h, hu, hv, H, hN = (ref["swhelpers_" + n] for n in ("h", "hu", "hv", "H", "hN"))
+    R = sw2d_numpy.compute_rhs(ctx, h, hu, hv, g=G, lf_mode=0, sources=True, H=H, Hx=np.full_like(H, 0.5),
+                               Hy=np.full_like(H, 0.25), CD=0.0, f=F_COR, hN=hN)
+    assert len(R) == 4
+    for c in range(4):
+        assert relerr(R[c], ref["swhelpers_cd0_RHS%d" % (c + 1)]) < RHS_TOL, c
+
+
 def test_limiter_restatement_matches_reference_function(ref):
     from oracle.output_numpy import positivity_limiter
 
