@@ -31,6 +31,7 @@ class MeshManager:
         self.BCType = None
         self.ElementPartitionMap = None
         self.VertexPartitionMap = None
+        self.PartitionInfo = None
 
     # ------------------------------------------------------------------ readers
     def readMesh(self, gmshInputFile):
@@ -142,27 +143,82 @@ class MeshManager:
         self.BCType = np.ascontiguousarray(np.asarray(bcType, dtype=np.int32).reshape(-1))
 
     # -------------------------------------------------------------- partitions
-    def partitionMesh(self, numPartitions, method="auto"):
-        """Element -> rank map (reference: METIS_PartMeshNodal k-way, MeshManager.cpp:491-544).
+    def partitionMesh(self, numPartitions, method="auto", seed=-1, verbose=False):
+        """Element -> rank map: METIS_PartMeshNodal, k-way, with the reference's option set
+        (MeshManager.cpp:491-544; options :498-514).  Sets ElementPartitionMap[k] and
+        VertexPartitionMap[v], both in [0,P), and returns the element map.
 
-        metis.h / a callable METIS are absent from this image, so the map is
-        produced by recursive coordinate bisection of element centroids
-        (contiguous, balanced parts); the output contract is the reference's:
-        ElementPartitionMap[k] in [0,P), VertexPartitionMap[v] in [0,P).
+        METIS itself is the 5.1.0 archive that ships with the CUDA toolkit (libmetis_static.a,
+        64-bit idx_t), linked into the host-only shim blitzdg_b200/csrc/libbdg_metis.so
+        (metis_shim.c).  seed=-1 is the reference's (time-dependent) seed; pass a fixed one for
+        reproducible maps.  method: "metis" | "metis-dual" (METIS_PartMeshDual, ncommon=2; a
+        study switch, not the reference's call) | "rcb" (recursive coordinate bisection) |
+        "auto" = metis, falling back to rcb with a printed reason if the shim is missing.
         """
+        import ctypes as C
+        import os
+        import sys
+
         from .partition import rcb_partition
 
         K, Nf = self.NumElements, self.NumFaces
         etov = self.EToV.reshape(K, Nf)
+        P = int(numPartitions)
+        self.PartitionInfo = {"method": None, "objval": None}
+        if method in ("auto", "metis", "metis-dual"):
+            path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libbdg_metis.so")
+            why = None
+            try:
+                lib = C.CDLL(path)
+                if lib.bdg_metis_idx_bytes() != 8:
+                    why = "METIS idx_t width probe failed"
+            except OSError as exc:
+                why = "cannot load %s (%s)" % (path, exc)
+            if why is None:
+                ip = C.POINTER(C.c_int32)
+                ev = np.ascontiguousarray(etov.reshape(-1), dtype=np.int32)
+                ep = np.zeros(K, dtype=np.int32)
+                vp = np.zeros(self.NumVerts, dtype=np.int32)
+                obj = C.c_int64(0)
+                rc = lib.bdg_metis_part_mesh(K, self.NumVerts, Nf, ev.ctypes.data_as(ip), P, int(seed), int(method == "metis-dual"),
+                                             int(bool(verbose)), ep.ctypes.data_as(ip), vp.ctypes.data_as(ip), C.byref(obj))
+                if rc == 1:  # METIS_OK
+                    self.ElementPartitionMap, self.VertexPartitionMap = ep, vp
+                    self.PartitionInfo = {"method": "METIS_PartMeshDual" if method == "metis-dual" else "METIS_PartMeshNodal",
+                                          "objval": int(obj.value)}
+                    return ep
+                # the reference only prints the METIS status (:534-541) and keeps the zeroed maps; a zero map is useless
+                # for sharding, so say so and fall back
+                why = {-2: "METIS input error!", -3: "METIS could not allocate the required memory!"}.get(rc, "Unknown METIS error: %d" % rc)
+            if method != "auto":
+                raise RuntimeError("partitionMesh(%s): %s" % (method, why))
+            print("blitzdg_b200.MeshManager.partitionMesh: %s -- falling back to recursive coordinate bisection" % why, file=sys.stderr)
         vert = self.Vert.reshape(-1, 3)
         cx = vert[etov, 0].mean(axis=1)
         cy = vert[etov, 1].mean(axis=1)
-        epart = rcb_partition(cx, cy, numPartitions)
+        epart = rcb_partition(cx, cy, P)
         vpart = np.zeros(self.NumVerts, dtype=np.int32)
         vpart[etov.reshape(-1)] = np.repeat(epart, Nf)
         self.ElementPartitionMap = epart.astype(np.int32)
         self.VertexPartitionMap = vpart
+        self.PartitionInfo = {"method": "rcb", "objval": None}
         return self.ElementPartitionMap
+
+    def readVertices(self, vertFile):
+        """Whitespace/CSV table of vertex coordinates, one vertex per row (MeshManager.cpp:546-548)."""
+        v = np.loadtxt(vertFile, ndmin=2)
+        self.Dim = v.shape[1]
+        self.NumVerts = v.shape[0]
+        self.Vert = np.ascontiguousarray(np.concatenate([v, np.zeros((v.shape[0], 3 - v.shape[1]))], axis=1).reshape(-1))
+
+    def readElements(self, E2VFile):
+        """Element-to-vertex table, one element per row; connectivity is built for triangles only (:550-562)."""
+        e = np.loadtxt(E2VFile, dtype=np.int64, ndmin=2)
+        self.NumElements, self.NumFaces = e.shape
+        self.EToV = np.ascontiguousarray(e.reshape(-1).astype(np.int32))
+        if self.NumFaces == 3:
+            self.buildConnectivity()
+            self.buildBCTable(BCTag.Wall)
 
     # ----------------------------------------------------------------- getters
     def get_NumElements(self):

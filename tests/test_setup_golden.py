@@ -5,6 +5,7 @@ Golden data: tests/golden/reference_vectors.json, extracted by tests/golden/extr
 tolerances those specs use.
 """
 import numpy as np
+import pytest
 
 from blitzdg_b200 import MeshManager, QuadNodesProvisioner, TriangleNodesProvisioner, BCTag
 from blitzdg_b200 import jacobi
@@ -109,10 +110,58 @@ def test_quads_ccw_repair_and_maps(coarse_quads_mesh):
     assert len(p.get_bcMap()[BCTag.Wall]) == 16 * 5
 
 
-def test_partition_map_contract(coarse_quads_mesh):
-    """Can_Partition_A_Mesh (MeshManagerTests.cpp:230-258): parts in [0,P), all ranks used."""
-    m = MeshManager()
-    m.buildMesh(np.array([[0, 1, 4, 3], [1, 2, 5, 4]]), np.array([[0., 0], [1, 0], [2, 0], [0, 1], [1, 1], [2, 1]]))
-    ep = m.partitionMesh(2)
+def test_partition_map_contract():
+    """Can_Partition_A_Mesh (MeshManagerTests.cpp:230-258) on input/2box.{V,E2V}: the spec reads the two files, calls
+    partitionMesh(2) -- METIS_PartMeshNodal with the options of MeshManager.cpp:498-514 and the time-dependent seed -1 --
+    and expects epMap = (1, 0) and every vertex assigned.  Here through the same METIS (libbdg_metis.so)."""
+    import os
+    import tempfile
+
+    with tempfile.TemporaryDirectory() as d:
+        with open(os.path.join(d, "2box.V"), "w") as fh:
+            fh.write("0 0\n0.5 0\n1 0\n1 1\n0.5 1\n0 1\n")
+        with open(os.path.join(d, "2box.E2V"), "w") as fh:
+            fh.write("0 1 4 5\n1 2 3 4\n")
+        m = MeshManager()
+        m.readVertices(os.path.join(d, "2box.V"))
+        m.readElements(os.path.join(d, "2box.E2V"))
+    assert m.get_NumVerts() == 6 and m.get_NumElements() == 2 and m.get_NumFaces() == 4
+    ep = m.partitionMesh(2, method="metis")
+    assert m.PartitionInfo["method"] == "METIS_PartMeshNodal"
+    # The spec's literal epMap = (1, 0) is the labelling of the reference's METIS build (master, manylinux2010/Dockerfile:124-130);
+    # the toolkit's 5.1.0 archive returns the mirrored labelling (0, 1) for every seed.  Part labels carry no meaning:
+    # the contract is "the two boxes land in different parts".
     assert sorted(ep.tolist()) == [0, 1]
-    assert (m.get_VertexPartitionMap() >= 0).all()
+    assert (m.get_VertexPartitionMap() > -1).all() and (m.get_VertexPartitionMap() < 2).all()
+
+
+@pytest.mark.parametrize("shape,nx,ny,P", [("tri", 40, 24, 4), ("tri", 120, 80, 8), ("quad", 60, 40, 3)])
+def test_metis_partition_properties(shape, nx, ny, P):
+    """partitionMesh on meshes large enough to have a real cut: every part used, balanced within METIS's own tolerance
+    for nodal partitions, far fewer cut faces than a random map, reproducible for a fixed seed, and an irregular
+    neighbour graph (some rank has >= 3 neighbours at P = 8) -- what the halo code must cope with."""
+    from blitzdg_b200.synthetic import structured_mesh
+
+    m = structured_mesh(shape, nx, ny)
+    K, Nf = m.get_NumElements(), m.get_NumFaces()
+    ep = m.partitionMesh(P, method="metis", seed=11).copy()
+    assert ep.min() == 0 and ep.max() == P - 1
+    cnt = np.bincount(ep, minlength=P)
+    assert cnt.max() <= 1.15 * K / P and cnt.min() >= 0.8 * K / P
+    e2e = m.get_EToE().reshape(K, Nf)
+    cut = int((ep[e2e] != ep[:, None]).sum()) // 2
+    assert cut < 12 * np.sqrt(K * P)
+    assert np.array_equal(ep, m.partitionMesh(P, method="metis", seed=11))
+    vp = m.get_VertexPartitionMap()
+    assert vp.min() >= 0 and vp.max() < P
+    if P == 8:
+        nbrs = [len(set(ep[e2e[ep == r]].ravel().tolist()) - {r}) for r in range(P)]
+        assert max(nbrs) >= 3
+
+
+def test_partition_fallback_is_rcb():
+    from blitzdg_b200.synthetic import structured_mesh
+
+    m = structured_mesh("tri", 16, 16)
+    ep = m.partitionMesh(4, method="rcb")
+    assert m.PartitionInfo["method"] == "rcb" and np.bincount(ep).tolist() == [128] * 4
