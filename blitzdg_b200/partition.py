@@ -33,6 +33,39 @@ def strip_partition(cy, nparts):
     return part
 
 
+def make_partition(mesh, nparts, how="metis", seed=20260101):
+    """ElementPartitionMap of `mesh` for `nparts` ranks.  how: "metis" = MeshManager.partitionMesh (METIS_PartMeshNodal
+    with the reference's options, src/MeshManager.cpp:491-544; fixed seed so that every rank of a job computes the same
+    map), "rcb" = recursive coordinate bisection, "strips" = balanced horizontal strips.  Returns (epart, description)."""
+    K, Nf = mesh.get_NumElements(), mesh.get_NumFaces()
+    if nparts <= 1:
+        return np.zeros(K, dtype=np.int32), "single part"
+    if how == "metis":
+        ep = mesh.partitionMesh(nparts, method="auto", seed=seed)
+        return np.asarray(ep, dtype=np.int32), "%s (k-way, reference options src/MeshManager.cpp:498-514, seed %d)" % (mesh.PartitionInfo["method"], seed)
+    cen = mesh.get_Vertices().reshape(-1, 3)[mesh.get_Elements().reshape(K, Nf)].mean(axis=1)
+    if how == "rcb":
+        return rcb_partition(cen[:, 0], cen[:, 1], nparts), "recursive coordinate bisection"
+    if how == "strips":
+        return strip_partition(cen[:, 1], nparts), "%d horizontal strips" % nparts
+    raise ValueError(how)
+
+
+def partition_stats(mesh, epart):
+    """Per-rank element counts, neighbour counts and cut faces of an element partition (for reports)."""
+    K, Nf = mesh.get_NumElements(), mesh.get_NumFaces()
+    epart = np.asarray(epart)
+    P = int(epart.max()) + 1
+    e2e = mesh.get_EToE().reshape(K, Nf)
+    nb = epart[e2e]
+    off = nb != epart[:, None]
+    pair = np.unique(np.stack([np.repeat(epart, Nf)[off.reshape(-1)], nb[off]], axis=1), axis=0)
+    return {"elements": np.bincount(epart, minlength=P).tolist(),
+            "neighbours": np.bincount(pair[:, 0], minlength=P).tolist() if len(pair) else [0] * P,
+            "cut_faces": np.bincount(np.repeat(epart, Nf)[off.reshape(-1)], minlength=P).tolist(),
+            "cut_faces_total": int(off.sum()) // 2}
+
+
 def build_local(mesh, epart, rank, N):
     """Provision rank `rank` of an element-partitioned mesh.
 

@@ -127,3 +127,86 @@ class Oracle:
         H = np.empty((Np, K))
         lib().oracle_depth_to_H(_d(values), values.size, Np, K, _d(H))
         return H
+
+
+# ---- extended-precision arbiter (oracle/sw2d_arbiter.c) -------------------------------------------------------------
+_arb = {}
+
+
+def arbiter_lib(quad=False):
+    name = "libarbiter_q.so" if quad else "libarbiter.so"
+    if name not in _arb:
+        path = os.path.join(_HERE, name)
+        if not os.path.exists(path):
+            subprocess.check_call(["make", "-C", _HERE, "-s", name], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        L = C.CDLL(path)
+        u8 = C.POINTER(C.c_uint8)
+        L.arbiter_sw2d_rhs.argtypes = [C.POINTER(bdg_dgcontext2d), C.POINTER(bdg_sw2d_params), u8, _dp, _dp, _dp, _dp, _dp, _dp,
+                                       C.c_double, C.c_int, _dp, C.c_double, C.c_int, C.c_int, _dp, _dp, _dp]
+        L.arbiter_sw2d_max_speed.argtypes = [C.POINTER(bdg_dgcontext2d), C.POINTER(bdg_sw2d_params), u8, _dp, _dp, _dp, _dp,
+                                             C.c_double, C.c_int, _dp, C.c_int, C.c_int]
+        L.arbiter_sw2d_max_speed.restype = C.c_double
+        _arb[name] = L
+    return _arb[name]
+
+
+class Arbiter:
+    """Extended-precision evaluation of the same RHS from the same fp64 inputs: the yardstick for "which fp64 result is
+    closer to the exact value".  rhs(..., elements=(k0, k1)) evaluates a range only (other columns of the result are NaN);
+    `threads` ranges run concurrently (ctypes releases the GIL)."""
+
+    def __init__(self, ctx, quad=False, **params):
+        self.ctx = ctx
+        self.cctx, self._keep = pack_context(ctx)
+        self.prm = make_params(**params)
+        self.L = arbiter_lib(quad)
+        self.H = self.Hx = self.Hy = None
+        Nfn = ctx.Nfaces * ctx.Nfp
+        self.bctag = np.zeros(Nfn * ctx.K, dtype=np.uint8)
+        for tag, ids in ctx.BCmap.items():
+            self.bctag[np.asarray(ids, dtype=np.int64)] = int(tag)
+
+    def set_bathymetry(self, H, Hx, Hy):
+        self.H, self.Hx, self.Hy = _c(H), _c(Hx), _c(Hy)
+
+    def _ranges(self, elements, threads):
+        k0, k1 = elements if elements is not None else (0, self.ctx.K)
+        threads = max(1, min(int(threads), k1 - k0))
+        cuts = [k0 + (k1 - k0) * i // threads for i in range(threads + 1)]
+        return [(cuts[i], cuts[i + 1]) for i in range(threads)]
+
+    def _run(self, fn, ranges):
+        import threading
+
+        res = [None] * len(ranges)
+
+        def work(i):
+            res[i] = fn(*ranges[i])
+
+        ths = [threading.Thread(target=work, args=(i,)) for i in range(len(ranges))]
+        for t in ths:
+            t.start()
+        for t in ths:
+            t.join()
+        return res
+
+    def rhs(self, h, hu, hv, t=0.0, ghost=None, elements=None, threads=None):
+        h, hu, hv = _c(h), _c(hu), _c(hv)
+        threads = threads or (os.cpu_count() or 1)
+        ng = 0
+        if ghost is not None:
+            ghost = _c(ghost)
+            ng = ghost.shape[1]
+        tags = self.bctag.ctypes.data_as(C.POINTER(C.c_uint8))
+        ranges = self._ranges(elements, threads)
+        lam = 0.0
+        if self.prm.lf_mode == 1:  # global LF speed: over ALL elements, whatever range is asked for
+            allr = self._ranges(None, threads)
+            lam = max(self._run(lambda a, b: self.L.arbiter_sw2d_max_speed(C.byref(self.cctx), C.byref(self.prm), tags, _d(self.H), _d(h),
+                                                                           _d(hu), _d(hv), t, ng, _d(ghost), a, b), allr))
+        out = [np.full_like(h, np.nan) for _ in range(3)]
+        rcs = self._run(lambda a, b: self.L.arbiter_sw2d_rhs(C.byref(self.cctx), C.byref(self.prm), tags, _d(self.H), _d(self.Hx), _d(self.Hy),
+                                                             _d(h), _d(hu), _d(hv), t, ng, _d(ghost), lam, a, b, _d(out[0]), _d(out[1]),
+                                                             _d(out[2])), ranges)
+        assert all(r == 0 for r in rcs)
+        return out

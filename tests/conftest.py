@@ -38,3 +38,27 @@ def coarse_quads_mesh():
     m = MeshManager()
     m.readMesh(os.path.join(GOLDEN, "coarse_box_quads.msh"))
     return m
+
+
+def fused_expected(sol):
+    """The fused single-launch kernel is the product path wherever sw2d_fused.cu covers the case: its absence there is
+    a FAILURE of the test, never a silent fall-back to the two-launch path.  Straight-sided triangles (a jittered
+    structured mesh is still affine) of the instantiated orders, no RHS filter."""
+    c = sol.ctx
+    return c.Nfaces == 3 and c.N <= 5 and not sol.prm.filter and not sol.prm.sources
+
+
+def kernel_variants(sol):
+    """Kernel variants to hold to the oracle for this solver: [1] or [1, 2]."""
+    out = [1]
+    if fused_expected(sol):
+        sol.set_variant(2)  # raises RuntimeError if the fused path was lost
+        out.append(2)
+    else:
+        try:
+            sol.set_variant(2)
+            out.append(2)
+        except RuntimeError:
+            pass
+    sol.set_variant(0)
+    return out

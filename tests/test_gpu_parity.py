@@ -46,15 +46,7 @@ def _state(ctx, seed=0, amp=0.3):
     return H, h, amp * rng.standard_normal(h.shape), amp * rng.standard_normal(h.shape)
 
 
-def _variants(sol):
-    out = [1]
-    try:
-        sol.set_variant(2)
-        out.append(2)
-    except RuntimeError:
-        pass
-    sol.set_variant(0)
-    return out
+from conftest import kernel_variants as _variants  # noqa: E402
 
 
 @pytest.mark.parametrize("quad,N", [(False, 1), (False, 2), (False, 3), (False, 4), (False, 5), (False, 8), (True, 3), (True, 6)])
@@ -119,10 +111,7 @@ def test_1000_lserk4_steps_coarse_box_n4(coarse_box_mesh, variant):
     dt, _ = orc.timestep(h, hu, hv, use_abs=True)
     dt *= 0.5
     sol = _solver(ctx)
-    try:
-        sol.set_variant(variant)
-    except RuntimeError:
-        pytest.skip("fused variant unavailable")
+    sol.set_variant(variant)  # N=4 affine triangles: both variants must exist
     sol.set_bathymetry(H)
     sol.set_state(h, hu, hv)
     sol.step(1000, dt)
@@ -236,103 +225,7 @@ def test_two_rank_halo_emulated_on_one_gpu():
         s.close()
 
 
-def test_full_size_properties_1M_triangles():
-    """BASELINE config 2 at full size through size-independent properties: still water is steady,
-    mass is conserved over LSERK4 steps with all-wall BC, state stays finite."""
-    mesh = structured_mesh("tri", 1000, 500)
-    prov = provision(mesh, 4)
-    ctx = prov.get_DGContext()
-    sol = _solver(ctx)
-    flat = np.full((ctx.Np, ctx.K), 10.0)
-    zero = np.zeros_like(flat)
-    sol.set_state(flat, zero, zero)
-    for R in sol.computeRHS():
-        assert np.abs(R).max() < 1e-7
-    H, h, hu, hv = gaussian_hump(ctx.x, ctx.y)
-    w = np.linalg.inv(ctx.V @ ctx.V.T).sum(axis=0)
-    mass0 = (w[:, None] * ctx.J * h).sum()
-    sol.set_bathymetry(H)  # eta = h - H in the blow-up guard (reference src/sw2d/main.cpp:193,238)
-    sol.set_state(h, hu, hv)
-    dt = 0.5 * sol.computeTimeStep() * (0.65 / 0.25)
-    sol.step(20, dt)
-    hg, hug, hvg, _ = sol.get_state()
-    mass1 = (w[:, None] * ctx.J * hg).sum()
-    assert abs(mass1 - mass0) < 1e-11 * abs(mass0)
-    assert np.isfinite(hg).all() and sol.check() < 1.01
-    # both kernel variants agree at full size
-    if 2 in _variants(sol):
-        sol.set_state(h, hu, hv)
-        sol.set_variant(1)
-        Ra = sol.computeRHS()
-        sol.set_variant(2)
-        Rb = sol.computeRHS()
-        # two summation orders of the same contraction: the gap is the conditioning of the volume term, which
-        # grows like rx ~ 1/h_mesh (cancellation of the constant g h^2/2 part): 5e-13 on a 64x32 grid, 2.5e-12 on
-        # 250x125, 1.2e-11 here (tools/dbg_variants.py)
-        for a, b in zip(Ra, Rb):
-            assert relerr(a, b) < 5e-11
-    sol.close()
-
-
-@pytest.mark.parametrize("name,shape,N,nx,ny", [("config 3", "tri", 8, 2000, 1000), ("config 4", "quad", 6, 2000, 1000),
-                                               ("config 5", "tri", 4, 4000, 2000)])
-def test_full_size_properties_other_configs(name, shape, N, nx, ny):
-    """BASELINE configs 3, 4 and 5 (all 16 M triangles on one GPU: byte offsets beyond 2^31) at full size through
-    size-independent properties: still water is steady, mass is conserved with all-wall BC, the state stays finite,
-    and a sample of elements agrees with the oracle evaluated on a sub-mesh cut out around them."""
-    import os
-
-    if name == "config 5" and os.environ.get("BDG_SKIP_16M"):
-        pytest.skip("BDG_SKIP_16M set")
-    prov = provision(structured_mesh(shape, nx, ny), N)
-    ctx = prov.get_DGContext()
-    sol = _solver(ctx)
-    flat = np.full((ctx.Np, ctx.K), 10.0)
-    zero = np.zeros_like(flat)
-    sol.set_state(flat, zero, zero)
-    for R in sol.computeRHS():
-        assert np.abs(R).max() < 1e-6 * N
-    del flat, zero
-    H, h, hu, hv = gaussian_hump(ctx.x, ctx.y)
-    w = np.linalg.inv(ctx.V @ ctx.V.T).sum(axis=0)
-    mass0 = (w[:, None] * ctx.J * h).sum()
-    sol.set_bathymetry(H)
-    # The RHS of an element depends on the element and its face neighbours only: the top row of cells (highest element
-    # indices = largest device offsets) must agree with the oracle on a 3-row strip mesh of the same cells.
-    from blitzdg_b200 import MeshManager
-    from blitzdg_b200.synthetic import structured_arrays
-
-    rows = 3
-    etov, vert = structured_arrays(shape, nx, rows, y0=1.0 - 2.0 * rows / ny, y1=1.0)
-    m = MeshManager()
-    m.buildMesh(etov, vert)
-    sub = provision(m, N).get_DGContext()
-    per_row = nx * (2 if shape == "tri" else 1)
-    top, tsub = slice(ctx.K - per_row, ctx.K), slice(sub.K - per_row, sub.K)
-    assert np.abs(ctx.y[:, top] - sub.y[:, tsub]).max() < 1e-12 and np.abs(ctx.x[:, top] - sub.x[:, tsub]).max() < 1e-12
-    _, ht, hut, hvt = gaussian_hump(ctx.x, ctx.y - 0.9)  # hump centred near the top edge, so the strip sees O(100) RHS values
-    _, hs, hus, hvs = gaussian_hump(sub.x, sub.y - 0.9)
-    sol.set_state(ht, hut, hvt)
-    R = sol.computeRHS()
-    Ro = _oracle(sub).rhs(hs, hus, hvs)
-    # Conditioning: the volume term differentiates g h^2/2 ~ 490 with metric factors ~ 2/h_cell and |Dr|_inf ~ N^2/2, and the
-    # O(100) result is what is left after cancellation -- so the bound is a few eps of that product (observed: 2.7e-8
-    # absolute on config 3, relative 1e-10), not 1e-12 of the result as on the unit-size meshes of the parity tests.
-    cond = 0.5 * 9.81 * float(ht.max()) ** 2 * (np.abs(ctx.rx).max() + np.abs(ctx.ry).max()) * np.abs(ctx.Dr).sum(axis=1).max()
-    for a, b in zip(R[1:], Ro[1:]):
-        assert np.abs(b[:, tsub]).max() > 10.0
-        err = np.abs(a[:, top] - b[:, tsub]).max()
-        assert err <= 8 * 2.2e-16 * cond and err <= 1e-9 * np.abs(b[:, tsub]).max(), (name, err, cond)
-    del R, Ro, ht, hut, hvt
-    sol.set_state(h, hu, hv)
-    dt = 0.5 * sol.computeTimeStep() * (0.65 / 0.25)
-    assert dt > 0
-    sol.step(5, dt)
-    hg, hug, hvg, _ = sol.get_state()
-    mass1 = (w[:, None] * ctx.J * hg).sum()
-    assert abs(mass1 - mass0) < 1e-11 * abs(mass0)
-    assert np.isfinite(hg).all() and np.isfinite(hug).all() and sol.check() < 1.01
-    sol.close()
+# BASELINE's full-size configs (2-5): tests/test_fullsize_parity.py (whole-mesh oracle + extended-precision arbiter)
 
 
 def test_streaming_state_calls_equal_serial_calls():

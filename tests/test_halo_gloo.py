@@ -12,7 +12,7 @@ import numpy as np
 import pytest
 
 from blitzdg_b200.initial_conditions import gaussian_hump
-from blitzdg_b200.partition import build_local, rcb_partition, strip_partition
+from blitzdg_b200.partition import build_local, make_partition
 from blitzdg_b200.synthetic import provision, structured_mesh
 
 
@@ -24,8 +24,9 @@ def _free_port():
     return p
 
 
-def _global_problem(shape, N):
-    mesh = structured_mesh(shape, 12, 8, jitter=0.15 if shape == "quad" else 0.0)
+def _global_problem(shape, N, how="strips"):
+    nx, ny = (24, 16) if how == "metis" else (12, 8)
+    mesh = structured_mesh(shape, nx, ny, jitter=0.15 if shape == "quad" else 0.0)
     ctx = provision(mesh, N).get_DGContext()
     H, h, hu, hv = gaussian_hump(ctx.x, ctx.y)
     rng = np.random.default_rng(5)
@@ -44,10 +45,8 @@ def _worker(rank, world, port, shape, N, how, out):
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
-        mesh, ctx, h, hu, hv = _global_problem(shape, N)
-        K, Nf = mesh.get_NumElements(), mesh.get_NumFaces()
-        cen = mesh.get_Vertices().reshape(-1, 3)[mesh.get_Elements().reshape(K, Nf)].mean(axis=1)
-        epart = strip_partition(cen[:, 1], world) if how == "strips" else rcb_partition(cen[:, 0], cen[:, 1], world)
+        mesh, ctx, h, hu, hv = _global_problem(shape, N, how)
+        epart, _ = make_partition(mesh, world, how)
         lctx, halo, info = build_local(mesh, epart, rank, N)
         el = info["elements"]
         q = [np.ascontiguousarray(a[:, el]) for a in (h, hu, hv)]
@@ -79,7 +78,8 @@ def _worker(rank, world, port, shape, N, how, out):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("shape,N,world,how", [("tri", 4, 2, "strips"), ("tri", 3, 4, "rcb"), ("quad", 3, 2, "strips")])
+@pytest.mark.parametrize("shape,N,world,how", [("tri", 4, 2, "strips"), ("tri", 3, 4, "rcb"), ("quad", 3, 2, "strips"),
+                                                ("tri", 4, 4, "metis"), ("quad", 3, 3, "metis")])
 def test_partitioned_rhs_equals_single_rank_over_gloo(shape, N, world, how):
     import torch.multiprocessing as mp
 
@@ -94,7 +94,7 @@ def test_partitioned_rhs_equals_single_rank_over_gloo(shape, N, world, how):
         p.join(timeout=60)
         assert p.exitcode == 0
     K = sum(r[2] for r in res)
-    assert K == 12 * 8 * (2 if shape == "tri" else 1)
+    assert K == (24 * 16 if how == "metis" else 12 * 8) * (2 if shape == "tri" else 1)
     for err, n_int, kloc in res:
         assert err < 1e-14, res          # same arithmetic per element: independent of the partition
         assert 0 < n_int < kloc          # interior-first renumbering leaves work to overlap with the exchange

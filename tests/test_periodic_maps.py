@@ -7,6 +7,7 @@ neighbour: the device element order, the fused kernel's tiles and the global-spe
 """
 import numpy as np
 import pytest
+from conftest import kernel_variants
 
 from blitzdg_b200.synthetic import provision, structured_mesh
 
@@ -102,12 +103,7 @@ def test_cuda_periodic_seam(shape, N, mode):
     orc.set_bathymetry(H, z, z)
     sol = SW2dSolver(ctx, mode=mode)
     sol.set_bathymetry(H, z, z)
-    variants = [1]
-    try:
-        sol.set_variant(2)
-        variants.append(2)
-    except RuntimeError:
-        pass
+    variants = kernel_variants(sol)
     Ro = orc.rhs(h, hu, hv)
     ho, huo, hvo = h.copy(), hu.copy(), hv.copy()
     res = [np.zeros_like(h) for _ in range(3)]

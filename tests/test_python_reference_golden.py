@@ -11,6 +11,7 @@ import os
 
 import numpy as np
 import pytest
+from conftest import kernel_variants
 
 from blitzdg_b200 import MeshManager, QuadNodesProvisioner, TriangleNodesProvisioner
 
@@ -135,12 +136,7 @@ def test_cuda_matches_sw2dquads_rhs(ref, tag, msh, quad, N):
     h, hu, hv = (ref["sw2dquads_%s_%s" % (tag, n)] for n in ("h", "hu", "hv"))
     sol = _solver(ctx)
     sol.set_state(h, hu, hv)
-    variants = [1]
-    try:
-        sol.set_variant(2)
-        variants.append(2)
-    except RuntimeError:
-        pass
+    variants = kernel_variants(sol)
     for var in variants:
         sol.set_variant(var)
         R = sol.computeRHS()
@@ -155,12 +151,7 @@ def test_cuda_matches_1000_lserk4_steps_of_reference_rhs(ref, tag, msh, quad, N)
     ctx = _ctx(msh, quad, N)
     h, hu, hv = (ref["sw2dquads_%s_%s" % (tag, n)] for n in ("h", "hu", "hv"))
     sol = _solver(ctx)
-    variants = [1]
-    try:
-        sol.set_variant(2)
-        variants.append(2)
-    except RuntimeError:
-        pass
+    variants = kernel_variants(sol)
     for var in variants:
         sol.set_variant(var)
         sol.set_state(h, hu, hv)
