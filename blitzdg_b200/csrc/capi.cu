@@ -83,22 +83,20 @@ int tile_kb(int R) {
   return kb;
 }
 
-struct Staging {
-  double *buf = nullptr;
-  size_t cap = 0;
-};
-Staging g_stage[16];
-
+// transposition staging buffer of one handle (grown on demand, freed at destroy): every use is enqueued on the handle's
+// own stream, so two handles -- even on the same device, driven from different threads -- never share it
 double *staging(bdg_sw2d *s, size_t n) {
-  Staging &st = g_stage[s->device & 15];
-  if (st.cap < n) {
-    if (st.buf) cudaFree(st.buf);
-    st.buf = nullptr;
-    st.cap = 0;
-    if (cudaMalloc(&st.buf, n * sizeof(double)) != cudaSuccess) return nullptr;
-    st.cap = n;
+  if (s->stage_cap < n) {
+    if (s->stage_buf) {
+      cudaStreamSynchronize(s->stream);  // earlier conversions may still read the old buffer
+      cudaFree(s->stage_buf);
+    }
+    s->stage_buf = nullptr;
+    s->stage_cap = 0;
+    if (cudaMalloc(&s->stage_buf, n * sizeof(double)) != cudaSuccess) return nullptr;
+    s->stage_cap = n;
   }
-  return st.buf;
+  return s->stage_buf;
 }
 
 // host row-major [R][K] -> device element-major [K][R]
@@ -166,7 +164,7 @@ extern "C" void bdg_sw2d_destroy(bdg_sw2d *s) {
   fused_release(s);
   void *ptrs[] = {s->q[0], s->q[1], s->res, s->rhs, s->sflux, s->d_Dr, s->d_Ds, s->d_Lift, s->d_Filt, s->d_rx, s->d_sx,
                   s->d_ry, s->d_sy, s->d_nx, s->d_ny, s->d_Fscale, s->d_aff, s->d_H, s->d_Hx, s->d_Hy, s->d_vmapP,
-                  s->d_fmask, s->d_bctag, s->d_facetag, s->d_scal, s->d_send_nodes, s->d_sendbuf, s->d_perm, s->d_vfrag, s->d_Dq, s->d_sponge, s->d_IM, s->d_out, s->in_raw, s->dl_raw};
+                  s->d_fmask, s->d_bctag, s->d_facetag, s->d_scal, s->d_send_nodes, s->d_sendbuf, s->d_perm, s->d_vfrag, s->d_Dq, s->d_sponge, s->d_IM, s->d_out, s->in_raw, s->dl_raw, s->stage_buf};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   free(s->h_nbr); free(s->h_send_off); free(s->h_recv_off);
@@ -210,8 +208,16 @@ static int create_impl(bdg_sw2d *s, const bdg_dgcontext2d *c, const bdg_sw2d_par
   for (long long k = 0; k < K; ++k)
     for (int sl = 0; sl < Nfn; ++sl)
       if (c->vmapM[k * Nfn + sl] != fmask[sl] + Np * k) return fail(s, BDG_E_INVALID, "vmapM is not Fmask + Np*k at element %lld slot %d", k, sl);
-  for (size_t i = 0; i < s->nF; ++i)
+  long long first_ghost_elem = K;  // first element with a '+' node in a ghost slot
+  for (size_t i = 0; i < s->nF; ++i) {
     if (c->vmapP[i] < 0 || c->vmapP[i] >= nTot) return fail(s, BDG_E_INVALID, "vmapP[%zu]=%d out of range", i, c->vmapP[i]);
+    if ((size_t)c->vmapP[i] >= s->nT && (long long)(i / Nfn) < first_ghost_elem) first_ghost_elem = (long long)(i / Nfn);
+  }
+  // The interior launch over [0,n_interior) overlaps the halo exchange on the promise that those elements read no ghost
+  // slot: a caller-supplied split that breaks the promise would be a silent data race, so it is rejected here.
+  if (halo && halo->n_interior > first_ghost_elem)
+    return fail(s, BDG_E_INVALID, "halo->n_interior=%d but element %lld reads a ghost slot (interior elements must come first)", halo->n_interior,
+                first_ghost_elem);
 
   // per-face-node BC tags from the BCmap lists (reference include/DGContext2D.hpp bcmap())
   std::vector<uint8_t> bctag(s->nF, 0), facetag((size_t)K * Nf, 0);
@@ -672,7 +678,11 @@ static int peer_setup(bdg_sw2d *s) {
   s->peer_ok = 0;
   const char *env = getenv("BDG_HALO");
   if (env && !strcmp(env, "nccl")) return BDG_OK;
-  if (!s->fused_ok || s->v.lf_global || s->nranks < 2 || s->n_nbr > kMaxNbr) return BDG_OK;
+  if (s->nranks < 2) return BDG_OK;
+  // Only conditions that are IDENTICAL on every rank may return before the handshake below (BDG_HALO, nranks): a
+  // rank-local one -- no fused path on this partition, more neighbours than the peer table holds, global-LF mode --
+  // is published as stride = -1 instead, so that all ranks leave the collectives together and fall back to NCCL together.
+  const bool local_ok = s->fused_ok && !s->v.lf_global && s->n_nbr <= kMaxNbr;
   ncclComm_t comm = (ncclComm_t)s->comm;
   const int P = s->nranks;
   int rc;
@@ -683,7 +693,7 @@ static int peer_setup(bdg_sw2d *s) {
   // my record and my ghost bases: gbase[r] = first ghost slot (plane index) that sender r fills, or -1
   PeerRecord mine;
   memset(&mine, 0, sizeof(mine));
-  bool ok = cudaIpcGetMemHandle(&mine.q[0], s->q[0]) == cudaSuccess && cudaIpcGetMemHandle(&mine.q[1], s->q[1]) == cudaSuccess &&
+  bool ok = local_ok && cudaIpcGetMemHandle(&mine.q[0], s->q[0]) == cudaSuccess && cudaIpcGetMemHandle(&mine.q[1], s->q[1]) == cudaSuccess &&
             cudaIpcGetMemHandle(&mine.flags, s->d_flags) == cudaSuccess;
   if (!ok) cudaGetLastError();
   mine.stride = ok ? s->v.stride : -1;
@@ -708,7 +718,7 @@ static int peer_setup(bdg_sw2d *s) {
     if (all[r].stride < 0) ok = false;  // every rank must take the same decision
   PeerTable pt;
   memset(&pt, 0, sizeof(pt));
-  pt.n = s->n_nbr;
+  pt.n = ok ? s->n_nbr : 0;
   for (int i = 0; i < s->n_nbr && ok; ++i) {
     const int r = s->h_nbr[i];
     void *p0 = nullptr, *p1 = nullptr, *pf = nullptr;
@@ -743,6 +753,8 @@ static int peer_setup(bdg_sw2d *s) {
   if ((rc = dev_upload(s, &s->d_put_dst, dst.data(), dst.size()))) return rc;
   CU(cudaStreamSynchronize(s->stream));
   s->peer = pt;
+  s->put_ctas = s->n_send > 0 ? (s->n_send + 2047) / 2048 : 1;  // >= 8 entries per thread, at most one CTA per SM
+  if (s->put_ctas > 148) s->put_ctas = 148;
   s->epoch = 0;
   s->ghost_valid = 0;
   s->peer_ok = 1;
@@ -995,13 +1007,16 @@ extern "C" int bdg_sw2d_sync(bdg_sw2d *s) {
 extern "C" int bdg_sw2d_check(bdg_sw2d *s, double *eta_max) {
   if (!s) return BDG_E_INVALID;
   CU(cudaSetDevice(s->device));
-  CU(cudaMemsetAsync(s->d_scal + S_ETAMAX, 0, 2 * sizeof(double), s->stream));
+  static_assert(S_NANFLAG == S_ETAMAX + 1 && S_HALO_TIMEOUT == S_ETAMAX + 2, "scalar slots");
+  CU(cudaMemsetAsync(s->d_scal + S_ETAMAX, 0, 2 * sizeof(double), s->stream));  // S_HALO_TIMEOUT stays: it is sticky
   cudaError_t e = launch_check(s, s->q[s->cur]);
   if (e != cudaSuccess) return fail(s, BDG_E_CUDA, "check: %s", cudaGetErrorString(e));
-  double r[2];
-  CU(cudaMemcpyAsync(r, s->d_scal + S_ETAMAX, 2 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  double r[3];
+  CU(cudaMemcpyAsync(r, s->d_scal + S_ETAMAX, 3 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
   CU(cudaStreamSynchronize(s->stream));
   if (eta_max) *eta_max = r[1] != 0.0 ? NAN : r[0];
+  if (r[2] != 0.0)  // a cut launch ran on stale ghost traces: every result since then is invalid
+    return fail(s, BDG_E_NCCL, "halo exchange timed out: a neighbour rank never published its face traces (peer-memory halo)");
   if (r[1] != 0.0 || r[0] > 1e8) return fail(s, BDG_E_UNSTABLE, "A numerical instability has occurred!");  // reference main.cpp:238-240
   return BDG_OK;
 }

@@ -14,7 +14,8 @@
 struct ncclComm;
 
 // scalar slots kept on the device (no host round trips inside bdg_sw2d_step)
-enum { S_T = 0, S_DT = 1, S_GMAX0 = 2, S_GMAX1 = 3, S_DTMAX = 4, S_ETAMAX = 5, S_NANFLAG = 6, S_COUNT = 8 };
+// S_HALO_TIMEOUT is sticky: set by k_wait_epoch when a neighbour's epoch never arrives, read (never cleared) by bdg_sw2d_check
+enum { S_T = 0, S_DT = 1, S_GMAX0 = 2, S_GMAX1 = 3, S_DTMAX = 4, S_ETAMAX = 5, S_NANFLAG = 6, S_HALO_TIMEOUT = 7, S_COUNT = 8 };
 
 // everything a kernel needs, passed by value
 struct Sw2dView {
@@ -101,7 +102,8 @@ struct bdg_sw2d {
   PeerTable peer;
   void *peer_base[3][kMaxNbr];    // opened IPC mappings (q0, q1, flags) to close at destroy
   unsigned long long *d_flags;    // [nranks] epochs published by my neighbours
-  unsigned int *d_put_counter;
+  unsigned int *d_put_counter;    // CTAs of the current k_put launch that have finished their stores (last one publishes)
+  int put_ctas;                   // grid of k_put
   long long *d_put_dst;           // [n_send] ghost slot index in the receiver's plane
   unsigned long long epoch;       // number of puts issued (identical on all ranks: same call sequence)
   int put_pending;                // a put on the communication stream has not been joined by the main stream yet
@@ -113,6 +115,8 @@ struct bdg_sw2d {
   cudaEvent_t ev_out_state, ev_out_kernel, ev_out_done;
   // streaming interface (capi.cu: stage_state / commit_state / get_state_async): raw row-major planes [3][Np*K]
   double *in_raw, *dl_raw;
+  double *stage_buf;              // transposition staging of set_state / get_state / rhs / set_bathymetry (per handle)
+  size_t stage_cap;
   cudaStream_t in_stream, dl_stream;
   cudaEvent_t ev_in_done, ev_in_free, ev_dl_conv, ev_dl_done;
   int staged, dl_pending;

@@ -22,14 +22,16 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
   return v;
 }
 
-// ONE CTA: thread t handles send entries t, t+1024, ...: trace node send_nodes[j] of fields h,hu,hv -> ghost slot
-// put_dst[j] of the neighbour seg_of[j]; then a single system-scope fence and the epoch is published to every
-// neighbour.  (A halo is a few thousand nodes: one CTA keeps the fence + flag protocol trivial and short.)
-__global__ void __launch_bounds__(1024) k_put(PeerTable pt, const double *__restrict__ q, long long stride,
-                                              const int32_t *__restrict__ send_nodes, const int32_t *__restrict__ seg_of,
-                                              const long long *__restrict__ put_dst, int n_send, int buf, int my_rank,
-                                              unsigned long long epoch) {
-  for (int j = threadIdx.x; j < n_send; j += blockDim.x) {
+// Grid-stride over the send list: entry j = trace node send_nodes[j] of fields h,hu,hv -> ghost slot put_dst[j] of
+// the neighbour seg_of[j].  Every CTA fences its own stores at system scope and counts itself done; the LAST CTA to
+// finish publishes the epoch to every neighbour (and re-arms the counter), so a METIS cut of 50 k+ nodes is spread
+// over many SMs instead of being serialised through one block, while the flag protocol stays a single release store
+// per neighbour.
+__global__ void __launch_bounds__(256) k_put(PeerTable pt, const double *__restrict__ q, long long stride,
+                                             const int32_t *__restrict__ send_nodes, const int32_t *__restrict__ seg_of,
+                                             const long long *__restrict__ put_dst, int n_send, int buf, int my_rank,
+                                             unsigned long long epoch, unsigned int *counter) {
+  for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n_send; j += gridDim.x * blockDim.x) {
     const int sg = seg_of[j];
     const long long m = send_nodes[j], d = put_dst[j], ps = pt.stride[sg];
     double *dst = pt.q[buf][sg];
@@ -37,13 +39,22 @@ __global__ void __launch_bounds__(1024) k_put(PeerTable pt, const double *__rest
     dst[ps + d] = q[stride + m];
     dst[2 * ps + d] = q[2 * stride + m];
   }
-  __threadfence_system();
+  __threadfence_system();  // my stores are visible system-wide before my arrival below can be observed
   __syncthreads();
-  if (threadIdx.x < pt.n) st_release_sys(pt.flags[threadIdx.x] + my_rank, epoch);
+  __shared__ int last;
+  if (threadIdx.x == 0) {
+    last = atomicAdd(counter, 1u) == gridDim.x - 1;
+    if (last) *counter = 0u;  // the next put on this stream starts from zero (launches of one handle never overlap)
+  }
+  __syncthreads();
+  if (last) {
+    __threadfence_system();  // acquire side of the counter: every other CTA's fenced stores precede the flags
+    if (threadIdx.x < pt.n) st_release_sys(pt.flags[threadIdx.x] + my_rank, epoch);
+  }
 }
 
-// lanes 0..n-1 wait until neighbour nbr[lane] has published `epoch`; ~60 s budget, then the NaN flag is raised
-// (bdg_sw2d_check reports it) instead of hanging the GPU
+// lanes 0..n-1 wait until neighbour nbr[lane] has published `epoch`; ~60 s budget, then the sticky S_HALO_TIMEOUT
+// flag is raised (bdg_sw2d_check returns BDG_E_NCCL from then on) instead of hanging the GPU
 __global__ void k_wait_epoch(const unsigned long long *flags, PeerTable pt, unsigned long long epoch, double *scal) {
   const int i = threadIdx.x;
   if (i >= pt.n) return;
@@ -52,7 +63,7 @@ __global__ void k_wait_epoch(const unsigned long long *flags, PeerTable pt, unsi
     if (ld_acquire_sys(f) >= epoch) return;
     __nanosleep(200);
   }
-  scal[S_NANFLAG] = 1.0;
+  scal[S_HALO_TIMEOUT] = 1.0;
 }
 
 }  // namespace
@@ -69,7 +80,7 @@ cudaError_t launch_put(bdg_sw2d *s, const double *q, int buf, unsigned long long
     st = s->comm_stream;
   }
   const int32_t *nodes = s->d_send_nodes, *seg = s->d_send_nodes + s->n_send;
-  k_put<<<1, 1024, 0, st>>>(s->peer, q, s->v.stride, nodes, seg, s->d_put_dst, s->n_send, buf, s->rank, epoch);
+  k_put<<<s->put_ctas, 256, 0, st>>>(s->peer, q, s->v.stride, nodes, seg, s->d_put_dst, s->n_send, buf, s->rank, epoch, s->d_put_counter);
   s->launches++;
   if (side) {
     cudaError_t e = cudaEventRecord(s->ev_recv, s->comm_stream);

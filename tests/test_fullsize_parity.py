@@ -20,13 +20,11 @@ a time on the host cores, so that its ~55 temporaries per pass stay bounded in m
 """
 import json
 import os
-import threading
 
 import numpy as np
 import pytest
 
 from blitzdg_b200.initial_conditions import gaussian_hump
-from blitzdg_b200.partition import build_local, strip_partition
 from blitzdg_b200.synthetic import provision, structured_mesh
 
 pytestmark = pytest.mark.gpu
@@ -39,46 +37,16 @@ def relerr(a, b):
 
 
 def oracle_rhs_strips(mesh, N, state, nstrips, strips=None, threads=None):
-    """Oracle RHS of the global state evaluated strip by strip.  Returns (R [3][Np][K] with NaN outside the evaluated
-    strips, element mask).  strips: which strip indices to evaluate (default all)."""
-    from oracle.binding import Oracle
+    """Oracle RHS of the global state evaluated strip by strip (oracle/threaded.py).  Returns (R [3][Np][K] with NaN
+    outside the evaluated strips, element mask).  strips: which strip indices to evaluate (default all)."""
+    from oracle.threaded import StripOracle
 
-    h, hu, hv = state
-    K, Nf = mesh.get_NumElements(), mesh.get_NumFaces()
-    cy = mesh.get_Vertices().reshape(-1, 3)[mesh.get_Elements().reshape(K, Nf), 1].mean(axis=1)
-    epart = strip_partition(cy, nstrips)
-    strips = list(range(nstrips)) if strips is None else list(strips)
-    R = [np.full(h.shape, np.nan) for _ in range(3)]
-    done = np.zeros(K, dtype=bool)
-    Np = h.shape[0]
-    lock = threading.Lock()
-    todo = list(strips)
-
-    def work():
-        while True:
-            with lock:
-                if not todo:
-                    return
-                r = todo.pop()
-            lctx, halo, info = build_local(mesh, epart, r, N)
-            el = info["elements"]
-            gk = info["ghost_keys"]
-            gnode, gelem = gk % Np, (gk // Np) % K
-            ghost = np.zeros((4, len(gk)))
-            for c, a in enumerate((h, hu, hv)):
-                ghost[c] = a[gnode, gelem]
-            Rl = Oracle(lctx).rhs(np.ascontiguousarray(h[:, el]), np.ascontiguousarray(hu[:, el]), np.ascontiguousarray(hv[:, el]), ghost=ghost)
-            for c in range(3):
-                R[c][:, el] = Rl[c]
-            done[el] = True
-
-    nthreads = threads or max(1, min(len(strips), (os.cpu_count() or 2) // 2, 8))
-    ths = [threading.Thread(target=work) for _ in range(nthreads)]
-    for t in ths:
-        t.start()
-    for t in ths:
-        t.join()
-    return R, done
+    threads = threads or max(1, min((os.cpu_count() or 2), 8))  # ~55 temporaries per strip and thread: bounded memory
+    so = StripOracle(mesh, N, nparts=nstrips, threads=threads, parts=strips)
+    so.set_state(*state)
+    R = so.rhs()
+    so.close()
+    return R, ~np.isnan(R[0][0])
 
 
 def record(name, row):
