@@ -450,6 +450,7 @@ extern "C" int bdg_sw2d_set_bathymetry(bdg_sw2d *s, const double *H, const doubl
   int rc;
   if (!H) {
     s->v.H = s->v.Hx = s->v.Hy = nullptr;
+    s->lam_valid = 0;
     return BDG_OK;
   }
   if (!s->d_H) {
@@ -464,6 +465,8 @@ extern "C" int bdg_sw2d_set_bathymetry(bdg_sw2d *s, const double *H, const doubl
   if (Hx && (rc = upload_transposed(s, Hx, s->d_Hx, Np, K))) return rc;
   if (Hy && (rc = upload_transposed(s, Hy, s->d_Hy, Np, K))) return rc;
   s->v.H = s->d_H; s->v.Hx = s->d_Hx; s->v.Hy = s->d_Hy;
+  s->delta_dirty = 1;  // the fused full-physics path rebuilds its star-state table before the next launch
+  s->lam_valid = 0;
   CU(cudaStreamSynchronize(s->stream));
   return BDG_OK;
 }
@@ -480,6 +483,7 @@ extern "C" int bdg_sw2d_set_sponge(bdg_sw2d *s, const double *sigma) {
   if (!s->d_sponge && (rc = dev_alloc(s, &s->d_sponge, s->nT))) return rc;
   if ((rc = upload_transposed(s, sigma, s->d_sponge, s->v.Np, s->v.K))) return rc;
   s->v.sponge = s->d_sponge;
+  s->lam_valid = 0;
   CU(cudaStreamSynchronize(s->stream));
   return BDG_OK;
 }
@@ -500,6 +504,7 @@ extern "C" int bdg_sw2d_set_state(bdg_sw2d *s, const double *h, const double *hu
   CU(cudaMemsetAsync(s->res, 0, sizeof(double) * 3 * s->v.stride, s->stream));  // reference src/sw2d/main.cpp:117-119
   s->t = t;
   s->ghost_valid = 0;
+  s->lam_valid = 0;
   CU(cudaMemcpyAsync(s->d_scal + S_T, &s->t, sizeof(double), cudaMemcpyHostToDevice, s->stream));
   CU(cudaStreamSynchronize(s->stream));
   return BDG_OK;
@@ -580,6 +585,7 @@ extern "C" int bdg_sw2d_commit_state(bdg_sw2d *s) {
   s->t = s->staged_t;
   s->staged = 0;
   s->ghost_valid = 0;
+  s->lam_valid = 0;
   CU(cudaMemcpyAsync(s->d_scal + S_T, &s->t, sizeof(double), cudaMemcpyHostToDevice, s->stream));
   return BDG_OK;
 }
@@ -810,17 +816,20 @@ static int use_fused(const bdg_sw2d *s) {
 
 // One RHS evaluation of the live state.  write_rhs: store RHS planes into rhs_out (bdg_sw2d_rhs);
 // otherwise apply LSERK4 stage (a,b).  slot alternates the global-LF scalar between S_GMAX0/1.
-// rk2 = 2, 3: first / second SSP-RK2 stage of the src/sw2d driver instead (generic path; the state is read from
-// q[cur], the result goes to q[cur^1], which in the second stage still holds q^n, and the buffers swap).
-static int enqueue_stage(bdg_sw2d *s, int write_rhs, double *rhs_out, double a, double b, int slot, int rk2 = 0) {
+// rk2 = 2, 3: first / second SSP-RK2 stage of the src/sw2d driver instead (the state is read from q[cur], the result
+// goes to q[cur^1], which in the second stage still holds q^n, and the buffers swap).  last: the next RHS evaluation
+// happens at t + dt (last stage of a time step).
+static int enqueue_stage(bdg_sw2d *s, int write_rhs, double *rhs_out, double a, double b, int slot, int rk2 = 0, int last = 0) {
   if (s->v.full && !s->v.H) return fail(s, BDG_E_INVALID, "sources=1 needs bdg_sw2d_set_bathymetry first");
   double *q = s->q[s->cur];
   const int K = s->v.K;
   const bool halo = s->comm && s->n_nbr > 0;
   // interior/cut split rounded down to a whole 32-element tile of the fused kernel: computing a few interior
   // elements with the cut launch is harmless and keeps both launches free of partially active tiles
-  const bool fused = use_fused(s) && !rk2;
+  const bool fused = use_fused(s);
   const int ksplit = halo ? (fused ? s->n_interior / 32 * 32 : s->n_interior) : K;
+  FusedStage fs;
+  fs.mode = rk2 ? rk2 : 1; fs.slot_next = -1; fs.slot_zero = -1; fs.last_stage = last;
   int rc;
   cudaError_t e;
   if (halo && s->peer_ok && fused) {
@@ -838,7 +847,7 @@ static int enqueue_stage(bdg_sw2d *s, int write_rhs, double *rhs_out, double a, 
     }
     if (write_rhs) {  // bdg_sw2d_rhs: one evaluation, nothing to overlap
       if ((e = launch_wait_epoch(s, s->epoch)) != cudaSuccess) return fail(s, BDG_E_CUDA, "wait: %s", cudaGetErrorString(e));
-      if ((e = launch_fused_stage(s, q, qo, s->res, 0, K, a, b, write_rhs, rhs_out, slot)) != cudaSuccess)
+      if ((e = launch_fused_stage(s, q, qo, s->res, 0, K, a, b, write_rhs, rhs_out, slot, &fs)) != cudaSuccess)
         return fail(s, BDG_E_CUDA, "fused(rhs): %s", cudaGetErrorString(e));
       return BDG_OK;
     }
@@ -851,12 +860,12 @@ static int enqueue_stage(bdg_sw2d *s, int write_rhs, double *rhs_out, double a, 
     CU(cudaStreamWaitEvent(s->comm_stream, s->ev_pack, 0));
     s->stream = s->comm_stream;
     e = launch_wait_epoch(s, s->epoch);
-    if (e == cudaSuccess) e = launch_fused_stage(s, q, qo, s->res, ksplit, K, a, b, 0, nullptr, slot);
+    if (e == cudaSuccess) e = launch_fused_stage(s, q, qo, s->res, ksplit, K, a, b, 0, nullptr, slot, &fs);
     if (e == cudaSuccess) e = launch_put(s, qo, s->cur ^ 1, ++s->epoch, 0);
     s->stream = main_stream;
     if (e != cudaSuccess) return fail(s, BDG_E_CUDA, "fused(cut)/put: %s", cudaGetErrorString(e));
     CU(cudaEventRecord(s->ev_recv, s->comm_stream));
-    if ((e = launch_fused_stage(s, q, qo, s->res, 0, ksplit, a, b, 0, nullptr, slot)) != cudaSuccess)
+    if ((e = launch_fused_stage(s, q, qo, s->res, 0, ksplit, a, b, 0, nullptr, slot, &fs)) != cudaSuccess)
       return fail(s, BDG_E_CUDA, "fused(interior): %s", cudaGetErrorString(e));
     CU(cudaStreamWaitEvent(main_stream, s->ev_recv, 0));
     if (!write_rhs) s->cur ^= 1;
@@ -868,6 +877,35 @@ static int enqueue_stage(bdg_sw2d *s, int write_rhs, double *rhs_out, double a, 
   }
   s->ghost_valid = 0;  // this path refreshes the ghosts itself (NCCL) and may update q in place
   if ((rc = halo_begin(s, q))) return rc;
+  if (fused && s->v.full) {
+    // Fused full physics (sw2d_fused.cu, FULL): ONE launch per stage.  The global LF speed of the state is carried over
+    // from the previous stage's epilogue (three rotating slots: this stage's, the next one's, the one being re-armed);
+    // only the first evaluation after a state change, and bdg_sw2d_rhs, run the reduction launch k_speed.
+    if ((rc = halo_wait(s))) return rc;  // the star states of cut faces and the speed reduction need every ghost
+    if (s->delta_dirty) {
+      if ((e = fused_build_delta(s)) != cudaSuccess) return fail(s, BDG_E_CUDA, "star-state table: %s", cudaGetErrorString(e));
+      s->delta_dirty = 0;
+    }
+    if (!s->lam_valid || write_rhs) {
+      CU(cudaMemsetAsync(s->d_scal + S_LAM0, 0, 3 * sizeof(double), s->stream));
+      s->lam_slot = 0;
+      if ((e = launch_generic_speed(s, q, S_LAM0)) != cudaSuccess) return fail(s, BDG_E_CUDA, "speed: %s", cudaGetErrorString(e));
+      if ((rc = allreduce_max(s, s->d_scal + S_LAM0))) return rc;
+    }
+    const int A = S_LAM0 + s->lam_slot, B = S_LAM0 + (s->lam_slot + 1) % 3, C3 = S_LAM0 + (s->lam_slot + 2) % 3;
+    if (!write_rhs) { fs.slot_next = B; fs.slot_zero = C3; }
+    if ((e = launch_fused_stage(s, q, s->q[s->cur ^ 1], s->res, 0, K, a, b, write_rhs, rhs_out, A, &fs)) != cudaSuccess)
+      return fail(s, BDG_E_CUDA, "fused(full): %s", cudaGetErrorString(e));
+    if (write_rhs) {
+      s->lam_valid = 0;
+    } else {
+      if ((rc = allreduce_max(s, s->d_scal + B))) return rc;
+      s->lam_slot = (s->lam_slot + 1) % 3;
+      s->lam_valid = 1;
+      s->cur ^= 1;
+    }
+    return BDG_OK;
+  }
   if (s->v.lf_global) {  // needs every trace, ghosts included: no overlap in this mode
     if ((rc = halo_wait(s))) return rc;
     if ((e = launch_generic_speed(s, q, slot)) != cudaSuccess) return fail(s, BDG_E_CUDA, "speed: %s", cudaGetErrorString(e));
@@ -875,11 +913,11 @@ static int enqueue_stage(bdg_sw2d *s, int write_rhs, double *rhs_out, double a, 
   }
   if (fused) {
     double *qo = s->q[s->cur ^ 1];
-    if ((e = launch_fused_stage(s, q, qo, s->res, 0, ksplit, a, b, write_rhs, rhs_out, slot)) != cudaSuccess)
+    if ((e = launch_fused_stage(s, q, qo, s->res, 0, ksplit, a, b, write_rhs, rhs_out, slot, &fs)) != cudaSuccess)
       return fail(s, BDG_E_CUDA, "fused(interior): %s", cudaGetErrorString(e));
     if (ksplit < K) {
       if ((rc = halo_wait(s))) return rc;
-      if ((e = launch_fused_stage(s, q, qo, s->res, ksplit, K, a, b, write_rhs, rhs_out, slot)) != cudaSuccess)
+      if ((e = launch_fused_stage(s, q, qo, s->res, ksplit, K, a, b, write_rhs, rhs_out, slot, &fs)) != cudaSuccess)
         return fail(s, BDG_E_CUDA, "fused(cut): %s", cudaGetErrorString(e));
     } else if (halo && !s->v.lf_global) {
       if ((rc = halo_wait(s))) return rc;
@@ -950,7 +988,7 @@ extern "C" int bdg_sw2d_step(bdg_sw2d *s, int32_t nsteps, double dt) {
   for (int st = 0; st < nsteps; ++st) {
     if (adaptive && (rc = enqueue_dt(s))) return rc;
     for (int stage = 0; stage < 5; ++stage) {  // reference src/advec1d/main.cpp:92-102
-      if ((rc = enqueue_stage(s, 0, nullptr, rk4a[stage], rk4b[stage], slot))) return rc;
+      if ((rc = enqueue_stage(s, 0, nullptr, rk4a[stage], rk4b[stage], slot, 0, stage == 4))) return rc;
       slot ^= 1;
     }
     if (device_time) {
@@ -983,7 +1021,7 @@ extern "C" int bdg_sw2d_step_ssprk2(bdg_sw2d *s, int32_t nsteps, double dt) {
   for (int st = 0; st < nsteps; ++st) {
     if (adaptive && (rc = enqueue_dt(s))) return rc;
     for (int stage = 0; stage < 2; ++stage) {
-      if ((rc = enqueue_stage(s, 0, nullptr, 0.0, 1.0, slot, 2 + stage))) return rc;
+      if ((rc = enqueue_stage(s, 0, nullptr, 0.0, 1.0, slot, 2 + stage, stage == 1))) return rc;
       slot ^= 1;
     }
     if (device_time) {
@@ -1033,6 +1071,7 @@ extern "C" int bdg_sw2d_limit_positivity(bdg_sw2d *s) {
   cudaError_t e = launch_positivity_limiter(s, s->q[s->cur]);
   if (e != cudaSuccess) return fail(s, BDG_E_CUDA, "limiter: %s", cudaGetErrorString(e));
   s->ghost_valid = 0;  // neighbours hold traces of the unlimited state
+  s->lam_valid = 0;
   return BDG_OK;
 }
 
@@ -1095,6 +1134,7 @@ extern "C" int bdg_sw2d_set_variant(bdg_sw2d *s, int32_t variant) {
   if (variant == 2 && !s->fused_ok) return fail(s, BDG_E_UNSUPPORTED, "fused path unavailable for this context (needs affine triangles, uniform face tags, no filter, supported order)");
   s->variant = variant;
   s->ghost_valid = 0;
+  s->lam_valid = 0;
   return BDG_OK;
 }
 extern "C" int bdg_sw2d_get_variant(const bdg_sw2d *s) { return s ? (use_fused(s) ? 2 : 1) : -1; }

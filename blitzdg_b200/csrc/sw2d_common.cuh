@@ -15,7 +15,8 @@ struct ncclComm;
 
 // scalar slots kept on the device (no host round trips inside bdg_sw2d_step)
 // S_HALO_TIMEOUT is sticky: set by k_wait_epoch when a neighbour's epoch never arrives, read (never cleared) by bdg_sw2d_check
-enum { S_T = 0, S_DT = 1, S_GMAX0 = 2, S_GMAX1 = 3, S_DTMAX = 4, S_ETAMAX = 5, S_NANFLAG = 6, S_HALO_TIMEOUT = 7, S_COUNT = 8 };
+// S_LAM0..2: global LF speed slots of the fused full-physics path (this stage's / the next stage's / the one being re-armed)
+enum { S_T = 0, S_DT = 1, S_GMAX0 = 2, S_GMAX1 = 3, S_DTMAX = 4, S_ETAMAX = 5, S_NANFLAG = 6, S_HALO_TIMEOUT = 7, S_LAM0 = 8, S_LAM1 = 9, S_LAM2 = 10, S_COUNT = 16 };
 
 // everything a kernel needs, passed by value
 struct Sw2dView {
@@ -89,6 +90,9 @@ struct bdg_sw2d {
   double *d_vfrag;      // operator fragments of the generic DMMA volume kernel (sw2d_volume_dmma.cu), NULL if Np > 64
   void *fused_ops;      // operator fragments of the fused path (device), NULL if unsupported
   int fused_ok;
+  int delta_dirty;      // fused full physics: the star-state table must be rebuilt from the bathymetry before the next launch
+  int lam_valid;        // ... and scal[S_LAM0 + lam_slot] holds the global LF speed of the live state
+  int lam_slot;
   double t;             // host mirror of the time (exact for fixed dt)
   int adaptive_used;
   // halo
@@ -145,8 +149,15 @@ cudaError_t launch_wait_epoch(bdg_sw2d *s, unsigned long long epoch);
 int fused_supported(const bdg_sw2d *s);
 cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const double *Lift, const int32_t *vmapP,
                           const uint8_t *facetag, const int32_t *fmask);  // host arrays of create; sets s->fused_ops when the path applies
+struct FusedStage {   // stepper form and global-LF bookkeeping of one fused launch (NULL = LSERK4 stage, nothing carried)
+  int mode;           // 1 LSERK4, 2 / 3 first / second SSP-RK2 stage (stepper_value above)
+  int slot_next;      // full mode: scal slot collecting the global LF speed of the new state, -1 = none
+  int slot_zero;      // ... and the slot to re-arm, -1 = none
+  int last_stage;     // the next RHS evaluation is at t + dt
+};
 cudaError_t launch_fused_stage(bdg_sw2d *s, const double *q_in, double *q_out, double *res, int k0, int k1, double a,
-                               double b, int write_rhs, double *rhs_out, int slot);
+                               double b, int write_rhs, double *rhs_out, int slot, const FusedStage *fs = nullptr);
+cudaError_t fused_build_delta(bdg_sw2d *s);  // star-state table of the fused full-physics path from v.H (device)
 void fused_release(bdg_sw2d *s);
 // generic path, second launch on the fp64 tensor pipe (sw2d_volume_dmma.cu)
 cudaError_t volume_dmma_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const double *Lift);

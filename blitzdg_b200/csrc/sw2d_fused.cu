@@ -154,18 +154,30 @@ struct Cfg {
   static constexpr uint32_t txQ = sizeof(double) * TNP;  // one field plane of a tile
   static constexpr uint32_t txMeta = sizeof(uint32_t) * kTile * NFN + sizeof(double) * kTile * kAW;
   static constexpr size_t sizeA = A_REGS ? 0 : sizeof(double) * MB * KB * 32;
-  // per tile buffer: Q[3][PS], Aff[kTile][13], Lm[kTile][NFN]; CTA-wide: R[3][TNP], Fl[4][PS], A, barriers
-  static constexpr size_t buf_bytes(int G) { return sizeof(double) * 3 * (TNP + G) + sizeof(double) * kTile * kAW + sizeof(uint32_t) * kTile * NFN; }
-  static constexpr size_t total(int nbuf, int G) { return nbuf * buf_bytes(G) + sizeof(double) * 3 * TNP + sizeof(double) * 4 * (TNP + G) + sizeA + 64 + 128 + (nbuf > 1 ? nbuf * sizeof(int32_t) * G : 0); }
+  static constexpr uint32_t txDl = sizeof(double) * kTile * NFN;  // full mode: one static double per face slot of the tile
+  // per tile buffer: Q[3][PS], Aff[kTile][13], Lm[kTile][NFN] (+ Dl[kTile][NFN] in full mode); CTA-wide: R[3][TNP],
+  // Fl[4][PS] (full mode: Fl[4][TNP] -- nodal fluxes and 1/h of the OWN nodes only, the traces are re-evaluated from their
+  // star states), A, barriers
+  __host__ __device__ static constexpr size_t buf_bytes(int G, bool full) {
+    return sizeof(double) * 3 * (TNP + G) + sizeof(double) * kTile * kAW + sizeof(uint32_t) * kTile * NFN + (full ? txDl : 0);
+  }
+  static constexpr size_t total(int nbuf, int G, bool full = false) {
+    return nbuf * buf_bytes(G, full) + sizeof(double) * 3 * TNP + sizeof(double) * 4 * (TNP + (full ? 0 : G)) + sizeA + 64 + 128 +
+           (nbuf > 1 ? nbuf * sizeof(int32_t) * G : 0);
+  }
   // Ghost slots of the persistent kernel's tile buffers: a COMPILE-TIME constant (every plane offset folds into the
   // LDS/STS immediates), the largest multiple of 8 that keeps `ctas` CTAs per SM (228 KB per SM, 1 KB reserved per
   // CTA); tiles with more ghosts run in the edge kernel.  Phase-1 work follows a tile's own ghost count, not this.
-  static constexpr int gfit(int ctas) {
-    const long budget = 233472 / ctas - 1024, fixed = (long)total(2, 0), per8 = (long)(total(2, 8) - total(2, 0));
+  static constexpr int gfit(int ctas, bool full) {
+    const long budget = 233472 / ctas - 1024, fixed = (long)total(2, 0, full), per8 = (long)(total(2, 8, full) - total(2, 0, full));
     const long g = budget > fixed ? (budget - fixed) / per8 * 8 : 0;
     return (int)(g > 600 ? 600 : g);
   }
-  static constexpr int GFIT = gfit(BDG_MINBLOCKS) >= 96 ? gfit(BDG_MINBLOCKS) : (gfit(2) >= 96 ? gfit(2) : gfit(1));
+  static constexpr int gfit_best(bool full) {
+    return gfit(BDG_MINBLOCKS, full) >= 96 ? gfit(BDG_MINBLOCKS, full) : (gfit(2, full) >= 96 ? gfit(2, full) : gfit(1, full));
+  }
+  static constexpr int GFIT = gfit_best(false);
+  static constexpr int GFIT_FULL = gfit_best(true);
 };
 
 struct StageArgs {
@@ -189,21 +201,30 @@ struct StageArgs {
   unsigned int *sched;    // persistent kernel: {next list position to claim, CTAs finished} of this stream's launches
   long long *prof;        // BDG_PHASEPROF builds: [kWarps][12] cycle sums
   double a, b;            // LSERK4 stage coefficients
+  // full physics / stepper forms
+  const double *dl;       // full mode: [ntiles_all*kTile][NFN] static double per face slot: H+ - H- (Out faces: H-), see k_build_delta
+  const double *r_src;    // what the R planes are loaded from: res (LSERK4, a != 0), q^n (second SSP-RK2 stage), NULL (nothing)
+  int mode;               // stepper_value(): 1 LSERK4 stage, 2 / 3 first / second SSP-RK2 stage (sw2d_common.cuh)
+  int store_res;          // R planes are written back to res (LSERK4)
+  int slot_next;          // full mode: scal slot that collects the global LF speed of the NEW state (< 0: none)
+  int slot_zero;          // ... and the slot to re-arm for the stage after the next (< 0: none)
+  int last_stage;         // the next RHS evaluation happens at t + dt (tidal forcing of the Out faces in the speed above)
 };
 
-template <int NP, int NFP>
+template <int NP, int NFP, bool FULL = false>
 struct Smem {
   using C = Cfg<NP, NFP>;
   unsigned char *base;
   int nbuf, G;
   __device__ int PS() const { return C::TNP + G; }
-  __device__ size_t bufb() const { return sizeof(double) * 3 * PS() + sizeof(double) * kTile * kAW + sizeof(uint32_t) * kTile * C::NFN; }
+  __device__ size_t bufb() const { return C::buf_bytes(G, FULL); }
   __device__ double *Q(int b) const { return reinterpret_cast<double *>(base + b * bufb()); }
   __device__ double *Aff(int b) const { return Q(b) + 3 * PS(); }
   __device__ uint32_t *Lm(int b) const { return reinterpret_cast<uint32_t *>(Aff(b) + kTile * kAW); }
+  __device__ double *Dl(int b) const { return reinterpret_cast<double *>(Lm(b) + kTile * C::NFN); }  // FULL only (8-byte aligned: kTile*NFN is even)
   __device__ double *R() const { return reinterpret_cast<double *>(base + nbuf * bufb()); }
   __device__ double *Fl() const { return R() + 3 * C::TNP; }
-  __device__ double *A() const { return Fl() + 4 * PS(); }
+  __device__ double *A() const { return Fl() + 4 * (FULL ? C::TNP : PS()); }
   __device__ uint64_t *Bar() const { return reinterpret_cast<uint64_t *>(reinterpret_cast<unsigned char *>(A()) + C::sizeA); }
   __device__ int4 *Ring() const { return reinterpret_cast<int4 *>(Bar() + 8); }  // 8 tile records (persistent kernel)
   __device__ int32_t *Ids(int b) const { return reinterpret_cast<int32_t *>(Ring() + 8) + b * G; }  // ghost sources of the tile after buffer b's
@@ -212,8 +233,8 @@ struct Smem {
 // Phase 1 for U nodes of one thread at once (j, j + kThreads, ...): the U dependency chains (reciprocal, two
 // square roots) are independent straight-line code, so the scheduler interleaves them.  Indices behind the
 // tile's last node are clamped: such lanes recompute (and re-store) the last node's values.
-template <int U>
-__device__ __forceinline__ void phase1_nodes(const double *__restrict__ sQ, double *__restrict__ sFl, int PS, int j0, int last, double g,
+template <int U, bool FULL>
+__device__ __forceinline__ void phase1_nodes(const double *__restrict__ sQ, double *__restrict__ sFl, int PS, int FPS, int j0, int last, double g,
                                              double half_g) {
   int j[U];
   double h[U], hu[U], hv[U];
@@ -227,11 +248,20 @@ __device__ __forceinline__ void phase1_nodes(const double *__restrict__ sQ, doub
 #pragma unroll
   for (int u = 0; u < U; ++u) {
     const double r = frcp(h[u]), uu = hu[u] * r, vv = hv[u] * r, gh2 = (half_g * h[u]) * h[u];
-    sFl[j[u]] = fma(hu[u], uu, gh2);            // F2
-    sFl[PS + j[u]] = hu[u] * vv;                // G2 = F3
-    sFl[2 * PS + j[u]] = fma(hv[u], vv, gh2);   // G3
-    sFl[3 * PS + j[u]] = fsqrt(fma(uu, uu, fma(vv, vv, 1e-300))) + fsqrt(g * h[u]);
+    sFl[j[u]] = fma(hu[u], uu, gh2);             // F2
+    sFl[FPS + j[u]] = hu[u] * vv;                // G2 = F3
+    sFl[2 * FPS + j[u]] = fma(hv[u], vv, gh2);   // G3
+    if (FULL)
+      sFl[3 * FPS + j[u]] = r;                   // 1/h for the source terms of the epilogue
+    else
+      sFl[3 * FPS + j[u]] = fsqrt(fma(uu, uu, fma(vv, vv, 1e-300))) + fsqrt(g * h[u]);
   }
+}
+
+// tidal free surface of the Out faces at time t (main.cpp:352): amp cos(om t) (tanh(ramp (t - T)) + 1) / 2
+__device__ __forceinline__ double tide_level(const Sw2dView &v, double t) {
+  const double om = 2.0 * 3.1415926535897932 / v.tide_period;
+  return v.tide_amp * cos(om * t) * 0.5 * (tanh(v.tide_ramp * (t - v.tide_period)) + 1);
 }
 
 // The arithmetic of one tile that sits in shared memory (A1-A13 of SURVEY.md Appendix A).  sQ: [3][PS] own +
@@ -240,15 +270,22 @@ __device__ __forceinline__ void phase1_nodes(const double *__restrict__ sQ, doub
 // optional wait on the res barrier before phase 3; the caller makes the tile visible first.
 // The operator fragments (Areg / sA) arrive pre-multiplied by dt (by 1 in write_rhs mode), so the accumulators
 // hold dt*RHS and the new res is a*res + acc.  All three phases are branch-free on their hot path: padding slots are
-// clamped to a valid neighbour (their operator columns are zero), the wall reflection is a rare warp-level
-// fix-up pass, and every thread keeps several independent dependency chains in flight.
-template <int NP, int NFP>
+// clamped to a valid neighbour (their operator columns are zero), boundary faces are a rare warp-level
+// variant, and every thread keeps several independent dependency chains in flight.
+//
+// FULL = the physics of src/sw2d/main.cpp:279-484: star states from ONE static double per face slot (sDl: H+ - H-; on Out
+// faces, where that is 0, H- for the tidal hP), every trace flux re-evaluated from its star state, global LF speed from
+// scal[p.slot], bed-slope / drag / Coriolis sources in the epilogue (Hx, Hy straight from global memory: a thread's
+// C fragment covers 4 nodes), and the global LF speed of the NEW state collected for the next stage (lam_next).
+template <int NP, int NFP, bool FULL>
 __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs &p, double *__restrict__ sQ, double *__restrict__ sR,
-                                             const double *__restrict__ sAff, const uint32_t *__restrict__ sLm, double *__restrict__ sFl,
-                                             const double *__restrict__ sA, const double *Areg, const int *fm, int PS, int nnodes, long long kt0,
-                                             bool need_res, uint64_t *bar_res, uint32_t res_parity PROF_ARGS) {
+                                             const double *__restrict__ sAff, const uint32_t *__restrict__ sLm, const double *__restrict__ sDl,
+                                             double *__restrict__ sFl, const double *__restrict__ sA, const double *Areg, const int *fm, int PS,
+                                             int nnodes, long long kt0, bool need_res, uint64_t *bar_res, uint32_t res_parity, double dtv,
+                                             double tide, double tide_next, double &lam_next PROF_ARGS) {
   using C = Cfg<NP, NFP>;
   constexpr int NFN = C::NFN, NPB = C::NPB, NFB = C::NFB, KB = C::KB, MB = C::MB, TNP = C::TNP;
+  const int FPS = FULL ? TNP : PS;  // stride of the flux planes
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int c = lane >> 2, t = lane & 3;
   const int e = w + 4 * (c < 4 ? c : (c ^ 1));  // my element (B-fragment column c); E(c) keeps B and C accesses conflict-free
@@ -256,15 +293,16 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   const double g = v.g, half_g = 0.5 * v.g;
   const double *af = sAff + e * kAW;
 
-  // ---- phase 1: nodal fluxes and wave speed at own and ghost nodes (A6, A7), flat mapping ------------------
+  // ---- phase 1: nodal fluxes (+ wave speed / 1/h) at own (and, simple mode, ghost) nodes (A6, A7), flat mapping ----
   {
-    const int wbase = w * 32, last = nnodes - 1;
+    const int nn = FULL ? TNP : nnodes;
+    const int wbase = w * 32, last = nn - 1;
     int i = 0;
-    for (; wbase + (i + 2) * kThreads < nnodes; i += 3) phase1_nodes<3>(sQ, sFl, PS, threadIdx.x + i * kThreads, last, g, half_g);
-    if (wbase + (i + 1) * kThreads < nnodes)
-      phase1_nodes<2>(sQ, sFl, PS, threadIdx.x + i * kThreads, last, g, half_g);
-    else if (wbase + i * kThreads < nnodes)
-      phase1_nodes<1>(sQ, sFl, PS, threadIdx.x + i * kThreads, last, g, half_g);
+    for (; wbase + (i + 2) * kThreads < nn; i += 3) phase1_nodes<3, FULL>(sQ, sFl, PS, FPS, threadIdx.x + i * kThreads, last, g, half_g);
+    if (wbase + (i + 1) * kThreads < nn)
+      phase1_nodes<2, FULL>(sQ, sFl, PS, FPS, threadIdx.x + i * kThreads, last, g, half_g);
+    else if (wbase + i * kThreads < nn)
+      phase1_nodes<1, FULL>(sQ, sFl, PS, FPS, threadIdx.x + i * kThreads, last, g, half_g);
   }
   PROF_T(2);
   compute_sync();
@@ -285,13 +323,58 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
     spdP = fsqrt(fma(u, u, fma(vv, vv, 1e-300))) + fsqrt(g * hM);
   };
   uint32_t word[NFB];
-  uint32_t wallmask = 0;
+  uint32_t bcmask = 0;  // positions whose face carries a BC tag (simple mode: Wall only)
 #pragma unroll
   for (int kb = 0; kb < NFB; ++kb) {
     word[kb] = sLm[e * NFN + (fm[kb] >> 20)];
-    wallmask |= ((word[kb] >> 16) == 3u ? 1u : 0u) << kb;
+    const uint32_t tag = word[kb] >> 16;
+    bcmask |= ((FULL ? (tag == 3u || tag == 2u) : tag == 3u) ? 1u : 0u) << kb;
   }
-  const bool any_wall = __any_sync(0xffffffffu, wallmask != 0u);
+  const bool any_wall = __any_sync(0xffffffffu, bcmask != 0u);
+  double sfl[NFB][3];  // Fscale * dFlux_i at my slots = LIFT-part B fragments
+  if constexpr (FULL) {
+    const double lamg = v.scal[p.slot];  // global LF speed of this state (main.cpp:413-414), from the previous stage's epilogue or k_speed
+    const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+    auto pass_f = [&](auto with_bc) {
+#pragma unroll
+      for (int kb = 0; kb < NFB; ++kb) {
+        const int f = (C::FACE_BLOCKS && kb < 3) ? kb : (fm[kb] >> 16) & 15;
+        const int m = eo + (fm[kb] & 0xffff), r = word[kb] & 0xffffu;
+        const double nx = af[4 + 3 * f], ny = af[5 + 3 * f], hfs = af[6 + 3 * f];  // (nx, ny, 1) * Fscale/2
+        double hM = sQ[m], huM = sQ[PS + m], hvM = sQ[2 * PS + m];
+        double hP = sQ[r], huP = sQ[PS + r], hvP = sQ[2 * PS + r];
+        double dlt = sDl[e * NFN + (fm[kb] >> 20)];
+        if (decltype(with_bc)::value && ((bcmask >> kb) & 1u)) {
+          if ((word[kb] >> 16) == 3u) {  // Wall (main.cpp:340-345)
+            const double ih = frcp(hfs), ux = nx * ih, uy = ny * ih, d = huM * ux + hvM * uy;
+            hP = hM;
+            huP = fma(-2.0 * ux, d, huM);
+            hvP = fma(-2.0 * uy, d, hvM);
+          } else {  // Out (main.cpp:348-353): the slot carries H-
+            hP = dlt + tide;
+            huP = huM; hvP = hvM;
+          }
+          dlt = 0.0;
+        }
+        // star states (main.cpp:355-368): h-* = max(0, h- + min(H+ - H-, 0)), h+* = max(0, h+ - max(H+ - H-, 0)); the momenta
+        // keep their values (hu* = h* (hu / h*) after h = h*), a dry trace poisons them like the reference's 0/0
+        const double hMs = fmax(0.0, hM + fmin(dlt, 0.0)), hPs = fmax(0.0, hP - fmax(dlt, 0.0));
+        if (!(hMs > 0.0)) huM = hvM = qnan;
+        if (!(hPs > 0.0)) huP = hvP = qnan;
+        const double rM = frcp(hMs), rP = frcp(hPs);
+        const double uM = huM * rM, vM = hvM * rM, uP = huP * rP, vP = hvP * rP;
+        const double pM = (half_g * hMs) * hMs, pP = (half_g * hPs) * hPs;
+        const double dF2 = fma(huM, uM, pM) - fma(huP, uP, pP), dG2 = huM * vM - huP * vP, dG3 = fma(hvM, vM, pM) - fma(hvP, vP, pP);
+        const double l = hfs * lamg;
+        const double dh = hMs - hPs, dhu = huM - huP, dhv = hvM - hvP;
+        sfl[kb][0] = fma(-l, dh, fma(dhu, nx, dhv * ny));
+        sfl[kb][1] = fma(-l, dhu, fma(dF2, nx, dG2 * ny));
+        sfl[kb][2] = fma(-l, dhv, fma(dG2, nx, dG3 * ny));
+      }
+    };
+    if (any_wall) pass_f(std::true_type{}); else pass_f(std::false_type{});
+  } else {
+  const uint32_t wallmask = bcmask;
   double lam0 = 0.0, lam1 = 0.0, lam2 = 0.0;  // per-face max speed (scalars: a runtime face index must not spill)
   if (v.lf_global) {
     lam0 = lam1 = lam2 = v.scal[p.slot];
@@ -330,7 +413,6 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
     lam1 = dmax(lam1, __shfl_xor_sync(0xffffffffu, lam1, 2));
     lam2 = dmax(lam2, __shfl_xor_sync(0xffffffffu, lam2, 2));
   }
-  double sfl[NFB][3];  // Fscale * dFlux_i at my slots = LIFT-part B fragments
   auto pass_b = [&](auto with_wall) {
 #pragma unroll
   for (int kb = 0; kb < NFB; ++kb) {
@@ -355,6 +437,7 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   }
   };
   if (any_wall) pass_b(std::true_type{}); else pass_b(std::false_type{});
+  }
   PROF_T(4);
   compute_sync();  // all '+' lookups into sQ/sFl are done: the tile may now be updated in place
   PROF_T(5);
@@ -364,6 +447,29 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   const int c0 = 2 * t, c1 = 2 * t + 1;
   const int e0 = w + 4 * (c0 < 4 ? c0 : (c0 ^ 1));  // C fragment column 2t   -> element E(2t)
   const int e1 = w + 4 * (c1 < 4 ? c1 : (c1 ^ 1));  // C fragment column 2t+1 -> element E(2t+1)
+  // full mode: static Hx, Hy (and the sponge coefficient) of my 4 C-fragment nodes, fetched now, used after the contraction
+  double sHx[MB][2], sHy[MB][2], sSg[MB][2];
+  if constexpr (FULL) {
+#pragma unroll
+    for (int rb = 0; rb < MB; ++rb)
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        const int n = min(8 * rb + gr, NP - 1);
+        const long long gm = min(kt0 + (cc ? e1 : e0), (long long)v.K - 1) * NP + n;
+        sHx[rb][cc] = __ldg(v.Hx + gm);
+        sHy[rb][cc] = __ldg(v.Hy + gm);
+      }
+  }
+  const bool sponge = p.mode != 1 && v.sponge != nullptr;
+  if (sponge) {
+#pragma unroll
+    for (int rb = 0; rb < MB; ++rb)
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        const int n = min(8 * rb + gr, NP - 1);
+        sSg[rb][cc] = __ldg(v.sponge + min(kt0 + (cc ? e1 : e0), (long long)v.K - 1) * NP + n);
+      }
+  }
   double acc[3][MB][2];
 #pragma unroll
   for (int rb = 0; rb < MB; ++rb)
@@ -372,7 +478,7 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
 #pragma unroll
   for (int kb = 0; kb < NPB; ++kb) {
     const int n = eo + min(4 * kb + t, NP - 1);  // padding rows of B meet zero columns of A
-    const double hu = sQ[PS + n], hv = sQ[2 * PS + n], F2 = sFl[n], G2 = sFl[PS + n], G3 = sFl[2 * PS + n];
+    const double hu = sQ[PS + n], hv = sQ[2 * PS + n], F2 = sFl[n], G2 = sFl[FPS + n], G3 = sFl[2 * FPS + n];
     double ba[3], bb[3];
     ba[0] = fma(rx, hu, ry * hv); bb[0] = fma(sx, hu, sy * hv);
     ba[1] = fma(rx, F2, ry * G2); bb[1] = fma(sx, F2, sy * G2);
@@ -401,6 +507,19 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   if (bar_res) mbar_wait(bar_res, res_parity);
   PROF_T(6);
   __syncwarp();  // every lane's B-fragment reads of this warp's elements precede the in-place update below
+  // sources (main.cpp:460-483) at my C-fragment nodes: g h Hx - CD u |u| + f hv  and  g h Hy - CD v |u| - f hu, times dt
+  if constexpr (FULL) {
+#pragma unroll
+    for (int rb = 0; rb < MB; ++rb)
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        const int o = (cc ? e1 : e0) * NP + min(8 * rb + gr, NP - 1);
+        const double h = sQ[o], hu = sQ[PS + o], hv = sQ[2 * PS + o], r = sFl[3 * FPS + o];
+        const double u = hu * r, vv = hv * r, nu = fsqrt(fma(u, u, fma(vv, vv, 1e-300))), gh = g * h;
+        acc[1][rb][cc] = fma(dtv, fma(v.fcor, hv, fma(-v.CD * u, nu, gh * sHx[rb][cc])), acc[1][rb][cc]);
+        acc[2][rb][cc] = fma(dtv, fma(-v.fcor, hu, fma(-v.CD * vv, nu, gh * sHy[rb][cc])), acc[2][rb][cc]);
+      }
+  }
   // epilogue: rows n = 8*rb + gr of elements e0, e1; acc = a*res + dt*rhs (stage mode) or rhs (write_rhs mode)
   if (p.write_rhs) {
 #pragma unroll
@@ -415,24 +534,72 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
         }
       }
     }
-  } else {
+    return;
+  }
 #pragma unroll
-    for (int rb = 0; rb < MB; ++rb) {
-      const int n = 8 * rb + gr;
-      if (n < NP) {
+  for (int rb = 0; rb < MB; ++rb) {
+    const int n = 8 * rb + gr;
+    if (n < NP) {
 #pragma unroll
-        for (int i = 0; i < 3; ++i) {
+      for (int i = 0; i < 3; ++i) {
 #pragma unroll
-          for (int cc = 0; cc < 2; ++cc) {
-            const int o = (cc ? e1 : e0) * NP + n;
+        for (int cc = 0; cc < 2; ++cc) {
+          const int o = (cc ? e1 : e0) * NP + n;
+          if (p.mode == 1) {  // LSERK4 stage (src/advec1d/main.cpp:98,101)
             const double rs = need_res ? fma(p.a, sR[i * TNP + o], acc[i][rb][cc]) : acc[i][rb][cc];
             sR[i * TNP + o] = rs;
             sQ[i * PS + o] = fma(p.b, rs, sQ[i * PS + o]);
+          } else {  // SSP-RK2 stages of the src/sw2d driver (main.cpp:217-219, 230-232) + sponge relaxation (:222-224, :235-236)
+            double val = p.mode == 2 ? sQ[i * PS + o] + acc[i][rb][cc] : 0.5 * ((sR[i * TNP + o] + sQ[i * PS + o]) + acc[i][rb][cc]);
+            if (sponge && i > 0 && sSg[rb][cc] != 0.0) val = val * frcp(fma(sSg[rb][cc] * val, val, 1.0));
+            sQ[i * PS + o] = val;
           }
         }
       }
     }
   }
+  // full mode: global LF speed of the NEW state at my face slots (main.cpp:397-414), for the next stage.  An interior
+  // face's '+' side is the '-' side of the neighbour (same star state: its H+ - H- is minus mine), which that
+  // neighbour -- another tile, or another rank before the all-reduce -- evaluates; BC faces take both sides here.
+  if constexpr (FULL) {
+    if (p.slot_next >= 0) {
+      __syncwarp();  // the new values of my element were written by other lanes of this warp
+      const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+#pragma unroll
+      for (int kb = 0; kb < NFB; ++kb) {
+        const int f = (C::FACE_BLOCKS && kb < 3) ? kb : (fm[kb] >> 16) & 15;
+        const int m = eo + (fm[kb] & 0xffff);
+        const uint32_t tag = word[kb] >> 16;
+        double dlt = sDl[e * NFN + (fm[kb] >> 20)];
+        const double hM = sQ[m];
+        double huM = sQ[PS + m], hvM = sQ[2 * PS + m];
+        const double Hm = dlt;
+        if (tag == 3u || tag == 2u) dlt = 0.0;
+        const double hMs = fmax(0.0, hM + fmin(dlt, 0.0));
+        if (!(hMs > 0.0)) huM = hvM = qnan;
+        const double rM = frcp(hMs), uM = huM * rM, vM = hvM * rM;
+        double sp = fsqrt(fma(uM, uM, fma(vM, vM, 1e-300))) + fsqrt(g * hMs);
+        if (tag == 3u) {  // wall: reflected momentum over the same depth
+          const double ih = frcp(af[6 + 3 * f]), ux = af[4 + 3 * f] * ih, uy = af[5 + 3 * f] * ih, d = huM * ux + hvM * uy;
+          const double uP = fma(-2.0 * ux, d, huM) * rM, vP = fma(-2.0 * uy, d, hvM) * rM;
+          sp = dmax(sp, fsqrt(fma(uP, uP, fma(vP, vP, 1e-300))) + fsqrt(g * hMs));
+        } else if (tag == 2u) {  // Out: tidal depth of the next evaluation, momentum copied
+          const double hPs = fmax(0.0, Hm + tide_next);
+          const double rP = frcp(hPs), uP = (hPs > 0.0 ? huM : qnan) * rP, vP = (hPs > 0.0 ? hvM : qnan) * rP;
+          sp = dmax(sp, fsqrt(fma(uP, uP, fma(vP, vP, 1e-300))) + fsqrt(g * hPs));
+        }
+        lam_next = dmax(lam_next, sp);
+      }
+    }
+  }
+}
+
+// end of a launch's work in one warp: fold the collected speed into scal[slot_next] (one atomic per warp and launch)
+__device__ __forceinline__ void publish_speed(const Sw2dView &v, const StageArgs &p, double lam_next) {
+  if (p.slot_next < 0) return;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) lam_next = dmax(lam_next, __shfl_xor_sync(0xffffffffu, lam_next, o));
+  if ((threadIdx.x & 31) == 0) atomicMax(reinterpret_cast<unsigned long long *>(v.scal + p.slot_next), (unsigned long long)__double_as_longlong(lam_next));
 }
 
 // per-thread constants: operator fragments scaled by `scale` (dt, or 1 in write_rhs mode), and for each of my
@@ -454,14 +621,14 @@ __device__ __forceinline__ void load_constants(const StageArgs &p, const Sw2dVie
 
 // ---- edge kernel: one tile per CTA, any tile (ragged mesh end, partially active range, write_rhs, tiles with
 // more ghost nodes than the persistent kernel's buffers hold) --------------------------------------------------
-template <int NP, int NFP>
-__global__ void __launch_bounds__(kThreads, 3) k_fused_edge(Sw2dView v, StageArgs p) {
+template <int NP, int NFP, bool FULL>
+__global__ void __launch_bounds__(kThreads, FULL ? 2 : 3) k_fused_edge(Sw2dView v, StageArgs p) {
   using C = Cfg<NP, NFP>;
   constexpr int NFN = C::NFN, TNP = C::TNP;
   extern __shared__ __align__(128) unsigned char smem[];
-  const Smem<NP, NFP> S{smem, 1, p.G};
+  const Smem<NP, NFP, FULL> S{smem, 1, p.G};
   const int PS = S.PS();
-  double *sQ = S.Q(0), *sR = S.R(), *sAff = S.Aff(0);
+  double *sQ = S.Q(0), *sR = S.R(), *sAff = S.Aff(0), *sDl = S.Dl(0);
   uint32_t *sLm = S.Lm(0);
 
   const int tid = threadIdx.x;
@@ -469,33 +636,51 @@ __global__ void __launch_bounds__(kThreads, 3) k_fused_edge(Sw2dView v, StageArg
   const long long kt0 = tile * kTile;
   const int nload = (int)min((long long)kTile, (long long)v.K - kt0);
   const bool all_active = nload == kTile && kt0 >= p.k0 && kt0 + kTile <= p.k1;
-  const bool need_res = !p.write_rhs && p.a != 0.0;
+  const bool need_res = !p.write_rhs && p.r_src != nullptr;
   const long long stride = v.stride;
   const long long base = kt0 * NP;
   const long long g0 = p.goff[tile];
   const int gc = (int)(p.goff[tile + 1] - g0);
+  if (FULL && blockIdx.x == 0 && tid == 0 && p.slot_zero >= 0) v.scal[p.slot_zero] = 0.0;
 
   // plain loads; neutral fill (h = 1) behind the mesh end; lmap is padded to whole tiles at create
   for (int x = tid; x < 3 * TNP; x += kThreads) {
     const int f = x / TNP, r = x - f * TNP;
     const bool in = r < nload * NP;
     sQ[f * PS + r] = in ? p.q_in[f * stride + base + r] : (f == 0 ? 1.0 : 0.0);
-    sR[x] = (in && need_res) ? p.res[f * stride + base + r] : 0.0;
+    sR[x] = (in && need_res) ? p.r_src[f * stride + base + r] : 0.0;
   }
   for (int x = tid; x < gc; x += kThreads) {
     const long long m = p.gflat[g0 + x];
     for (int f = 0; f < 3; ++f) sQ[f * PS + TNP + x] = p.q_in[f * stride + m];
   }
   for (int x = tid; x < kTile * NFN; x += kThreads) sLm[x] = p.lmap[kt0 * NFN + x];
+  if (FULL)
+    for (int x = tid; x < kTile * NFN; x += kThreads) sDl[x] = p.dl[kt0 * NFN + x];  // padded to whole tiles like lmap
   for (int x = tid; x < kTile * kAW; x += kThreads) sAff[x] = x < nload * kAW ? v.aff[kt0 * kAW + x] : 0.0;
   double Areg[C::A_REGS ? C::MB * C::KB : 1];
   int fm[C::NFB];
-  load_constants<NP, NFP>(p, v, Areg, S.A(), fm, p.write_rhs ? 1.0 : v.scal[S_DT]);
+  const double dtv = p.write_rhs ? 1.0 : v.scal[S_DT];
+  load_constants<NP, NFP>(p, v, Areg, S.A(), fm, dtv);
+  double tide = 0.0, tide_next = 0.0, lam_next = 0.0;
+  if (FULL) {
+    const double t = v.scal[S_T];
+    tide = tide_level(v, t);
+    tide_next = p.last_stage ? tide_level(v, t + v.scal[S_DT]) : tide;
+  }
   __syncthreads();
 
   PROF_DECL
-  compute_tile<NP, NFP>(v, p, sQ, sR, sAff, sLm, S.Fl(), S.A(), Areg, fm, PS, TNP + gc, kt0, need_res, nullptr, 0 PROF_PASS);
+  compute_tile<NP, NFP, FULL>(v, p, sQ, sR, sAff, sLm, sDl, S.Fl(), S.A(), Areg, fm, PS, TNP + gc, kt0, need_res, nullptr, 0, dtv, tide,
+                              tide_next, lam_next PROF_PASS);
   if (p.write_rhs) return;
+  if (FULL) {
+    // elements outside the active range / behind the mesh end must not contribute (their values are not stored)
+    const int lane = tid & 31, w = tid >> 5, c = lane >> 2;
+    const long long k = kt0 + w + 4 * (c < 4 ? c : (c ^ 1));
+    if (!(k >= p.k0 && k < p.k1)) lam_next = 0.0;
+    publish_speed(v, p, lam_next);
+  }
 
   if (all_active) {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -503,7 +688,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_fused_edge(Sw2dView v, StageArg
     if (tid == 0) {
       for (int f = 0; f < 3; ++f) {
         bulk_s2g(p.q_out + f * stride + base, sQ + f * PS, C::txQ);
-        bulk_s2g(p.res + f * stride + base, sR + f * TNP, C::txQ);
+        if (p.store_res) bulk_s2g(p.res + f * stride + base, sR + f * TNP, C::txQ);
       }
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
@@ -515,7 +700,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_fused_edge(Sw2dView v, StageArg
       const long long k = kt0 + r / NP;
       if (k >= p.k0 && k < p.k1) {
         p.q_out[f * stride + base + r] = sQ[f * PS + r];
-        p.res[f * stride + base + r] = sR[x];
+        if (p.store_res) p.res[f * stride + base + r] = sR[x];
       }
     }
   }
@@ -538,18 +723,20 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-template <int NP, int NFP>
+template <int NP, int NFP, bool FULL>
 __global__ void __launch_bounds__(kThreadsWS, BDG_MINBLOCKS) k_fused_persistent(Sw2dView v, StageArgs p) {
   using C = Cfg<NP, NFP>;
   constexpr int TNP = C::TNP;
+  constexpr int GF = FULL ? C::GFIT_FULL : C::GFIT;
   extern __shared__ __align__(128) unsigned char smem[];
-  const Smem<NP, NFP> S{smem, 2, C::GFIT};
-  constexpr int PS = TNP + C::GFIT;
+  const Smem<NP, NFP, FULL> S{smem, 2, GF};
+  constexpr int PS = TNP + GF;
   uint64_t *bar = S.Bar();  // [0],[1]: full[b]; [2]: resfull; [3],[4]: done[b]
   int4 *ring = S.Ring();
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
-  const bool need_res = p.a != 0.0;
+  const bool need_res = p.r_src != nullptr;
   const long long stride = v.stride;
+  if (FULL && blockIdx.x == 0 && tid == 0 && p.slot_zero >= 0) v.scal[p.slot_zero] = 0.0;
   // Tiles are claimed dynamically (atomic counter p.sched[0], list positions 0..ntiles-1): a CTA that starts late
   // -- its SM slot was still held by the cut-element launch of a partitioned run -- or sits on a slower SM simply
   // claims fewer.  The record of local tile j+3 is claimed and fetched together with tile j; a failed claim leaves an
@@ -604,9 +791,10 @@ __global__ void __launch_bounds__(kThreadsWS, BDG_MINBLOCKS) k_fused_persistent(
       if (!has_rec) ring[(j + 3) & 7] = kEnd;  // ordered before the arrive below, which the readers acquire
       const bool has_ids = rj1.x >= 0 && rj1.y > 0;
       const uint32_t idb = has_ids ? sizeof(int32_t) * rj1.y : 0;
-      mbar_expect_tx(&bar[b], 3 * C::txQ + C::txMeta + (has_rec ? 16u : 0u) + idb);
+      mbar_expect_tx(&bar[b], 3 * C::txQ + C::txMeta + (FULL ? C::txDl : 0u) + (has_rec ? 16u : 0u) + idb);
       for (int f = 0; f < 3; ++f) bulk_g2s(S.Q(b) + f * PS, p.q_in + f * stride + kt0 * NP, C::txQ, &bar[b]);
       bulk_g2s(S.Lm(b), p.lmap + kt0 * C::NFN, sizeof(uint32_t) * kTile * C::NFN, &bar[b]);
+      if (FULL) bulk_g2s(S.Dl(b), p.dl + kt0 * C::NFN, C::txDl, &bar[b]);
       bulk_g2s(S.Aff(b), v.aff + kt0 * kAW, sizeof(double) * kTile * kAW, &bar[b]);
       if (has_rec) bulk_g2s(&ring[(j + 3) & 7], recs + pos3, 16, &bar[b]);
       if (has_ids) bulk_g2s(S.Ids(b), p.gflat + (((long long)rj1.w << 32) | (unsigned)rj1.z), idb, &bar[b]);
@@ -614,7 +802,7 @@ __global__ void __launch_bounds__(kThreadsWS, BDG_MINBLOCKS) k_fused_persistent(
     auto res_ready = [&](int tile) {  // lane 0: R is free; fill it (a != 0) or just say so
       if (need_res) {
         mbar_expect_tx(&bar[2], 3 * C::txQ);
-        for (int f = 0; f < 3; ++f) bulk_g2s(S.R() + f * TNP, p.res + f * stride + (long long)tile * kTile * NP, C::txQ, &bar[2]);
+        for (int f = 0; f < 3; ++f) bulk_g2s(S.R() + f * TNP, p.r_src + f * stride + (long long)tile * kTile * NP, C::txQ, &bar[2]);
       } else {
         mbar_arrive(&bar[2]);
       }
@@ -623,7 +811,7 @@ __global__ void __launch_bounds__(kThreadsWS, BDG_MINBLOCKS) k_fused_persistent(
       const long long base = (long long)tile * kTile * NP;
       for (int f = 0; f < 3; ++f) {
         bulk_s2g(p.q_out + f * stride + base, S.Q(b) + f * PS, C::txQ);
-        bulk_s2g(p.res + f * stride + base, S.R() + f * TNP, C::txQ);
+        if (p.store_res) bulk_s2g(p.res + f * stride + base, S.R() + f * TNP, C::txQ);
       }
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
     };
@@ -678,7 +866,14 @@ __global__ void __launch_bounds__(kThreadsWS, BDG_MINBLOCKS) k_fused_persistent(
   asm volatile("setmaxnreg.inc.sync.aligned.u32 136;");
   double Areg[C::A_REGS ? C::MB * C::KB : 1];
   int fm[C::NFB];
-  load_constants<NP, NFP>(p, v, Areg, S.A(), fm, v.scal[S_DT]);
+  const double dtv = v.scal[S_DT];
+  load_constants<NP, NFP>(p, v, Areg, S.A(), fm, dtv);
+  double tide = 0.0, tide_next = 0.0, lam_next = 0.0;
+  if (FULL) {
+    const double t = v.scal[S_T];
+    tide = tide_level(v, t);
+    tide_next = p.last_stage ? tide_level(v, t + dtv) : tide;
+  }
   compute_sync();
   PROF_DECL
   for (int it = 0;; ++it) {
@@ -688,14 +883,15 @@ __global__ void __launch_bounds__(kThreadsWS, BDG_MINBLOCKS) k_fused_persistent(
     PROF_T(0);
     mbar_wait(&bar[b], (it >> 1) & 1);
     PROF_T(1);
-    compute_tile<NP, NFP>(v, p, S.Q(b), S.R(), S.Aff(b), S.Lm(b), S.Fl(), S.A(), Areg, fm, PS, TNP + rc.y, (long long)rc.x * kTile, need_res,
-                          &bar[2], it & 1 PROF_PASS);
+    compute_tile<NP, NFP, FULL>(v, p, S.Q(b), S.R(), S.Aff(b), S.Lm(b), S.Dl(b), S.Fl(), S.A(), Areg, fm, PS, TNP + rc.y, (long long)rc.x * kTile,
+                                need_res, &bar[2], it & 1, dtv, tide, tide_next, lam_next PROF_PASS);
     PROF_T(7);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     compute_sync();
     if (tid == 0) mbar_arrive(&bar[3 + b]);
     PROF_T(8);
   }
+  if (FULL) publish_speed(v, p, lam_next);
 #ifdef BDG_PHASEPROF
   if ((tid & 31) == 0 && p.prof)
     for (int i = 0; i < 12; ++i) atomicAdd((unsigned long long *)p.prof + (tid >> 5) * 12 + i, (unsigned long long)pacc[i]);
@@ -712,37 +908,46 @@ struct FusedOps {
   int4 *rec;
   int32_t *biglist;
   std::vector<int> reg_tiles, big_tiles;  // host copies (sorted tile ids) to cut launch ranges
+  // the full-physics instantiation has its own (larger) ghost capacity, hence its own split into regular and big tiles
+  int4 *rec_full = nullptr;
+  int32_t *biglist_full = nullptr;
+  std::vector<int> reg_tiles_full, big_tiles_full;
   int Gcap, Gmax;                         // ghost slots of the persistent / edge kernel buffers (multiples of 8)
   int Np, Nfp;
+  double *dl = nullptr;     // full mode: static double per face slot, [ntiles*kTile][Nfn] (k_build_delta)
+  long long n_slots = 0;    // ntiles*kTile*Nfn
   long long *prof = nullptr;
 };
 
 int g_sm_count[16] = {};
 
-template <int NP, int NFP>
+template <int NP, int NFP, bool FULL>
 cudaError_t launch_t(bdg_sw2d *s, StageArgs a, const FusedOps *ops) {
   using C = Cfg<NP, NFP>;
   static int ctas_per_sm[16] = {};
   static int attr_key[16] = {};
   const int dev = s->device & 15;
-  size_t smem_edge = C::total(1, ops->Gmax), smem_pers = C::total(2, ops->Gcap);
+  const int Gcap = FULL ? C::GFIT_FULL : C::GFIT;
+  size_t smem_edge = C::total(1, ops->Gmax, FULL), smem_pers = C::total(2, Gcap, FULL);
 #ifdef BDG_PHASEPROF
   if (getenv("BDG_EXTRA_SMEM")) smem_pers += atoi(getenv("BDG_EXTRA_SMEM"));  // occupancy experiments: 1 or 2 CTAs per SM
 #endif
   cudaError_t e;
-  if (attr_key[dev] != ops->Gmax * 4096 + ops->Gcap + 1) {
-    if ((e = cudaFuncSetAttribute(k_fused_edge<NP, NFP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_edge)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_fused_persistent<NP, NFP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pers)) != cudaSuccess) return e;
-    cudaFuncSetAttribute(k_fused_edge<NP, NFP>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    cudaFuncSetAttribute(k_fused_persistent<NP, NFP>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm[dev], k_fused_persistent<NP, NFP>, kThreadsWS, smem_pers)) != cudaSuccess) return e;
+  if (attr_key[dev] != ops->Gmax * 4096 + Gcap + 1) {
+    if ((e = cudaFuncSetAttribute(k_fused_edge<NP, NFP, FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_edge)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_fused_persistent<NP, NFP, FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pers)) != cudaSuccess) return e;
+    cudaFuncSetAttribute(k_fused_edge<NP, NFP, FULL>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(k_fused_persistent<NP, NFP, FULL>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm[dev], k_fused_persistent<NP, NFP, FULL>, kThreadsWS, smem_pers)) != cudaSuccess) return e;
     if ((e = cudaDeviceGetAttribute(&g_sm_count[dev], cudaDevAttrMultiProcessorCount, s->device)) != cudaSuccess) return e;
     if (ctas_per_sm[dev] < 1) return cudaErrorLaunchOutOfResources;
-    attr_key[dev] = ops->Gmax * 4096 + ops->Gcap + 1;
+    attr_key[dev] = ops->Gmax * 4096 + Gcap + 1;
   }
   // tiles [t0,t1) cover [k0,k1); the fully active ones [p0,p1) (k1 <= K, so they are also full) go to the
   // persistent kernel when they are regular (<= Gcap ghosts); ragged / partially active head and tail tiles and
   // the big tiles inside [p0,p1) go to the edge kernel
+  const std::vector<int> &reg_tiles = FULL ? ops->reg_tiles_full : ops->reg_tiles;
+  const std::vector<int> &big_tiles = FULL ? ops->big_tiles_full : ops->big_tiles;
   const int t0 = a.k0 / kTile, t1 = (a.k1 - 1) / kTile + 1;
   int p0 = (a.k0 + kTile - 1) / kTile, p1 = a.k1 / kTile;
   if (a.write_rhs || p1 <= p0) p0 = p1 = t1;
@@ -754,27 +959,37 @@ cudaError_t launch_t(bdg_sw2d *s, StageArgs a, const FusedOps *ops) {
     h.tile0 = use_list ? 0 : first;
     h.list_first = use_list ? first : 0;
     h.ntiles = count;
-    k_fused_edge<NP, NFP><<<count, kThreads, smem_edge, s->stream>>>(s->v, h);
+    k_fused_edge<NP, NFP, FULL><<<count, kThreads, smem_edge, s->stream>>>(s->v, h);
     s->launches++;
   };
   edge(t0, p0 - t0, 0);
   if (p1 > p0) {
-    const int jr0 = (int)(std::lower_bound(ops->reg_tiles.begin(), ops->reg_tiles.end(), p0) - ops->reg_tiles.begin());
-    const int jr1 = (int)(std::lower_bound(ops->reg_tiles.begin(), ops->reg_tiles.end(), p1) - ops->reg_tiles.begin());
+    const int jr0 = (int)(std::lower_bound(reg_tiles.begin(), reg_tiles.end(), p0) - reg_tiles.begin());
+    const int jr1 = (int)(std::lower_bound(reg_tiles.begin(), reg_tiles.end(), p1) - reg_tiles.begin());
     if (jr1 > jr0) {
       StageArgs m = a;
-      m.G = ops->Gcap;
+      m.G = Gcap;
+      m.rec = FULL ? ops->rec_full : ops->rec;
       m.list_first = jr0; m.ntiles = jr1 - jr0; m.use_list = 1; m.tile0 = 0;
       int grid = g_sm_count[dev] * ctas_per_sm[dev];
       // while a halo exchange is in flight leave a few SMs one CTA short, so the NCCL send/recv kernel finds room
       if (s->comm && !s->peer_ok && s->n_nbr > 0 && a.k0 == 0 && a.k1 < s->v.K) grid -= 16;
       if (grid > m.ntiles) grid = m.ntiles;
-      k_fused_persistent<NP, NFP><<<grid, kThreadsWS, smem_pers, s->stream>>>(s->v, m);
+      k_fused_persistent<NP, NFP, FULL><<<grid, kThreadsWS, smem_pers, s->stream>>>(s->v, m);
       s->launches++;
     }
-    const int jb0 = (int)(std::lower_bound(ops->big_tiles.begin(), ops->big_tiles.end(), p0) - ops->big_tiles.begin());
-    const int jb1 = (int)(std::lower_bound(ops->big_tiles.begin(), ops->big_tiles.end(), p1) - ops->big_tiles.begin());
-    edge(jb0, jb1 - jb0, 1);
+    const int jb0 = (int)(std::lower_bound(big_tiles.begin(), big_tiles.end(), p0) - big_tiles.begin());
+    const int jb1 = (int)(std::lower_bound(big_tiles.begin(), big_tiles.end(), p1) - big_tiles.begin());
+    StageArgs hb = a;
+    (void)hb;
+    if (jb1 > jb0) {
+      StageArgs h = a;
+      h.G = ops->Gmax;
+      h.biglist = FULL ? ops->biglist_full : ops->biglist;
+      h.use_list = 1; h.tile0 = 0; h.list_first = jb0; h.ntiles = jb1 - jb0;
+      k_fused_edge<NP, NFP, FULL><<<jb1 - jb0, kThreads, smem_edge, s->stream>>>(s->v, h);
+      s->launches++;
+    }
   }
   edge(p1, t1 - p1, 0);
   return cudaGetLastError();
@@ -887,8 +1102,12 @@ void arrange_slots(int Np, int Nfp, int Nfn, int NFB, bool face_blocks, const in
 
 }  // namespace
 
+// Full physics (star states + sources) is fused in its reference form, i.e. with the GLOBAL Lax-Friedrichs speed of
+// src/sw2d/main.cpp:413-414; sources with a per-face speed (a combination only the Python drivers use) stay on the
+// two-launch path.
 int fused_supported(const bdg_sw2d *s) {
-  if (!s->is_affine || s->v.Nf != 3 || s->v.full || s->v.use_filter) return 0;
+  if (!s->is_affine || s->v.Nf != 3 || s->v.use_filter) return 0;
+  if (s->v.full && !s->v.lf_global) return 0;
 #define X(np, nfp) \
   if (s->v.Np == np && s->v.Nfp == nfp) return 1;
   BDG_FUSED_ORDERS(X)
@@ -987,16 +1206,31 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
     fprintf(stderr, "[blitzdg_b200] fused tiles %d, ghosts per tile: mean %.1f median %d cap %d max %d\n", ntiles,
             (double)gflat.size() / ntiles, sorted[ntiles / 2], Gcap, Gmax);
   if (Gmax8 > kGI * kThreads || tnp + Gmax8 > 65535) return cudaSuccess;  // not representable: stay on the generic path
-  std::vector<int4> rec;
+  std::vector<int4> rec, rec_full;
   FusedOps *ops = new FusedOps();
+  int cap_full = 0;
+#define X(np, nfp) \
+  if (Np == np && Nfp == nfp) cap_full = Cfg<np, nfp>::GFIT_FULL;
+  BDG_FUSED_ORDERS(X)
+#undef X
   for (int T = 0; T < ntiles; ++T) {
+    const int4 r = make_int4(T, cnt[T], (int)(goff[T] & 0xffffffffLL), (int)(goff[T] >> 32));
     if (cnt[T] <= Gcap) {
       ops->reg_tiles.push_back(T);
-      rec.push_back(make_int4(T, cnt[T], (int)(goff[T] & 0xffffffffLL), (int)(goff[T] >> 32)));
+      rec.push_back(r);
     } else {
       ops->big_tiles.push_back(T);
     }
+    if (cnt[T] <= cap_full) {
+      ops->reg_tiles_full.push_back(T);
+      rec_full.push_back(r);
+    } else {
+      ops->big_tiles_full.push_back(T);
+    }
   }
+  std::vector<int32_t> bigf(ops->big_tiles_full.begin(), ops->big_tiles_full.end());
+  if (bigf.empty()) bigf.push_back(0);
+  if (rec_full.empty()) rec_full.push_back(make_int4(0, 0, 0, 0));
   std::vector<long long> goff64(goff.begin(), goff.end());
   if (gflat.empty()) gflat.push_back(0);
   std::vector<int32_t> big(ops->big_tiles.begin(), ops->big_tiles.end());
@@ -1020,7 +1254,10 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
   };
   if ((e = up(&ops->slotinfo, slotinfo)) != cudaSuccess || (e = up(&ops->Afrag, frag)) != cudaSuccess || (e = up(&ops->lmap, lmap)) != cudaSuccess ||
       (e = up(&ops->gflat, gflat)) != cudaSuccess || (e = up(&ops->goff, goff64)) != cudaSuccess ||
-      (e = up(&ops->rec, rec)) != cudaSuccess || (e = up(&ops->biglist, big)) != cudaSuccess) {
+      (e = up(&ops->rec, rec)) != cudaSuccess || (e = up(&ops->biglist, big)) != cudaSuccess ||
+      (s->v.full && ((e = up(&ops->rec_full, rec_full)) != cudaSuccess || (e = up(&ops->biglist_full, bigf)) != cudaSuccess ||
+                     (e = cudaMalloc((void **)&ops->dl, sizeof(double) * (size_t)ntiles * kTile * Nfn)) != cudaSuccess ||
+                     (e = cudaMemset(ops->dl, 0, sizeof(double) * (size_t)ntiles * kTile * Nfn)) != cudaSuccess))) {
     s->fused_ops = ops;
     fused_release(s);
     return e;
@@ -1029,8 +1266,34 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
   cudaMalloc((void **)&ops->prof, sizeof(long long) * kWarps * 12);
   cudaMemset(ops->prof, 0, sizeof(long long) * kWarps * 12);
 #endif
+  ops->n_slots = (long long)ntiles * kTile * Nfn;
   s->fused_ops = ops;
   return cudaSuccess;
+}
+
+namespace {
+// static double per face slot for the star states (main.cpp:355-368): H+ - H- (exact for nearly equal depths); on Out
+// faces, where '+' = '-', H- itself, which the tidal hP = H- + tide needs (main.cpp:352).  Padding slots stay 0.
+__global__ void k_build_delta(Sw2dView v, double *__restrict__ dl) {
+  const long long nF = (long long)v.Nfn * v.K;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nF; i += (long long)gridDim.x * blockDim.x) {
+    const long long k = i / v.Nfn;
+    const int sl = (int)(i - k * v.Nfn);
+    const double HM = v.H[k * v.Np + v.fmask[sl]], HP = v.H[v.vmapP[i]];
+    const int tag = v.facetag[k * v.Nf + sl / v.Nfp];
+    dl[i] = tag == 2 ? HM : (tag == 3 ? 0.0 : HP - HM);
+  }
+}
+}  // namespace
+
+// (re)builds the star-state table from the bathymetry on the device (ghost depths included): after set_bathymetry and,
+// on a partitioned mesh, after the neighbours' depths have arrived
+cudaError_t fused_build_delta(bdg_sw2d *s) {
+  FusedOps *ops = static_cast<FusedOps *>(s->fused_ops);
+  if (!ops || !ops->dl || !s->v.H) return cudaSuccess;
+  k_build_delta<<<1184, 256, 0, s->stream>>>(s->v, ops->dl);
+  s->launches++;
+  return cudaGetLastError();
 }
 
 void fused_release(bdg_sw2d *s) {
@@ -1051,13 +1314,13 @@ void fused_release(bdg_sw2d *s) {
     cudaFree(ops->prof);
   }
 #endif
-  cudaFree(ops->sched); cudaFree(ops->slotinfo); cudaFree(ops->Afrag); cudaFree(ops->lmap); cudaFree(ops->gflat); cudaFree(ops->goff); cudaFree(ops->rec); cudaFree(ops->biglist);
+  cudaFree(ops->sched); cudaFree(ops->slotinfo); cudaFree(ops->Afrag); cudaFree(ops->lmap); cudaFree(ops->gflat); cudaFree(ops->goff); cudaFree(ops->rec); cudaFree(ops->biglist); cudaFree(ops->rec_full); cudaFree(ops->biglist_full); cudaFree(ops->dl);
   delete ops;
   s->fused_ops = nullptr;
 }
 
 cudaError_t launch_fused_stage(bdg_sw2d *s, const double *q_in, double *q_out, double *res, int k0, int k1, double a, double b,
-                               int write_rhs, double *rhs_out, int slot) {
+                               int write_rhs, double *rhs_out, int slot, const FusedStage *fs) {
   if (k1 <= k0) return cudaSuccess;
   FusedOps *ops = static_cast<FusedOps *>(s->fused_ops);
   if (!ops) return cudaErrorNotSupported;
@@ -1068,8 +1331,18 @@ cudaError_t launch_fused_stage(bdg_sw2d *s, const double *q_in, double *q_out, d
   args.k0 = k0; args.k1 = k1; args.tile0 = 0; args.ntiles = 0;
   args.write_rhs = write_rhs; args.slot = slot; args.a = a; args.b = b; args.prof = ops->prof; args.slotinfo = ops->slotinfo;
   args.sched = ops->sched + (s->stream == s->comm_stream ? 2 : 0);  // launches on the two streams may overlap
-#define X(np, nfp) \
-  if (ops->Np == np && ops->Nfp == nfp) return launch_t<np, nfp>(s, args, ops);
+  args.dl = ops->dl;
+  args.mode = fs ? fs->mode : 1;
+  args.slot_next = fs ? fs->slot_next : -1;
+  args.slot_zero = fs ? fs->slot_zero : -1;
+  args.last_stage = fs ? fs->last_stage : 0;
+  // R planes: the residual (LSERK4, unless a = 0 wipes it), q^n still sitting in the destination buffer (second SSP-RK2
+  // stage), nothing (first SSP-RK2 stage, RHS evaluation)
+  args.r_src = write_rhs ? nullptr : (args.mode == 1 ? (a != 0.0 ? res : nullptr) : (args.mode == 3 ? q_out : nullptr));
+  args.store_res = !write_rhs && args.mode == 1;
+#define X(np, nfp)                                                        \
+  if (ops->Np == np && ops->Nfp == nfp)                                   \
+    return s->v.full ? launch_t<np, nfp, true>(s, args, ops) : launch_t<np, nfp, false>(s, args, ops);
   BDG_FUSED_ORDERS(X)
 #undef X
   return cudaErrorNotSupported;

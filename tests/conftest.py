@@ -43,9 +43,10 @@ def coarse_quads_mesh():
 def fused_expected(sol):
     """The fused single-launch kernel is the product path wherever sw2d_fused.cu covers the case: its absence there is
     a FAILURE of the test, never a silent fall-back to the two-launch path.  Straight-sided triangles (a jittered
-    structured mesh is still affine) of the instantiated orders, no RHS filter."""
+    structured mesh is still affine) of the instantiated orders, no RHS filter; full physics (star states + sources) in
+    its reference form, i.e. with the global Lax-Friedrichs speed."""
     c = sol.ctx
-    return c.Nfaces == 3 and c.N <= 5 and not sol.prm.filter and not sol.prm.sources
+    return c.Nfaces == 3 and c.N <= 5 and not sol.prm.filter and (not sol.prm.sources or sol.prm.lf_mode == 1)
 
 
 def kernel_variants(sol):

@@ -14,9 +14,18 @@ sizes the asserted bound is relative to that measured noise floor:
     cuda_vs_oracle <= 2.5 * oracle_vs_exact + 2e-13      (triangle inequality of the two)
 while the unit-size meshes of tests/test_gpu_parity.py hold the plain 1e-12.
 
-The oracle runs over the whole mesh in strips (blitzdg_b200.partition.build_local with ghost traces taken from the
-global state -- the arithmetic of an element does not depend on the partition, tests/test_halo_gloo.py), a few strips at
-a time on the host cores, so that its ~55 temporaries per pass stay bounded in memory.
+A second, independent limit applies to the fused kernel (variant 2): it reads 13 geometry doubles per straight-sided
+triangle (B_alg's 104 B) where the reference stores rx, sx, ry, sy per NODE and nx, ny, Fscale per FACE NODE.  On an
+affine element those per-node copies are mathematically equal, but the reference's setup computes each from nodal
+coordinates (Dr x with |x| ~ 1 and differences ~ h_cell), so they scatter by eps |Dr| |x| / h_cell: 1e-12 relative in the
+metrics and ~2.5e-13 absolute in the unit normals on the 1 M mesh (`geometry_noise`, measured from the arrays).  The
+kernel uses their mean; the oracle and the arbiter use each node's own copy.  The effect on the RHS is largest on wall
+faces, where a normal that is off by 1e-13 turns tangential momentum into a reflection jump that Fscale*LIFT ~ 1e4/h_cell
+amplifies -- the reference's OWN result there is only defined to that level (another LAPACK build scatters differently,
+SURVEY.md F9).  It is measured without any kernel: `geometry_effect` = arbiter(per-node geometry) vs arbiter(element /
+face means).  So variant 2 is held
+    to the arbiter on the SAME averaged geometry at the fp64 floor:   v2_cuda_vs_exact_meangeom <= 1.5 * floor + 2e-13
+    to the reference-ordered oracle within floor + that effect:       v2_cuda_vs_oracle <= 2.5 * floor + 1.1 * geometry_effect + 2e-13
 """
 import json
 import os
@@ -49,6 +58,35 @@ def oracle_rhs_strips(mesh, N, state, nstrips, strips=None, threads=None):
     return R, ~np.isnan(R[0][0])
 
 
+def geometry_noise(ctx):
+    """Largest relative scatter of the per-node copies of the (mathematically constant) affine geometry factors: rx, sx,
+    ry, sy within an element, nx, ny, Fscale within a face -- the rounding noise of the reference's own setup."""
+    worst = 0.0
+    vol = [ctx.rx, ctx.sx, ctx.ry, ctx.sy]
+    scale = max(float(np.abs(a).max()) for a in vol)
+    for a in vol:
+        worst = max(worst, float((a.max(axis=0) - a.min(axis=0)).max()) / scale)
+    Nfp = ctx.Nfp
+    for a in (ctx.nx, ctx.ny, ctx.Fscale):
+        b = a.reshape(ctx.Nfaces, Nfp, -1)
+        worst = max(worst, float((b.max(axis=1) - b.min(axis=1)).max()) / float(np.abs(a).max()))
+    return worst
+
+
+def mean_geometry(ctx):
+    """The context with every affine geometry factor replaced by its element / face mean, as bdg_sw2d_create folds them."""
+    import copy
+
+    c = copy.copy(ctx)
+    for name in ("rx", "sx", "ry", "sy"):
+        a = getattr(ctx, name)
+        setattr(c, name, np.ascontiguousarray(np.broadcast_to(a.mean(axis=0, keepdims=True), a.shape)))
+    for name in ("nx", "ny", "Fscale"):
+        a = getattr(ctx, name).reshape(ctx.Nfaces, ctx.Nfp, -1)
+        setattr(c, name, np.ascontiguousarray(np.broadcast_to(a.mean(axis=1, keepdims=True), a.shape).reshape(ctx.Nfaces * ctx.Nfp, -1)))
+    return c
+
+
 def record(name, row):
     path = os.path.join(ROOT, "gpurun_out", "parity_fullsize.json")
     try:
@@ -78,9 +116,10 @@ def test_full_mesh_rhs_against_oracle_and_arbiter(name, shape, N, nx, ny, strips
     mesh = structured_mesh(shape, nx, ny)
     ctx = provision(mesh, N).get_DGContext()
     H, h, hu, hv = gaussian_hump(ctx.x, ctx.y)
-    # a moving state, so that every flux component and the wall reflection carry weight
-    hu = 0.5 * h * np.sin(3.0 * ctx.x + 1.0) * np.cos(2.0 * ctx.y)
-    hv = 0.4 * h * np.cos(2.5 * ctx.x) * np.sin(3.5 * ctx.y + 0.5)
+    # a moving state that respects the wall BC (no normal flow at x, y = +-1), so that max|RHS| is set by the interior and
+    # not by an O(1/h_cell) reflection jump at the walls: every flux component carries weight
+    hu = 0.5 * h * np.sin(np.pi * ctx.x) * np.cos(2.0 * ctx.y)
+    hv = 0.4 * h * np.cos(2.5 * ctx.x) * np.sin(np.pi * ctx.y)
     hu, hv = np.ascontiguousarray(hu), np.ascontiguousarray(hv)
     sol = SW2dSolver(ctx)
     sol.set_state(h, hu, hv)
@@ -102,11 +141,19 @@ def test_full_mesh_rhs_against_oracle_and_arbiter(name, shape, N, nx, ny, strips
     for var in variants:
         row["v%d_cuda_vs_exact" % var] = [relerr(Rc[var][c], Ra[c]) for c in range(3)]
         row["v%d_cuda_vs_oracle" % var] = [relerr(Rc[var][c][:, mask], Ro[c][:, mask]) for c in range(3)]
+    if 2 in variants:
+        row["geometry_noise"] = geometry_noise(ctx)
+        Rm = Arbiter(mean_geometry(ctx)).rhs(h, hu, hv)
+        row["geometry_effect"] = [relerr(Rm[c], Ra[c]) for c in range(3)]
+        row["v2_cuda_vs_exact_meangeom"] = [relerr(Rc[2][c], Rm[c]) for c in range(3)]
     record(name, row)
     print(name, json.dumps(row))
-    for var in variants:
-        assert max(row["v%d_cuda_vs_exact" % var]) <= 1.5 * floor + 2e-13, row
-        assert max(row["v%d_cuda_vs_oracle" % var]) <= 2.5 * floor + 2e-13, row
+    assert max(row["v1_cuda_vs_exact"]) <= 1.5 * floor + 2e-13, row
+    assert max(row["v1_cuda_vs_oracle"]) <= 2.5 * floor + 2e-13, row
+    if 2 in variants:
+        assert max(row["v2_cuda_vs_exact_meangeom"]) <= 1.5 * floor + 2e-13, row
+        assert max(row["v2_cuda_vs_oracle"]) <= 2.5 * floor + 1.1 * max(row["geometry_effect"]) + 2e-13, row
+        assert row["geometry_noise"] < 1e-10
     # the absolute level, so that a regression of either side shows: conditioning ~ eps * |Dr|_inf * (2/h_cell) * g h^2/2 / |RHS|
     assert floor < 1e-9
 

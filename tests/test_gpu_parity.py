@@ -195,6 +195,60 @@ def test_synthetic_mesh_rhs_and_steps(shape, N, nx, ny, jit):
     sol.close()
 
 
+@pytest.mark.parametrize("N,nx,ny,bed", [(4, 64, 32, "slope"), (4, 40, 24, "steps"), (3, 33, 17, "steps"), (5, 20, 12, "slope"), (2, 50, 30, "steps")])
+def test_full_physics_fused_on_structured_meshes(N, nx, ny, bed):
+    """src/sw2d physics (global LF, star states, Out faces with tide, sources) through the fused single-launch kernel on
+    meshes with many tiles (persistent + edge kernels): RHS, LSERK4 steps with the global speed carried from stage to stage,
+    then the driver's SSP-RK2 loop with a sponge, all against the oracle (which agrees bitwise with the reference's own
+    compiled computeRHS, tests/test_reference_compiled.py).  bed = steps: a different bed level per element, so that the star
+    states differ from the plain traces on every interior face."""
+    mesh = structured_mesh("tri", nx, ny)
+    ctx = provision(mesh, N).get_DGContext()
+    _, h, hu, hv = _state(ctx, seed=N, amp=0.3)
+    rng = np.random.default_rng(40 + N)
+    H = 12 + 0.5 * ctx.x + 0.25 * ctx.y
+    if bed == "steps":
+        H = H + 0.2 * rng.standard_normal(ctx.K)[None, :]
+    Hx, Hy = np.full_like(H, 0.5), np.full_like(H, 0.25)
+    h = np.ascontiguousarray(H + (h - 10.0))
+    wall = np.asarray(ctx.BCmap[3]).reshape(-1, ctx.Nfp)
+    yv = ctx.y.T.reshape(-1)[np.asarray(ctx.vmapM)[wall]]
+    top = (yv > 1.0 - 1e-9).all(axis=1)
+    ctx.BCmap = {3: wall[~top].reshape(-1), 2: wall[top].reshape(-1)}  # open top edge
+    orc = _oracle(ctx, lf_mode=1, sources=1, CFL=0.25)
+    orc.set_bathymetry(H, Hx, Hy)
+    t0 = 3600 * 12.42 + 500.0
+    Ro = orc.rhs(h, hu, hv, t=t0)
+    dt = 0.5 * orc.timestep(h, hu, hv)[0]
+    ho, huo, hvo = h.copy(), hu.copy(), hv.copy()
+    res = [np.zeros_like(h) for _ in range(3)]
+    t1 = orc.step(ho, huo, hvo, res, 12, dt, t=t0)
+    sponge = 30.0 * rng.random(h.shape)
+    h2, hu2, hv2 = ho.copy(), huo.copy(), hvo.copy()
+    t2 = orc.step_ssprk2(h2, hu2, hv2, 10, dt, t=t1, sponge=sponge)
+    sol = _solver(ctx, mode="full")
+    sol.set_bathymetry(H, Hx, Hy)
+    sol.set_sponge(sponge)
+    assert _variants(sol) == [1, 2]
+    for var in (1, 2):
+        sol.set_variant(var)
+        sol.set_state(h, hu, hv, t=t0)
+        R = sol.computeRHS()
+        for c in range(3):
+            assert relerr(R[c], Ro[c]) < RHS_TOL, (var, c, relerr(R[c], Ro[c]))
+        sol.step(12, dt)
+        hg, hug, hvg, tg = sol.get_state()
+        assert abs(tg - t1) <= 1e-12 * t1
+        assert max(relerr(hg, ho), relerr(hug, huo), relerr(hvg, hvo)) < STEP_TOL, var
+        R = sol.computeRHS()  # an RHS between steps must not disturb the carried speed
+        sol.step_ssprk2(10, dt)
+        hg, hug, hvg, tg = sol.get_state()
+        assert abs(tg - t2) <= 1e-12 * t2
+        assert max(relerr(hg, h2), relerr(hug, hu2), relerr(hvg, hv2)) < STEP_TOL, var
+        sol.check()
+    sol.close()
+
+
 def test_two_rank_halo_emulated_on_one_gpu():
     """Element-partitioned RHS with ghost traces moved through the pack/set_ghosts hooks equals the
     single-rank oracle (bitwise-independent of P in per-face mode up to the parity tolerance)."""
