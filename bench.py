@@ -236,7 +236,7 @@ def cpu_reference(args, world, threads, budget_s, steps=1, warmup=0, max_element
         mesh = global_mesh(args, world)
     K = mesh.get_NumElements()
     t_setup = time.perf_counter()
-    if full or rk2 or threads == 1:
+    if full or rk2:
         threads = 1
         ctx = provision(mesh, args.order).get_DGContext()
         H, h, hu, hv = gaussian_hump(ctx.x, ctx.y)
@@ -263,7 +263,8 @@ def cpu_reference(args, world, threads, budget_s, steps=1, warmup=0, max_element
     else:
         from oracle.threaded import StripOracle
 
-        so = StripOracle(mesh, args.order, threads=threads, CFL=0.65)
+        # threads == 1: ONE Oracle instance over the whole mesh, advanced stage by stage (the same C calls as oracle_sw2d_step)
+        so = StripOracle(mesh, args.order, nparts=1 if threads == 1 else None, threads=threads, CFL=0.65)
         Np = so.Np
         xs = np.zeros((Np, K))
         ys = np.zeros((Np, K))
@@ -281,6 +282,8 @@ def cpu_reference(args, world, threads, budget_s, steps=1, warmup=0, max_element
     advance(1)  # calibration (also the first warm-up)
     one = time.perf_counter() - t0
     n = max(1, int(budget_s / max(1, steps + warmup) / max(one, 1e-3)))
+    if per_call == 1 and n >= 5:
+        n -= n % 5  # whole LSERK4 steps
     for _ in range(max(0, warmup - 1)):
         advance(n)
     times = []

@@ -126,7 +126,7 @@ EXPORTS = [
     "bdg_sw2d_algorithmic_bytes_per_stage", "bdg_nccl_unique_id", "bdg_sw2d_comm_init",
     "bdg_sw2d_halo_pack_to_host", "bdg_sw2d_halo_set_ghosts", "bdg_element_order", "bdg_version",
     "bdg_sw2d_set_sponge", "bdg_sw2d_step_ssprk2", "bdg_sw2d_set_output", "bdg_sw2d_output_begin", "bdg_sw2d_output_wait",
-    "bdg_sw2d_limit_positivity", "bdg_sw2d_stage_state", "bdg_sw2d_commit_state", "bdg_sw2d_get_state_async", "bdg_sw2d_get_state_wait",
+    "bdg_sw2d_limit_positivity", "bdg_sw2d_set_tracer", "bdg_sw2d_get_tracer", "bdg_sw2d_rhs_tracer", "bdg_sw2d_stage_state", "bdg_sw2d_commit_state", "bdg_sw2d_get_state_async", "bdg_sw2d_get_state_wait",
 ]
 
 
@@ -165,6 +165,9 @@ def load():
     L.bdg_sw2d_output_begin.argtypes = [vp, _dp, _dp, _dp]
     L.bdg_sw2d_output_wait.argtypes = [vp]
     L.bdg_sw2d_limit_positivity.argtypes = [vp]
+    L.bdg_sw2d_set_tracer.argtypes = [vp, _dp]
+    L.bdg_sw2d_get_tracer.argtypes = [vp, _dp]
+    L.bdg_sw2d_rhs_tracer.argtypes = [vp, _dp]
     L.bdg_sw2d_stage_state.argtypes = [vp, _dp, _dp, _dp, C.c_double]
     L.bdg_sw2d_commit_state.argtypes = [vp]
     L.bdg_sw2d_get_state_async.argtypes = [vp, _dp, _dp, _dp]

@@ -164,7 +164,7 @@ extern "C" void bdg_sw2d_destroy(bdg_sw2d *s) {
   fused_release(s);
   void *ptrs[] = {s->q[0], s->q[1], s->res, s->rhs, s->sflux, s->d_Dr, s->d_Ds, s->d_Lift, s->d_Filt, s->d_rx, s->d_sx,
                   s->d_ry, s->d_sy, s->d_nx, s->d_ny, s->d_Fscale, s->d_aff, s->d_H, s->d_Hx, s->d_Hy, s->d_vmapP,
-                  s->d_fmask, s->d_bctag, s->d_facetag, s->d_scal, s->d_send_nodes, s->d_sendbuf, s->d_perm, s->d_vfrag, s->d_Dq, s->d_sponge, s->d_IM, s->d_out, s->in_raw, s->dl_raw, s->stage_buf};
+                  s->d_fmask, s->d_bctag, s->d_facetag, s->d_scal, s->d_send_nodes, s->d_sendbuf, s->d_perm, s->d_vfrag, s->d_Dq, s->d_sponge, s->d_IM, s->d_out, s->in_raw, s->dl_raw, s->stage_buf, s->qN[0], s->qN[1], s->resN};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   free(s->h_nbr); free(s->h_send_off); free(s->h_recv_off);
@@ -808,6 +808,64 @@ extern "C" int bdg_sw2d_halo_set_ghosts(bdg_sw2d *s, const double *recv_buf) {
   return BDG_OK;
 }
 
+// ======================================================================================== tracer
+extern "C" int bdg_sw2d_set_tracer(bdg_sw2d *s, const double *hN) {
+  if (!s) return BDG_E_INVALID;
+  CU(cudaSetDevice(s->device));
+  if (!hN) {
+    CU(cudaStreamSynchronize(s->stream));
+    for (double **p : {&s->qN[0], &s->qN[1], &s->resN}) {
+      if (*p) cudaFree(*p);
+      *p = nullptr;
+    }
+    return BDG_OK;
+  }
+  if (s->v.lf_global) return fail(s, BDG_E_UNSUPPORTED, "tracer: needs the per-face Lax-Friedrichs speed (lf_mode = 0), the form of swhelpers/rhs.py");
+  if (s->n_nbr > 0) return fail(s, BDG_E_UNSUPPORTED, "tracer: single rank only (no halo exchange of hN yet)");
+  int rc;
+  for (double **p : {&s->qN[0], &s->qN[1], &s->resN})
+    if (!*p && (rc = dev_alloc(s, p, s->nT))) return rc;
+  s->curN = 0;
+  if ((rc = upload_transposed(s, hN, s->qN[0], s->v.Np, s->v.K))) return rc;
+  CU(cudaMemsetAsync(s->resN, 0, sizeof(double) * s->nT, s->stream));
+  CU(cudaMemsetAsync(s->qN[1], 0, sizeof(double) * s->nT, s->stream));
+  CU(cudaStreamSynchronize(s->stream));
+  return BDG_OK;
+}
+
+extern "C" int bdg_sw2d_get_tracer(bdg_sw2d *s, double *hN) {
+  if (!s || !hN) return BDG_E_INVALID;
+  if (!s->qN[0]) return fail(s, BDG_E_INVALID, "no tracer set");
+  CU(cudaSetDevice(s->device));
+  int rc = download_transposed(s, s->qN[s->curN], hN, s->v.Np, s->v.K);
+  if (rc) return rc;
+  CU(cudaStreamSynchronize(s->stream));
+  return BDG_OK;
+}
+
+extern "C" int bdg_sw2d_rhs_tracer(bdg_sw2d *s, double *RHS4) {
+  if (!s || !RHS4) return BDG_E_INVALID;
+  if (!s->qN[0]) return fail(s, BDG_E_INVALID, "no tracer set");
+  CU(cudaSetDevice(s->device));
+  int rc;
+  if (!s->rhs && (rc = dev_alloc(s, &s->rhs, 3 * s->nT))) return rc;
+  cudaError_t e = launch_tracer(s, s->q[s->cur], s->qN[s->curN], nullptr, s->rhs, 0, 0.0, 0.0);
+  if (e != cudaSuccess) return fail(s, BDG_E_CUDA, "tracer: %s", cudaGetErrorString(e));
+  if ((rc = download_transposed(s, s->rhs, RHS4, s->v.Np, s->v.K))) return rc;
+  CU(cudaStreamSynchronize(s->stream));
+  return BDG_OK;
+}
+
+// tracer stage beside a flow stage: reads the PRE-stage flow state q[cur] (the flow kernels write the other buffer or,
+// on the in-place LSERK4 two-launch path, run after this launch on the same stream)
+static int enqueue_tracer_stage(bdg_sw2d *s, double a, double b, int mode) {
+  if (!s->qN[0]) return BDG_OK;
+  cudaError_t e = launch_tracer(s, s->q[s->cur], s->qN[s->curN], s->qN[s->curN ^ 1], nullptr, mode, a, b);
+  if (e != cudaSuccess) return fail(s, BDG_E_CUDA, "tracer: %s", cudaGetErrorString(e));
+  s->curN ^= 1;
+  return BDG_OK;
+}
+
 // ====================================================================================== hot path
 static int use_fused(const bdg_sw2d *s) {
   if (s->variant == 1) return 0;
@@ -988,6 +1046,7 @@ extern "C" int bdg_sw2d_step(bdg_sw2d *s, int32_t nsteps, double dt) {
   for (int st = 0; st < nsteps; ++st) {
     if (adaptive && (rc = enqueue_dt(s))) return rc;
     for (int stage = 0; stage < 5; ++stage) {  // reference src/advec1d/main.cpp:92-102
+      if ((rc = enqueue_tracer_stage(s, rk4a[stage], rk4b[stage], 1))) return rc;
       if ((rc = enqueue_stage(s, 0, nullptr, rk4a[stage], rk4b[stage], slot, 0, stage == 4))) return rc;
       slot ^= 1;
     }
@@ -1021,6 +1080,7 @@ extern "C" int bdg_sw2d_step_ssprk2(bdg_sw2d *s, int32_t nsteps, double dt) {
   for (int st = 0; st < nsteps; ++st) {
     if (adaptive && (rc = enqueue_dt(s))) return rc;
     for (int stage = 0; stage < 2; ++stage) {
+      if ((rc = enqueue_tracer_stage(s, 0.0, 1.0, 2 + stage))) return rc;
       if ((rc = enqueue_stage(s, 0, nullptr, 0.0, 1.0, slot, 2 + stage, stage == 1))) return rc;
       slot ^= 1;
     }

@@ -81,6 +81,8 @@ struct bdg_sw2d {
   double *sflux;        // [3][nF] generic path: Fscale*dFlux
   double *d_Dr, *d_Ds, *d_Lift, *d_Filt, *d_rx, *d_sx, *d_ry, *d_sy, *d_nx, *d_ny, *d_Fscale, *d_aff;
   double *d_H, *d_Hx, *d_Hy, *d_sponge;
+  double *qN[2], *resN;   // tracer hN (sw2d_tracer.cu): ping-pong pair + residual, [Np*K]; NULL = no tracer
+  int curN;
   int32_t *d_vmapP, *d_fmask;
   int32_t *d_perm;      // device element k = caller's element d_perm[k] (sw2d_order.cu); NULL = identity
   uint8_t *d_bctag, *d_facetag;
@@ -144,6 +146,8 @@ cudaError_t launch_pack(bdg_sw2d *s, const double *q, int with_H);
 cudaError_t launch_positivity_limiter(bdg_sw2d *s, double *q);  // swhelpers/limiters.py:3-21 on the live state, in place
 cudaError_t launch_output_fields(bdg_sw2d *s, const double *q, cudaStream_t stream);  // eta, u, v interpolated into s->d_out
 cudaError_t launch_put(bdg_sw2d *s, const double *q, int buf, unsigned long long epoch, int side);
+// tracer stage / RHS beside the flow's stage kernel (mode 0: RHS4 into rhs_out; 1 LSERK4; 2, 3 SSP-RK2 forms)
+cudaError_t launch_tracer(bdg_sw2d *s, const double *q, const double *hN_in, double *hN_out, double *rhs_out, int mode, double a, double b);
 cudaError_t launch_wait_epoch(bdg_sw2d *s, unsigned long long epoch);
 // fused DMMA path (affine triangles): q_in -> q_out, res in place, elements [k0,k1)
 int fused_supported(const bdg_sw2d *s);

@@ -173,6 +173,23 @@ class SW2dSolver:
         """swhelpers/limiters.py:3-21 on the device state, in place (the Python drivers call it after a stage)."""
         self._ck(self.lib.bdg_sw2d_limit_positivity(self.h))
 
+    # tracer: the 4th conserved field hN of the Python drivers (sw2d.py:30-33,129-140; swhelpers/rhs.py:206-297) -----------
+    def set_tracer(self, hN):
+        """hN [Np][K] (None removes it); step() / step_ssprk2() then advance it with the flow."""
+        a = self._in(hN) if hN is not None else None
+        self._ck(self.lib.bdg_sw2d_set_tracer(self.h, _dp(a)))
+
+    def get_tracer(self):
+        out = np.empty(self.shape)
+        self._ck(self.lib.bdg_sw2d_get_tracer(self.h, _dp(out)))
+        return out
+
+    def computeRHS4(self):
+        """RHS4 of sw2dComputeRHS (swhelpers/rhs.py:275-296) on the current device state."""
+        out = np.empty(self.shape)
+        self._ck(self.lib.bdg_sw2d_rhs_tracer(self.h, _dp(out)))
+        return out
+
     def sync(self):
         self._ck(self.lib.bdg_sw2d_sync(self.h))
 

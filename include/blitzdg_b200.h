@@ -137,6 +137,17 @@ int bdg_sw2d_check(bdg_sw2d *s, double *eta_max);
  * q = mean(q) + theta*(q - mean(q)) for h, hu, hv (arithmetic node means).  Stream-ordered like bdg_sw2d_step. */
 int bdg_sw2d_limit_positivity(bdg_sw2d *s);
 
+/* --- tracer --------------------------------------------------------------------------------
+ * The 4th conserved field hN of the reference's Python drivers (swhelpers/rhs.py:206-297, swhelpers/flux.py:18-20,
+ * sw2d.py:30-33,129-140): F4 = hN u, G4 = hN v, the flow's per-face Lax-Friedrichs speed, hN+ = hN- on walls.
+ * set_tracer: hN [Np][K] (copied; zeroes its RK residual); NULL removes the tracer.  While a tracer is set,
+ * bdg_sw2d_step / bdg_sw2d_step_ssprk2 advance it with the flow (one extra launch per stage).  Needs lf_mode = 0
+ * (the only form the reference has) and a single rank; otherwise BDG_E_UNSUPPORTED.
+ * rhs_tracer: RHS4 of the current state, host out [Np][K] -- the parity entry point. */
+int bdg_sw2d_set_tracer(bdg_sw2d *s, const double *hN);
+int bdg_sw2d_get_tracer(bdg_sw2d *s, double *hN);
+int bdg_sw2d_rhs_tracer(bdg_sw2d *s, double *RHS4);
+
 /* --- output path ---------------------------------------------------------------------------
  * Every outputInterval steps the drivers derive eta = h - H, u = hu/h, v = hv/h (reference src/sw2d/main.cpp:199-210)
  * and VtkOutputter::writeFieldToFile (reference include/VtkOutputter.hpp:48-101) interpolates each to the equispaced

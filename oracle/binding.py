@@ -41,6 +41,7 @@ def lib():
         L.oracle_depth_to_H.restype = None
         L.oracle_bed_slopes.argtypes = [C.POINTER(bdg_dgcontext2d), _dp, _dp, _dp]
         L.oracle_bed_slopes.restype = None
+        L.oracle_sw2d_rhs_tracer.argtypes = [C.POINTER(bdg_dgcontext2d), C.POINTER(bdg_sw2d_params), _dp, _dp, _dp, _dp, _dp]
         L.oracle_lserk4_stage.argtypes = [C.c_int, C.c_double, C.c_size_t, _dp, _dp, _dp]
         L.oracle_lserk4_stage.restype = None
         L.oracle_lserk4_coeffs.argtypes = [_dp, _dp]
@@ -81,6 +82,23 @@ class Oracle:
         lib().oracle_sw2d_rhs(C.byref(self.cctx), C.byref(self.prm), _d(self.H), _d(self.Hx), _d(self.Hy), _d(h), _d(hu),
                               _d(hv), t, ng, _d(ghost), _d(out[0]), _d(out[1]), _d(out[2]))
         return out
+
+    def rhs_tracer(self, h, hu, hv, hN):
+        """RHS4 of the tracer equation (swhelpers/rhs.py:206-297), per-face LF."""
+        h, hu, hv, hN = _c(h), _c(hu), _c(hv), _c(hN)
+        out = np.empty_like(h)
+        lib().oracle_sw2d_rhs_tracer(C.byref(self.cctx), C.byref(self.prm), _d(h), _d(hu), _d(hv), _d(hN), _d(out))
+        return out
+
+    def step_with_tracer(self, h, hu, hv, hN, res, nsteps, dt):
+        """In-place nsteps LSERK4 steps of flow + tracer (res: 4 residual arrays); every stage evaluates both RHS on the
+        same pre-stage state, as sw2d.py:129-140 does."""
+        for _ in range(nsteps):
+            for st in range(5):
+                R = self.rhs(h, hu, hv)
+                R4 = self.rhs_tracer(h, hu, hv, hN)
+                for rhs, r, q in zip(R + [R4], res, (h, hu, hv, hN)):
+                    self.stage(st, dt, rhs, r, q)
 
     def timestep(self, h, hu, hv, use_abs=False):
         h, hu, hv = _c(h), _c(hu), _c(hv)

@@ -302,6 +302,71 @@ int oracle_sw2d_rhs(const bdg_dgcontext2d *dg, const bdg_sw2d_params *prm, const
   return 0;
 }
 
+/* 4th (tracer) equation of the reference's Python drivers, swhelpers/rhs.py:206-297 with swhelpers/flux.py:18-20:
+ * F4 = hN*u, G4 = hN*v, per-face LF speed of the flow (rhs.py:259-268), reflected momentum on walls (rhs.py:236-238;
+ * hN+ = hN- there because vmapP = vmapM).  Sweep structure of the Python code: whole-array statements, np.dot
+ * contractions (sequential here).  RHS4 [Np][K] row-major. */
+int oracle_sw2d_rhs_tracer(const bdg_dgcontext2d *dg, const bdg_sw2d_params *prm, const double *h, const double *hu,
+                           const double *hv, const double *hN, double *RHS4) {
+  const int Np = dg->Np, Nfp = dg->Nfp, Nf = dg->Nfaces, K = dg->K, Nfn = Nf * Nfp;
+  const size_t nF = (size_t)Nfn * K, nT = (size_t)Np * K;
+  const double g = prm->g;
+  double *hC = dalloc(nT), *huC = dalloc(nT), *hvC = dalloc(nT), *hNC = dalloc(nT), *nxC = dalloc(nF), *nyC = dalloc(nF);
+  oracle_full_to_vector(h, hC, Np, K);
+  oracle_full_to_vector(hu, huC, Np, K);
+  oracle_full_to_vector(hv, hvC, Np, K);
+  oracle_full_to_vector(hN, hNC, Np, K);
+  oracle_full_to_vector(dg->nx, nxC, Nfn, K);
+  oracle_full_to_vector(dg->ny, nyC, Nfn, K);
+  double *hM = dalloc(nF), *hP = dalloc(nF), *uM = dalloc(nF), *uP = dalloc(nF), *vM = dalloc(nF), *vP = dalloc(nF),
+         *nM = dalloc(nF), *nP = dalloc(nF), *huM = dalloc(nF), *huP = dalloc(nF), *hvM = dalloc(nF), *hvP = dalloc(nF);
+  for (size_t i = 0; i < nF; ++i) {
+    const int mM = dg->vmapM[i], mP = dg->vmapP[i];
+    hM[i] = hC[mM]; hP[i] = hC[mP];
+    uM[i] = huC[mM] / hC[mM]; uP[i] = huC[mP] / hC[mP];
+    vM[i] = hvC[mM] / hC[mM]; vP[i] = hvC[mP] / hC[mP];
+    nM[i] = hNC[mM]; nP[i] = hNC[mP];
+  }
+  for (size_t i = 0; i < nF; ++i) { huM[i] = hM[i] * uM[i]; hvM[i] = hM[i] * vM[i]; huP[i] = hP[i] * uP[i]; hvP[i] = hP[i] * vP[i]; } /* rhs.py:228-232 */
+  for (int j = 0; j < dg->bc_count[3]; ++j) { /* rhs.py:236-238 */
+    const int w = dg->bc_face_nodes[3][j];
+    const double d = huM[w] * nxC[w] + hvM[w] * nyC[w];
+    huP[w] = huM[w] - 2 * nxC[w] * d;
+    hvP[w] = hvM[w] - 2 * nyC[w] * d;
+  }
+  double *F4M = dalloc(nF), *G4M = dalloc(nF), *F4P = dalloc(nF), *G4P = dalloc(nF), *spd = dalloc(nF), *dF = dalloc(nF);
+  for (size_t i = 0; i < nF; ++i) { /* flux.py:6-20 at the traces */
+    const double um = huM[i] / hM[i], vm = hvM[i] / hM[i], up = huP[i] / hP[i], vp = hvP[i] / hP[i];
+    F4M[i] = nM[i] * um; G4M[i] = nM[i] * vm;
+    F4P[i] = nP[i] * up; G4P[i] = nP[i] * vp;
+    const double sM = sqrt(um * um + vm * vm) + sqrt(g * hM[i]), sP = sqrt(up * up + vp * vp) + sqrt(g * hP[i]);
+    spd[i] = sM > sP ? sM : sP;
+  }
+  for (size_t c = 0; c < (size_t)Nf * K; ++c) { /* rhs.py:266-268 */
+    double m = spd[c * Nfp];
+    for (int j = 1; j < Nfp; ++j)
+      if (spd[c * Nfp + j] > m) m = spd[c * Nfp + j];
+    for (int j = 0; j < Nfp; ++j) spd[c * Nfp + j] = m;
+  }
+  for (size_t i = 0; i < nF; ++i) dF[i] = 0.5 * ((F4M[i] - F4P[i]) * nxC[i] + (G4M[i] - G4P[i]) * nyC[i] - spd[i] * (nM[i] - nP[i]));
+  double *dFm = dalloc(nF), *F4 = dalloc(nT), *G4 = dalloc(nT), *a = dalloc(nT), *b = dalloc(nT), *sr = dalloc(nF);
+  oracle_vector_to_full(dF, dFm, Nfn, K);
+  for (size_t m = 0; m < nT; ++m) { const double u = hu[m] / h[m], v = hv[m] / h[m]; F4[m] = hN[m] * u; G4[m] = hN[m] * v; }
+  contract(dg->Dr, Np, Np, F4, K, a);
+  contract(dg->Ds, Np, Np, F4, K, b);
+  for (size_t m = 0; m < nT; ++m) RHS4[m] = -(dg->rx[m] * a[m] + dg->sx[m] * b[m]);
+  contract(dg->Dr, Np, Np, G4, K, a);
+  contract(dg->Ds, Np, Np, G4, K, b);
+  for (size_t m = 0; m < nT; ++m) RHS4[m] = RHS4[m] + (-(dg->ry[m] * a[m] + dg->sy[m] * b[m]));
+  for (size_t i = 0; i < nF; ++i) sr[i] = dg->Fscale[i] * dFm[i];
+  contract(dg->Lift, Np, Nfn, sr, K, a);
+  for (size_t m = 0; m < nT; ++m) RHS4[m] = RHS4[m] + a[m];
+  free(hC); free(huC); free(hvC); free(hNC); free(nxC); free(nyC); free(hM); free(hP); free(uM); free(uP); free(vM); free(vP);
+  free(nM); free(nP); free(huM); free(huP); free(hvM); free(hvP); free(F4M); free(G4M); free(F4P); free(G4P); free(spd); free(dF);
+  free(dFm); free(F4); free(G4); free(a); free(b); free(sr);
+  return 0;
+}
+
 /* sw2d::computeTimeStep (main.cpp:253-277); use_abs=1 gives the sw2d-simple variant (abs(Fscale), :108-109).
  * Returns max_i(Fscale_i*spd_i) in *fsc_max as well so ranks can reduce it. */
 double oracle_sw2d_timestep(const bdg_dgcontext2d *dg, const bdg_sw2d_params *prm, const double *h,

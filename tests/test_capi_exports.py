@@ -60,7 +60,8 @@ def test_null_handle_is_rejected_by_every_entry_point():
         "bdg_sw2d_output_wait": (nul,), "bdg_sw2d_limit_positivity": (nul,), "bdg_sw2d_stage_state": (nul, dp, dp, dp, 0.0),
         "bdg_sw2d_commit_state": (nul,), "bdg_sw2d_get_state_async": (nul, dp, dp, dp), "bdg_sw2d_get_state_wait": (nul,),
         "bdg_sw2d_set_variant": (nul, 1), "bdg_sw2d_comm_init": (nul, nul), "bdg_sw2d_halo_pack_to_host": (nul, dp),
-        "bdg_sw2d_halo_set_ghosts": (nul, dp),
+        "bdg_sw2d_halo_set_ghosts": (nul, dp), "bdg_sw2d_set_tracer": (nul, dp), "bdg_sw2d_get_tracer": (nul, dp),
+        "bdg_sw2d_rhs_tracer": (nul, dp),
     }
     for name, args in calls.items():
         assert getattr(lib, name)(*args) == capi.BDG_E_INVALID, name

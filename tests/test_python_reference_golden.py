@@ -120,6 +120,16 @@ def test_numpy_transcription_matches_tracer_equation(ref):
         assert relerr(R[c], ref["swhelpers_cd0_RHS%d" % (c + 1)]) < RHS_TOL, c
 
 
+def test_oracle_tracer_matches_reference_rhs4(ref):
+    """oracle_sw2d_rhs_tracer (C restatement of swhelpers/rhs.py:206-297) against RHS4 of the reference's own function;
+    RHS4 does not see the sources, so both fixture variants (with / without drag) must give it."""
+    ctx = _ctx("coarse_box.msh", False, 4)
+    h, hu, hv, hN = (ref["swhelpers_" + n] for n in ("h", "hu", "hv", "hN"))
+    R4 = _oracle(ctx).rhs_tracer(h, hu, hv, hN)
+    for tag in ("cd0", "cd"):
+        assert relerr(R4, ref["swhelpers_%s_RHS4" % tag]) < RHS_TOL, tag
+
+
 def test_limiter_restatement_matches_reference_function(ref):
     from oracle.output_numpy import positivity_limiter
 
@@ -176,6 +186,57 @@ def test_cuda_matches_swhelpers_rhs_with_sources(ref, tag, CD):
     for c in range(3):
         assert relerr(R[c], want[c]) < RHS_TOL, c
     sol.close()
+
+
+@pytest.mark.gpu
+def test_cuda_tracer_matches_reference_rhs4_and_oracle_steps(ref):
+    """The tracer kernel (sw2d_tracer.cu) through the C ABI: RHS4 against the reference function's output, then LSERK4 and
+    SSP-RK2 steps of flow + tracer against the oracle, on both flow kernel variants (the tracer launch reads the pre-stage
+    flow state beside either)."""
+    from conftest import kernel_variants
+
+    ctx = _ctx("coarse_box.msh", False, 4)
+    h, hu, hv, hN = (ref["swhelpers_" + n] for n in ("h", "hu", "hv", "hN"))
+    sol = _solver(ctx)
+    orc = _oracle(ctx, CFL=0.65)
+    dt = 0.5 * orc.timestep(h, hu, hv, use_abs=True)[0]
+    q = [np.array(a) for a in (h, hu, hv, hN)]
+    res = [np.zeros_like(h) for _ in range(4)]
+    orc.step_with_tracer(q[0], q[1], q[2], q[3], res, 40, dt)
+    for var in kernel_variants(sol):
+        sol.set_variant(var)
+        sol.set_state(h, hu, hv)
+        sol.set_tracer(hN)
+        assert relerr(sol.computeRHS4(), ref["swhelpers_cd0_RHS4"]) < RHS_TOL, var
+        sol.step(40, dt)
+        got = list(sol.get_state()[:3]) + [sol.get_tracer()]
+        for a, b, n in zip(got, q, ("h", "hu", "hv", "hN")):
+            assert relerr(a, b) < STEP_TOL, (var, n)
+        # tracer mass is conserved with all-wall BC (its flux vanishes with the normal velocity)
+        w = np.linalg.inv(ctx.V @ ctx.V.T).sum(axis=0)
+        m0, m1 = (w[:, None] * ctx.J * hN).sum(), (w[:, None] * ctx.J * got[3]).sum()
+        assert abs(m1 - m0) < 1e-11 * abs(m0)
+        # the src/sw2d loop form: hN1 = hN + dt RHS4(q); hN = (hN + hN1 + dt RHS4(q1, hN1)) / 2
+        sol.set_state(h, hu, hv)
+        sol.set_tracer(hN)
+        sol.step_ssprk2(10, dt)
+        a = [np.array(x) for x in (h, hu, hv, hN)]
+        for _ in range(10):
+            R, R4 = orc.rhs(a[0], a[1], a[2]), orc.rhs_tracer(a[0], a[1], a[2], a[3])
+            b = [x + dt * r for x, r in zip(a, R + [R4])]
+            R, R4 = orc.rhs(b[0], b[1], b[2]), orc.rhs_tracer(b[0], b[1], b[2], b[3])
+            a = [0.5 * ((x + y) + dt * r) for x, y, r in zip(a, b, R + [R4])]
+        got = list(sol.get_state()[:3]) + [sol.get_tracer()]
+        for x, y, n in zip(got, a, ("h", "hu", "hv", "hN")):
+            assert relerr(x, y) < STEP_TOL, (var, n)
+    sol.set_tracer(None)
+    with pytest.raises(RuntimeError):
+        sol.get_tracer()
+    sol.close()
+    full = _solver(ctx, mode="full")  # global LF: not the reference's tracer form
+    with pytest.raises(RuntimeError):
+        full.set_tracer(hN)
+    full.close()
 
 
 @pytest.mark.gpu
