@@ -103,6 +103,12 @@ __device__ __forceinline__ void compute_sync() { asm volatile("bar.sync 1, %0;" 
 // the shared fp64 pipe for the arithmetic; a NaN compares largest and so reaches the blow-up guard
 __device__ __forceinline__ double dmax(double a, double b) { return __double_as_longlong(a) > __double_as_longlong(b) ? a : b; }
 
+// max(x, 0), min(x, 0) and "x > 0" through the sign / bit pattern (integer pipe instead of DSETP / DMNMX on the shared fp64 pipe).
+// A NaN produced by the arithmetic here is the canonical positive one and passes through pos_part / is_pos unchanged.
+__device__ __forceinline__ double pos_part(double x) { return __double2hiint(x) < 0 ? 0.0 : x; }
+__device__ __forceinline__ double neg_part(double x) { return __double2hiint(x) < 0 ? x : 0.0; }
+__device__ __forceinline__ bool is_pos(double x) { return __double_as_longlong(x) > 0; }
+
 // 1/x: MUFU seed (20+ bits) + two Newton steps; no denormal / inf handling (h > 0 here)
 __device__ __forceinline__ double frcp(double x) {
   double r;
@@ -176,8 +182,17 @@ struct Cfg {
   static constexpr int gfit_best(bool full) {
     return gfit(BDG_MINBLOCKS, full) >= 96 ? gfit(BDG_MINBLOCKS, full) : (gfit(2, full) >= 96 ? gfit(2, full) : gfit(1, full));
   }
+  // CTAs per SM the persistent kernel is built for: the first of (BDG_MINBLOCKS, 2, 1) whose buffers hold >= 96 ghosts.
+  // N <= 4: 3; N = 5: 2; N >= 6 (operator in shared memory, 0.9-1.4 K nodes per tile): 1.
+  static constexpr int ctas_best(bool full) { return gfit(BDG_MINBLOCKS, full) >= 96 ? BDG_MINBLOCKS : (gfit(2, full) >= 96 ? 2 : 1); }
   static constexpr int GFIT = gfit_best(false);
   static constexpr int GFIT_FULL = gfit_best(true);
+  // register split of the persistent kernel's two warpgroups (setmaxnreg): compute / copy
+  static constexpr int regs_compute(bool full) { return ctas_best(full) >= 3 ? 136 : (ctas_best(full) == 2 ? 208 : 0); }
+  static constexpr int regs_copy(bool full) { return ctas_best(full) >= 3 ? 24 : (ctas_best(full) == 2 ? 40 : 0); }
+  static constexpr int CTAS = ctas_best(false), CTAS_FULL = ctas_best(true);
+  static constexpr int REGS_COMPUTE = regs_compute(false), REGS_COMPUTE_FULL = regs_compute(true);
+  static constexpr int REGS_COPY = regs_copy(false), REGS_COPY_FULL = regs_copy(true);
 };
 
 struct StageArgs {
@@ -282,7 +297,7 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
                                              const double *__restrict__ sAff, const uint32_t *__restrict__ sLm, const double *__restrict__ sDl,
                                              double *__restrict__ sFl, const double *__restrict__ sA, const double *Areg, const int *fm, int PS,
                                              int nnodes, long long kt0, bool need_res, uint64_t *bar_res, uint32_t res_parity, double dtv,
-                                             double tide, double tide_next, double &lam_next PROF_ARGS) {
+                                             double lamg, double tide, double tide_next, double &lam_next PROF_ARGS) {
   using C = Cfg<NP, NFP>;
   constexpr int NFN = C::NFN, NPB = C::NPB, NFB = C::NFB, KB = C::KB, MB = C::MB, TNP = C::TNP;
   const int FPS = FULL ? TNP : PS;  // stride of the flux planes
@@ -333,7 +348,8 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   const bool any_wall = __any_sync(0xffffffffu, bcmask != 0u);
   double sfl[NFB][3];  // Fscale * dFlux_i at my slots = LIFT-part B fragments
   if constexpr (FULL) {
-    const double lamg = v.scal[p.slot];  // global LF speed of this state (main.cpp:413-414), from the previous stage's epilogue or k_speed
+    // lamg: global LF speed of this state (main.cpp:413-414), from the previous stage's epilogue or k_speed; read ONCE per
+    // launch by the caller (a load per tile would put an L2 round trip into every phase 2)
     const double qnan = __longlong_as_double(0x7ff8000000000000LL);
     auto pass_f = [&](auto with_bc) {
 #pragma unroll
@@ -358,9 +374,9 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
         }
         // star states (main.cpp:355-368): h-* = max(0, h- + min(H+ - H-, 0)), h+* = max(0, h+ - max(H+ - H-, 0)); the momenta
         // keep their values (hu* = h* (hu / h*) after h = h*), a dry trace poisons them like the reference's 0/0
-        const double hMs = fmax(0.0, hM + fmin(dlt, 0.0)), hPs = fmax(0.0, hP - fmax(dlt, 0.0));
-        if (!(hMs > 0.0)) huM = hvM = qnan;
-        if (!(hPs > 0.0)) huP = hvP = qnan;
+        const double hMs = pos_part(hM + neg_part(dlt)), hPs = pos_part(hP - pos_part(dlt));
+        if (!is_pos(hMs)) huM = hvM = qnan;
+        if (!is_pos(hPs)) huP = hvP = qnan;
         const double rM = frcp(hMs), rP = frcp(hPs);
         const double uM = huM * rM, vM = hvM * rM, uP = huP * rP, vP = hvP * rP;
         const double pM = (half_g * hMs) * hMs, pP = (half_g * hPs) * hPs;
@@ -377,7 +393,7 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   const uint32_t wallmask = bcmask;
   double lam0 = 0.0, lam1 = 0.0, lam2 = 0.0;  // per-face max speed (scalars: a runtime face index must not spill)
   if (v.lf_global) {
-    lam0 = lam1 = lam2 = v.scal[p.slot];
+    lam0 = lam1 = lam2 = lamg;
   } else {
     auto pass_a = [&](auto with_wall) {
 #pragma unroll
@@ -575,8 +591,8 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
         double huM = sQ[PS + m], hvM = sQ[2 * PS + m];
         const double Hm = dlt;
         if (tag == 3u || tag == 2u) dlt = 0.0;
-        const double hMs = fmax(0.0, hM + fmin(dlt, 0.0));
-        if (!(hMs > 0.0)) huM = hvM = qnan;
+        const double hMs = pos_part(hM + neg_part(dlt));
+        if (!is_pos(hMs)) huM = hvM = qnan;
         const double rM = frcp(hMs), uM = huM * rM, vM = hvM * rM;
         double sp = fsqrt(fma(uM, uM, fma(vM, vM, 1e-300))) + fsqrt(g * hMs);
         if (tag == 3u) {  // wall: reflected momentum over the same depth
@@ -584,8 +600,8 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
           const double uP = fma(-2.0 * ux, d, huM) * rM, vP = fma(-2.0 * uy, d, hvM) * rM;
           sp = dmax(sp, fsqrt(fma(uP, uP, fma(vP, vP, 1e-300))) + fsqrt(g * hMs));
         } else if (tag == 2u) {  // Out: tidal depth of the next evaluation, momentum copied
-          const double hPs = fmax(0.0, Hm + tide_next);
-          const double rP = frcp(hPs), uP = (hPs > 0.0 ? huM : qnan) * rP, vP = (hPs > 0.0 ? hvM : qnan) * rP;
+          const double hPs = pos_part(Hm + tide_next);
+          const double rP = frcp(hPs), uP = (is_pos(hPs) ? huM : qnan) * rP, vP = (is_pos(hPs) ? hvM : qnan) * rP;
           sp = dmax(sp, fsqrt(fma(uP, uP, fma(vP, vP, 1e-300))) + fsqrt(g * hPs));
         }
         lam_next = dmax(lam_next, sp);
@@ -663,6 +679,7 @@ __global__ void __launch_bounds__(kThreads, FULL ? 2 : 3) k_fused_edge(Sw2dView 
   const double dtv = p.write_rhs ? 1.0 : v.scal[S_DT];
   load_constants<NP, NFP>(p, v, Areg, S.A(), fm, dtv);
   double tide = 0.0, tide_next = 0.0, lam_next = 0.0;
+  const double lamg = (FULL || v.lf_global) ? v.scal[p.slot] : 0.0;
   if (FULL) {
     const double t = v.scal[S_T];
     tide = tide_level(v, t);
@@ -671,7 +688,7 @@ __global__ void __launch_bounds__(kThreads, FULL ? 2 : 3) k_fused_edge(Sw2dView 
   __syncthreads();
 
   PROF_DECL
-  compute_tile<NP, NFP, FULL>(v, p, sQ, sR, sAff, sLm, sDl, S.Fl(), S.A(), Areg, fm, PS, TNP + gc, kt0, need_res, nullptr, 0, dtv, tide,
+  compute_tile<NP, NFP, FULL>(v, p, sQ, sR, sAff, sLm, sDl, S.Fl(), S.A(), Areg, fm, PS, TNP + gc, kt0, need_res, nullptr, 0, dtv, lamg, tide,
                               tide_next, lam_next PROF_PASS);
   if (p.write_rhs) return;
   if (FULL) {
@@ -724,7 +741,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
 }
 
 template <int NP, int NFP, bool FULL>
-__global__ void __launch_bounds__(kThreadsWS, BDG_MINBLOCKS) k_fused_persistent(Sw2dView v, StageArgs p) {
+__global__ void __launch_bounds__(kThreadsWS, FULL ? Cfg<NP, NFP>::CTAS_FULL : Cfg<NP, NFP>::CTAS) k_fused_persistent(Sw2dView v, StageArgs p) {
   using C = Cfg<NP, NFP>;
   constexpr int TNP = C::TNP;
   constexpr int GF = FULL ? C::GFIT_FULL : C::GFIT;
@@ -759,7 +776,8 @@ __global__ void __launch_bounds__(kThreadsWS, BDG_MINBLOCKS) k_fused_persistent(
   __syncthreads();
 
   if (w >= kWarps) {  // ------------------------------------------------------------------ copy warp
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
+    constexpr int kRegsCopy = FULL ? C::REGS_COPY_FULL : C::REGS_COPY;
+    if constexpr (kRegsCopy > 0) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsCopy));
     if (w > kWarps) return;
     auto gather = [&](int b, int gcount, const int32_t *ids) {
       double *dst = S.Q(b) + TNP;
@@ -863,12 +881,14 @@ __global__ void __launch_bounds__(kThreadsWS, BDG_MINBLOCKS) k_fused_persistent(
   }
 
   // ---------------------------------------------------------------------------------------- compute warps
-  asm volatile("setmaxnreg.inc.sync.aligned.u32 136;");
+  constexpr int kRegsCompute = FULL ? C::REGS_COMPUTE_FULL : C::REGS_COMPUTE;
+  if constexpr (kRegsCompute > 0) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsCompute));
   double Areg[C::A_REGS ? C::MB * C::KB : 1];
   int fm[C::NFB];
   const double dtv = v.scal[S_DT];
   load_constants<NP, NFP>(p, v, Areg, S.A(), fm, dtv);
   double tide = 0.0, tide_next = 0.0, lam_next = 0.0;
+  const double lamg = (FULL || v.lf_global) ? v.scal[p.slot] : 0.0;
   if (FULL) {
     const double t = v.scal[S_T];
     tide = tide_level(v, t);
@@ -884,7 +904,7 @@ __global__ void __launch_bounds__(kThreadsWS, BDG_MINBLOCKS) k_fused_persistent(
     mbar_wait(&bar[b], (it >> 1) & 1);
     PROF_T(1);
     compute_tile<NP, NFP, FULL>(v, p, S.Q(b), S.R(), S.Aff(b), S.Lm(b), S.Dl(b), S.Fl(), S.A(), Areg, fm, PS, TNP + rc.y, (long long)rc.x * kTile,
-                                need_res, &bar[2], it & 1, dtv, tide, tide_next, lam_next PROF_PASS);
+                                need_res, &bar[2], it & 1, dtv, lamg, tide, tide_next, lam_next PROF_PASS);
     PROF_T(7);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     compute_sync();
@@ -1098,7 +1118,9 @@ void arrange_slots(int Np, int Nfp, int Nfn, int NFB, bool face_blocks, const in
   }
 }
 
-#define BDG_FUSED_ORDERS(X) X(3, 2) X(6, 3) X(10, 4) X(15, 5) X(21, 6)
+// simple physics: N = 1..8; full physics (a second instantiation of every kernel): N = 1..5
+#define BDG_FUSED_ORDERS_FULL(X) X(3, 2) X(6, 3) X(10, 4) X(15, 5) X(21, 6)
+#define BDG_FUSED_ORDERS(X) BDG_FUSED_ORDERS_FULL(X) X(28, 7) X(36, 8) X(45, 9)
 
 }  // namespace
 
@@ -1107,7 +1129,7 @@ void arrange_slots(int Np, int Nfp, int Nfn, int NFB, bool face_blocks, const in
 // two-launch path.
 int fused_supported(const bdg_sw2d *s) {
   if (!s->is_affine || s->v.Nf != 3 || s->v.use_filter) return 0;
-  if (s->v.full && !s->v.lf_global) return 0;
+  if (s->v.full && (!s->v.lf_global || s->v.Np > 21)) return 0;
 #define X(np, nfp) \
   if (s->v.Np == np && s->v.Nfp == nfp) return 1;
   BDG_FUSED_ORDERS(X)
@@ -1211,7 +1233,7 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
   int cap_full = 0;
 #define X(np, nfp) \
   if (Np == np && Nfp == nfp) cap_full = Cfg<np, nfp>::GFIT_FULL;
-  BDG_FUSED_ORDERS(X)
+  BDG_FUSED_ORDERS_FULL(X)
 #undef X
   for (int T = 0; T < ntiles; ++T) {
     const int4 r = make_int4(T, cnt[T], (int)(goff[T] & 0xffffffffLL), (int)(goff[T] >> 32));
@@ -1340,9 +1362,15 @@ cudaError_t launch_fused_stage(bdg_sw2d *s, const double *q_in, double *q_out, d
   // stage), nothing (first SSP-RK2 stage, RHS evaluation)
   args.r_src = write_rhs ? nullptr : (args.mode == 1 ? (a != 0.0 ? res : nullptr) : (args.mode == 3 ? q_out : nullptr));
   args.store_res = !write_rhs && args.mode == 1;
-#define X(np, nfp)                                                        \
-  if (ops->Np == np && ops->Nfp == nfp)                                   \
-    return s->v.full ? launch_t<np, nfp, true>(s, args, ops) : launch_t<np, nfp, false>(s, args, ops);
+  if (s->v.full) {
+#define X(np, nfp) \
+  if (ops->Np == np && ops->Nfp == nfp) return launch_t<np, nfp, true>(s, args, ops);
+    BDG_FUSED_ORDERS_FULL(X)
+#undef X
+    return cudaErrorNotSupported;
+  }
+#define X(np, nfp) \
+  if (ops->Np == np && ops->Nfp == nfp) return launch_t<np, nfp, false>(s, args, ops);
   BDG_FUSED_ORDERS(X)
 #undef X
   return cudaErrorNotSupported;

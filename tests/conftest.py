@@ -46,7 +46,11 @@ def fused_expected(sol):
     structured mesh is still affine) of the instantiated orders, no RHS filter; full physics (star states + sources) in
     its reference form, i.e. with the global Lax-Friedrichs speed."""
     c = sol.ctx
-    return c.Nfaces == 3 and c.N <= 5 and not sol.prm.filter and (not sol.prm.sources or sol.prm.lf_mode == 1)
+    if c.Nfaces != 3 or sol.prm.filter:
+        return False
+    if sol.prm.sources:  # full physics: orders 1..5, global LF
+        return c.N <= 5 and sol.prm.lf_mode == 1
+    return c.N <= 8
 
 
 def kernel_variants(sol):

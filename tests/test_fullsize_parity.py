@@ -100,7 +100,7 @@ def record(name, row):
 
 CASES = [  # name, shape, N, nx, ny, oracle strips (total, evaluated), fused variant expected
     ("config 2: 1M tri N=4", "tri", 4, 1000, 500, (8, None), True),
-    ("config 3: 4M tri N=8", "tri", 8, 2000, 1000, (40, None), False),
+    ("config 3: 4M tri N=8", "tri", 8, 2000, 1000, (40, None), True),
     ("config 4: 2M quad N=6", "quad", 6, 2000, 1000, (40, None), False),
     ("config 5: 16M tri N=4", "tri", 4, 4000, 2000, (16, (0, 7, 8)), True),  # oracle on 3 M elements: boundary strip + the two around the hump
 ]
@@ -124,7 +124,7 @@ def test_full_mesh_rhs_against_oracle_and_arbiter(name, shape, N, nx, ny, strips
     sol = SW2dSolver(ctx)
     sol.set_state(h, hu, hv)
     variants = [1]
-    if fused:  # affine triangles N <= 5: the fused kernel is the product, its absence is a failure
+    if fused:  # affine triangles N <= 8: the fused kernel is the product, its absence is a failure
         sol.set_variant(2)
         variants.append(2)
     Rc = {}
