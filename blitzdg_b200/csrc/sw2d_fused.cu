@@ -97,7 +97,8 @@ __device__ __forceinline__ void dmma884(double &d0, double &d1, double a, double
 }
 
 // barrier of the kThreads compute threads (the persistent kernel has a fifth, copy-only warp that never joins it)
-__device__ __forceinline__ void compute_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kThreads) : "memory"); }
+template <int NT>
+__device__ __forceinline__ void compute_sync() { asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory"); }
 
 // max of two NON-NEGATIVE doubles (wave speeds) through their bit patterns: integer compares instead of DSETP keep
 // the shared fp64 pipe for the arithmetic; a NaN compares largest and so reaches the blow-up guard
@@ -191,6 +192,14 @@ struct Cfg {
   static constexpr int regs_compute(bool full) { return ctas_best(full) >= 3 ? 136 : (ctas_best(full) == 2 ? 208 : 0); }
   static constexpr int regs_copy(bool full) { return ctas_best(full) >= 3 ? 24 : (ctas_best(full) == 2 ? 40 : 0); }
   static constexpr int CTAS = ctas_best(false), CTAS_FULL = ctas_best(true);
+  // Compute warps per tile.  With ONE CTA per SM (N >= 6) four warps leave a single warp per scheduler, which cannot hide
+  // the A-fragment loads and the DMMA latency (measured: DMMA pipe 47 % active at N = 8); there TWO warps share each group
+  // of 8 elements and split the row blocks of the contraction (WH = 2): both build the same B fragments (pointwise work
+  // that is small against 560 DMMAs per group), each owns half of the accumulators and of the epilogue rows.
+  static constexpr int WH = (CTAS == 1 && MB >= 2) ? 2 : 1;
+  static constexpr int NCW = 4 * WH, NCT = 32 * NCW;  // compute warps / threads
+  static constexpr int NTWS = NCT + 128;              // persistent kernel: + the copy warpgroup
+  static constexpr int RBH = (MB + WH - 1) / WH;      // row blocks per warp
   static constexpr int REGS_COMPUTE = regs_compute(false), REGS_COMPUTE_FULL = regs_compute(true);
   static constexpr int REGS_COPY = regs_copy(false), REGS_COPY_FULL = regs_copy(true);
 };
@@ -248,14 +257,14 @@ struct Smem {
 // Phase 1 for U nodes of one thread at once (j, j + kThreads, ...): the U dependency chains (reciprocal, two
 // square roots) are independent straight-line code, so the scheduler interleaves them.  Indices behind the
 // tile's last node are clamped: such lanes recompute (and re-store) the last node's values.
-template <int U, bool FULL>
+template <int U, bool FULL, int NT>
 __device__ __forceinline__ void phase1_nodes(const double *__restrict__ sQ, double *__restrict__ sFl, int PS, int FPS, int j0, int last, double g,
                                              double half_g) {
   int j[U];
   double h[U], hu[U], hv[U];
 #pragma unroll
   for (int u = 0; u < U; ++u) {
-    j[u] = min(j0 + u * kThreads, last);
+    j[u] = min(j0 + u * NT, last);
     h[u] = sQ[j[u]];
     hu[u] = sQ[PS + j[u]];
     hv[u] = sQ[2 * PS + j[u]];
@@ -299,9 +308,12 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
                                              int nnodes, long long kt0, bool need_res, uint64_t *bar_res, uint32_t res_parity, double dtv,
                                              double lamg, double tide, double tide_next, double &lam_next PROF_ARGS) {
   using C = Cfg<NP, NFP>;
-  constexpr int NFN = C::NFN, NPB = C::NPB, NFB = C::NFB, KB = C::KB, MB = C::MB, TNP = C::TNP;
+  constexpr int NFN = C::NFN, NPB = C::NPB, NFB = C::NFB, KB = C::KB, MB = C::MB, TNP = C::TNP, NT = C::NCT, RBH = C::RBH;
+  static_assert(!(C::A_REGS && C::WH > 1) && !(FULL && C::WH > 1), "the split-row-block layout is built for the big orders");
   const int FPS = FULL ? TNP : PS;  // stride of the flux planes
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31, wfull = threadIdx.x >> 5;
+  const int w = wfull & 3;             // element group of my warp: elements w + 4*c'
+  const int rb0 = C::WH > 1 ? (wfull >> 2) * RBH : 0;  // first row block of my warp (WH = 2: the upper warps take the second half)
   const int c = lane >> 2, t = lane & 3;
   const int e = w + 4 * (c < 4 ? c : (c ^ 1));  // my element (B-fragment column c); E(c) keeps B and C accesses conflict-free
   const int eo = e * NP;
@@ -311,16 +323,16 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   // ---- phase 1: nodal fluxes (+ wave speed / 1/h) at own (and, simple mode, ghost) nodes (A6, A7), flat mapping ----
   {
     const int nn = FULL ? TNP : nnodes;
-    const int wbase = w * 32, last = nn - 1;
+    const int wbase = wfull * 32, last = nn - 1;
     int i = 0;
-    for (; wbase + (i + 2) * kThreads < nn; i += 3) phase1_nodes<3, FULL>(sQ, sFl, PS, FPS, threadIdx.x + i * kThreads, last, g, half_g);
-    if (wbase + (i + 1) * kThreads < nn)
-      phase1_nodes<2, FULL>(sQ, sFl, PS, FPS, threadIdx.x + i * kThreads, last, g, half_g);
-    else if (wbase + i * kThreads < nn)
-      phase1_nodes<1, FULL>(sQ, sFl, PS, FPS, threadIdx.x + i * kThreads, last, g, half_g);
+    for (; wbase + (i + 2) * NT < nn; i += 3) phase1_nodes<3, FULL, NT>(sQ, sFl, PS, FPS, threadIdx.x + i * NT, last, g, half_g);
+    if (wbase + (i + 1) * NT < nn)
+      phase1_nodes<2, FULL, NT>(sQ, sFl, PS, FPS, threadIdx.x + i * NT, last, g, half_g);
+    else if (wbase + i * NT < nn)
+      phase1_nodes<1, FULL, NT>(sQ, sFl, PS, FPS, threadIdx.x + i * NT, last, g, half_g);
   }
   PROF_T(2);
-  compute_sync();
+  compute_sync<NT>();
   PROF_T(3);
 
   // ---- phase 2: face slots of my element: '+' trace, BC, speed, flux jump (A1-A8) ---------------------
@@ -455,42 +467,44 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   if (any_wall) pass_b(std::true_type{}); else pass_b(std::false_type{});
   }
   PROF_T(4);
-  compute_sync();  // all '+' lookups into sQ/sFl are done: the tile may now be updated in place
+  compute_sync<NT>();  // all '+' lookups into sQ/sFl are done: the tile may now be updated in place
   PROF_T(5);
-  // ---- phase 3: B fragments -> DMMA (six independent accumulator chains: 3 fields x MB row blocks) -> stage update
+  // ---- phase 3: B fragments -> DMMA (3 fields x RBH row blocks of independent accumulator chains) -> stage update
+  // My row blocks are rb0 .. rb0+RBH-1 (WH = 1: all of them, rb0 = 0 at compile time).  A second-half warp whose last
+  // row block lies behind MB (odd MB) computes it on the clamped operator block and drops the result.
   const double rx = af[0], sx = af[1], ry = af[2], sy = af[3];
   const int gr = lane >> 2;  // C fragment row within a row block
   const int c0 = 2 * t, c1 = 2 * t + 1;
   const int e0 = w + 4 * (c0 < 4 ? c0 : (c0 ^ 1));  // C fragment column 2t   -> element E(2t)
   const int e1 = w + 4 * (c1 < 4 ? c1 : (c1 ^ 1));  // C fragment column 2t+1 -> element E(2t+1)
   // full mode: static Hx, Hy (and the sponge coefficient) of my 4 C-fragment nodes, fetched now, used after the contraction
-  double sHx[MB][2], sHy[MB][2], sSg[MB][2];
+  double sHx[RBH][2], sHy[RBH][2], sSg[RBH][2];
   if constexpr (FULL) {
 #pragma unroll
-    for (int rb = 0; rb < MB; ++rb)
+    for (int r = 0; r < RBH; ++r)
 #pragma unroll
       for (int cc = 0; cc < 2; ++cc) {
-        const int n = min(8 * rb + gr, NP - 1);
+        const int n = min(8 * (rb0 + r) + gr, NP - 1);
         const long long gm = min(kt0 + (cc ? e1 : e0), (long long)v.K - 1) * NP + n;
-        sHx[rb][cc] = __ldg(v.Hx + gm);
-        sHy[rb][cc] = __ldg(v.Hy + gm);
+        sHx[r][cc] = __ldg(v.Hx + gm);
+        sHy[r][cc] = __ldg(v.Hy + gm);
       }
   }
   const bool sponge = p.mode != 1 && v.sponge != nullptr;
   if (sponge) {
 #pragma unroll
-    for (int rb = 0; rb < MB; ++rb)
+    for (int r = 0; r < RBH; ++r)
 #pragma unroll
       for (int cc = 0; cc < 2; ++cc) {
-        const int n = min(8 * rb + gr, NP - 1);
-        sSg[rb][cc] = __ldg(v.sponge + min(kt0 + (cc ? e1 : e0), (long long)v.K - 1) * NP + n);
+        const int n = min(8 * (rb0 + r) + gr, NP - 1);
+        sSg[r][cc] = __ldg(v.sponge + min(kt0 + (cc ? e1 : e0), (long long)v.K - 1) * NP + n);
       }
   }
-  double acc[3][MB][2];
+  double acc[3][RBH][2];
 #pragma unroll
-  for (int rb = 0; rb < MB; ++rb)
+  for (int r = 0; r < RBH; ++r)
 #pragma unroll
-    for (int i = 0; i < 3; ++i) acc[i][rb][0] = acc[i][rb][1] = 0.0;
+    for (int i = 0; i < 3; ++i) acc[i][r][0] = acc[i][r][1] = 0.0;
 #pragma unroll
   for (int kb = 0; kb < NPB; ++kb) {
     const int n = eo + min(4 * kb + t, NP - 1);  // padding rows of B meet zero columns of A
@@ -500,61 +514,65 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
     ba[1] = fma(rx, F2, ry * G2); bb[1] = fma(sx, F2, sy * G2);
     ba[2] = fma(rx, G2, ry * G3); bb[2] = fma(sx, G2, sy * G3);
 #pragma unroll
-    for (int rb = 0; rb < MB; ++rb) {
-      const double a1 = C::A_REGS ? Areg[rb * KB + kb] : sA[(rb * KB + kb) * 32 + lane];
-      const double a2 = C::A_REGS ? Areg[rb * KB + NPB + kb] : sA[(rb * KB + NPB + kb) * 32 + lane];
+    for (int r = 0; r < RBH; ++r) {
+      const int rb = min(rb0 + r, MB - 1);
+      const double a1 = C::A_REGS ? Areg[r * KB + kb] : sA[(rb * KB + kb) * 32 + lane];
+      const double a2 = C::A_REGS ? Areg[r * KB + NPB + kb] : sA[(rb * KB + NPB + kb) * 32 + lane];
 #pragma unroll
-      for (int i = 0; i < 3; ++i) dmma884(acc[i][rb][0], acc[i][rb][1], a1, ba[i]);
+      for (int i = 0; i < 3; ++i) dmma884(acc[i][r][0], acc[i][r][1], a1, ba[i]);
 #pragma unroll
-      for (int i = 0; i < 3; ++i) dmma884(acc[i][rb][0], acc[i][rb][1], a2, bb[i]);
+      for (int i = 0; i < 3; ++i) dmma884(acc[i][r][0], acc[i][r][1], a2, bb[i]);
     }
   }
 #pragma unroll
   for (int kb = 0; kb < NFB; ++kb) {
 #pragma unroll
-    for (int rb = 0; rb < MB; ++rb) {
-      const double a3 = C::A_REGS ? Areg[rb * KB + 2 * NPB + kb] : sA[(rb * KB + 2 * NPB + kb) * 32 + lane];
+    for (int r = 0; r < RBH; ++r) {
+      const int rb = min(rb0 + r, MB - 1);
+      const double a3 = C::A_REGS ? Areg[r * KB + 2 * NPB + kb] : sA[(rb * KB + 2 * NPB + kb) * 32 + lane];
 #pragma unroll
-      for (int i = 0; i < 3; ++i) dmma884(acc[i][rb][0], acc[i][rb][1], a3, sfl[kb][i]);
+      for (int i = 0; i < 3; ++i) dmma884(acc[i][r][0], acc[i][r][1], a3, sfl[kb][i]);
     }
   }
   // res is first needed here, a whole DMMA chain after the tile's other inputs: its load (which has to wait for the
   // previous tile's store to drain from the same buffer) hides behind the contraction
   if (bar_res) mbar_wait(bar_res, res_parity);
   PROF_T(6);
-  __syncwarp();  // every lane's B-fragment reads of this warp's elements precede the in-place update below
+  // every B-fragment read of an element precedes its in-place update below: the readers are the lanes of this warp
+  // (WH = 1) or of the two warps that share the element group (WH = 2: a CTA-wide barrier of the compute warps)
+  if constexpr (C::WH > 1) compute_sync<NT>(); else __syncwarp();
   // sources (main.cpp:460-483) at my C-fragment nodes: g h Hx - CD u |u| + f hv  and  g h Hy - CD v |u| - f hu, times dt
   if constexpr (FULL) {
 #pragma unroll
-    for (int rb = 0; rb < MB; ++rb)
+    for (int r = 0; r < RBH; ++r)
 #pragma unroll
       for (int cc = 0; cc < 2; ++cc) {
-        const int o = (cc ? e1 : e0) * NP + min(8 * rb + gr, NP - 1);
-        const double h = sQ[o], hu = sQ[PS + o], hv = sQ[2 * PS + o], r = sFl[3 * FPS + o];
-        const double u = hu * r, vv = hv * r, nu = fsqrt(fma(u, u, fma(vv, vv, 1e-300))), gh = g * h;
-        acc[1][rb][cc] = fma(dtv, fma(v.fcor, hv, fma(-v.CD * u, nu, gh * sHx[rb][cc])), acc[1][rb][cc]);
-        acc[2][rb][cc] = fma(dtv, fma(-v.fcor, hu, fma(-v.CD * vv, nu, gh * sHy[rb][cc])), acc[2][rb][cc]);
+        const int o = (cc ? e1 : e0) * NP + min(8 * (rb0 + r) + gr, NP - 1);
+        const double h = sQ[o], hu = sQ[PS + o], hv = sQ[2 * PS + o], rr = sFl[3 * FPS + o];
+        const double u = hu * rr, vv = hv * rr, nu = fsqrt(fma(u, u, fma(vv, vv, 1e-300))), gh = g * h;
+        acc[1][r][cc] = fma(dtv, fma(v.fcor, hv, fma(-v.CD * u, nu, gh * sHx[r][cc])), acc[1][r][cc]);
+        acc[2][r][cc] = fma(dtv, fma(-v.fcor, hu, fma(-v.CD * vv, nu, gh * sHy[r][cc])), acc[2][r][cc]);
       }
   }
   // epilogue: rows n = 8*rb + gr of elements e0, e1; acc = a*res + dt*rhs (stage mode) or rhs (write_rhs mode)
   if (p.write_rhs) {
 #pragma unroll
-    for (int rb = 0; rb < MB; ++rb) {
-      const int n = 8 * rb + gr;
+    for (int r = 0; r < RBH; ++r) {
+      const int n = 8 * (rb0 + r) + gr;
 #pragma unroll
       for (int cc = 0; cc < 2; ++cc) {
         const long long k = kt0 + (cc ? e1 : e0);
         if (n < NP && k >= p.k0 && k < p.k1) {
 #pragma unroll
-          for (int i = 0; i < 3; ++i) p.rhs_out[(long long)i * NP * v.K + k * NP + n] = acc[i][rb][cc];
+          for (int i = 0; i < 3; ++i) p.rhs_out[(long long)i * NP * v.K + k * NP + n] = acc[i][r][cc];
         }
       }
     }
     return;
   }
 #pragma unroll
-  for (int rb = 0; rb < MB; ++rb) {
-    const int n = 8 * rb + gr;
+  for (int r = 0; r < RBH; ++r) {
+    const int n = 8 * (rb0 + r) + gr;
     if (n < NP) {
 #pragma unroll
       for (int i = 0; i < 3; ++i) {
@@ -562,12 +580,12 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
         for (int cc = 0; cc < 2; ++cc) {
           const int o = (cc ? e1 : e0) * NP + n;
           if (p.mode == 1) {  // LSERK4 stage (src/advec1d/main.cpp:98,101)
-            const double rs = need_res ? fma(p.a, sR[i * TNP + o], acc[i][rb][cc]) : acc[i][rb][cc];
+            const double rs = need_res ? fma(p.a, sR[i * TNP + o], acc[i][r][cc]) : acc[i][r][cc];
             sR[i * TNP + o] = rs;
             sQ[i * PS + o] = fma(p.b, rs, sQ[i * PS + o]);
           } else {  // SSP-RK2 stages of the src/sw2d driver (main.cpp:217-219, 230-232) + sponge relaxation (:222-224, :235-236)
-            double val = p.mode == 2 ? sQ[i * PS + o] + acc[i][rb][cc] : 0.5 * ((sR[i * TNP + o] + sQ[i * PS + o]) + acc[i][rb][cc]);
-            if (sponge && i > 0 && sSg[rb][cc] != 0.0) val = val * frcp(fma(sSg[rb][cc] * val, val, 1.0));
+            double val = p.mode == 2 ? sQ[i * PS + o] + acc[i][r][cc] : 0.5 * ((sR[i * TNP + o] + sQ[i * PS + o]) + acc[i][r][cc]);
+            if (sponge && i > 0 && sSg[r][cc] != 0.0) val = val * frcp(fma(sSg[r][cc] * val, val, 1.0));
             sQ[i * PS + o] = val;
           }
         }
@@ -628,7 +646,7 @@ __device__ __forceinline__ void load_constants(const StageArgs &p, const Sw2dVie
 #pragma unroll
     for (int i = 0; i < C::MB * C::KB; ++i) Areg[i] = scale * __ldg(p.Afrag + i * 32 + lane);
   } else {
-    for (int x = tid; x < C::MB * C::KB * 32; x += kThreads) sA[x] = scale * __ldg(p.Afrag + x);
+    for (int x = tid; x < C::MB * C::KB * 32; x += C::NCT) sA[x] = scale * __ldg(p.Afrag + x);
   }
 #pragma unroll
   for (int kb = 0; kb < C::NFB; ++kb) fm[kb] = __ldg(p.slotinfo + 4 * kb + (lane & 3));
@@ -638,9 +656,9 @@ __device__ __forceinline__ void load_constants(const StageArgs &p, const Sw2dVie
 // ---- edge kernel: one tile per CTA, any tile (ragged mesh end, partially active range, write_rhs, tiles with
 // more ghost nodes than the persistent kernel's buffers hold) --------------------------------------------------
 template <int NP, int NFP, bool FULL>
-__global__ void __launch_bounds__(kThreads, FULL ? 2 : 3) k_fused_edge(Sw2dView v, StageArgs p) {
+__global__ void __launch_bounds__(Cfg<NP, NFP>::NCT, (FULL || Cfg<NP, NFP>::CTAS < 3) ? (Cfg<NP, NFP>::CTAS < 2 ? 1 : 2) : 3) k_fused_edge(Sw2dView v, StageArgs p) {
   using C = Cfg<NP, NFP>;
-  constexpr int NFN = C::NFN, TNP = C::TNP;
+  constexpr int NFN = C::NFN, TNP = C::TNP, kThreads = C::NCT;
   extern __shared__ __align__(128) unsigned char smem[];
   const Smem<NP, NFP, FULL> S{smem, 1, p.G};
   const int PS = S.PS();
@@ -693,7 +711,7 @@ __global__ void __launch_bounds__(kThreads, FULL ? 2 : 3) k_fused_edge(Sw2dView 
   if (p.write_rhs) return;
   if (FULL) {
     // elements outside the active range / behind the mesh end must not contribute (their values are not stored)
-    const int lane = tid & 31, w = tid >> 5, c = lane >> 2;
+    const int lane = tid & 31, w = (tid >> 5) & 3, c = lane >> 2;
     const long long k = kt0 + w + 4 * (c < 4 ? c : (c ^ 1));
     if (!(k >= p.k0 && k < p.k1)) lam_next = 0.0;
     publish_speed(v, p, lam_next);
@@ -734,14 +752,13 @@ __global__ void __launch_bounds__(kThreads, FULL ? 2 : 3) k_fused_edge(Sw2dView 
 // of tile it+1 (ids came with tile it) -> drain -> res of tile it -> bulk load of tile it+1 into the drained buffer.
 // 2 warpgroups: warps 0..3 compute, warp 4 copies, warps 5..7 only give their registers back (setmaxnreg works per
 // warpgroup): launched at 80 registers/thread (3 CTAs/SM), the compute warpgroup grows to 136, the other shrinks to 24.
-constexpr int kThreadsWS = 2 * kThreads;
 
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
 template <int NP, int NFP, bool FULL>
-__global__ void __launch_bounds__(kThreadsWS, FULL ? Cfg<NP, NFP>::CTAS_FULL : Cfg<NP, NFP>::CTAS) k_fused_persistent(Sw2dView v, StageArgs p) {
+__global__ void __launch_bounds__(Cfg<NP, NFP>::NTWS, FULL ? Cfg<NP, NFP>::CTAS_FULL : Cfg<NP, NFP>::CTAS) k_fused_persistent(Sw2dView v, StageArgs p) {
   using C = Cfg<NP, NFP>;
   constexpr int TNP = C::TNP;
   constexpr int GF = FULL ? C::GFIT_FULL : C::GFIT;
@@ -775,10 +792,10 @@ __global__ void __launch_bounds__(kThreadsWS, FULL ? Cfg<NP, NFP>::CTAS_FULL : C
   }
   __syncthreads();
 
-  if (w >= kWarps) {  // ------------------------------------------------------------------ copy warp
+  if (w >= C::NCW) {  // ------------------------------------------------------------------ copy warp
     constexpr int kRegsCopy = FULL ? C::REGS_COPY_FULL : C::REGS_COPY;
     if constexpr (kRegsCopy > 0) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsCopy));
-    if (w > kWarps) return;
+    if (w > C::NCW) return;
     auto gather = [&](int b, int gcount, const int32_t *ids) {
       double *dst = S.Q(b) + TNP;
       for (int x = lane; x < gcount; x += 32) {
@@ -894,7 +911,7 @@ __global__ void __launch_bounds__(kThreadsWS, FULL ? Cfg<NP, NFP>::CTAS_FULL : C
     tide = tide_level(v, t);
     tide_next = p.last_stage ? tide_level(v, t + dtv) : tide;
   }
-  compute_sync();
+  compute_sync<C::NCT>();
   PROF_DECL
   for (int it = 0;; ++it) {
     const int b = it & 1;
@@ -907,7 +924,7 @@ __global__ void __launch_bounds__(kThreadsWS, FULL ? Cfg<NP, NFP>::CTAS_FULL : C
                                 need_res, &bar[2], it & 1, dtv, lamg, tide, tide_next, lam_next PROF_PASS);
     PROF_T(7);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    compute_sync();
+    compute_sync<C::NCT>();
     if (tid == 0) mbar_arrive(&bar[3 + b]);
     PROF_T(8);
   }
@@ -958,7 +975,7 @@ cudaError_t launch_t(bdg_sw2d *s, StageArgs a, const FusedOps *ops) {
     if ((e = cudaFuncSetAttribute(k_fused_persistent<NP, NFP, FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pers)) != cudaSuccess) return e;
     cudaFuncSetAttribute(k_fused_edge<NP, NFP, FULL>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     cudaFuncSetAttribute(k_fused_persistent<NP, NFP, FULL>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm[dev], k_fused_persistent<NP, NFP, FULL>, kThreadsWS, smem_pers)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm[dev], k_fused_persistent<NP, NFP, FULL>, C::NTWS, smem_pers)) != cudaSuccess) return e;
     if ((e = cudaDeviceGetAttribute(&g_sm_count[dev], cudaDevAttrMultiProcessorCount, s->device)) != cudaSuccess) return e;
     if (ctas_per_sm[dev] < 1) return cudaErrorLaunchOutOfResources;
     attr_key[dev] = ops->Gmax * 4096 + Gcap + 1;
@@ -979,7 +996,7 @@ cudaError_t launch_t(bdg_sw2d *s, StageArgs a, const FusedOps *ops) {
     h.tile0 = use_list ? 0 : first;
     h.list_first = use_list ? first : 0;
     h.ntiles = count;
-    k_fused_edge<NP, NFP, FULL><<<count, kThreads, smem_edge, s->stream>>>(s->v, h);
+    k_fused_edge<NP, NFP, FULL><<<count, C::NCT, smem_edge, s->stream>>>(s->v, h);
     s->launches++;
   };
   edge(t0, p0 - t0, 0);
@@ -995,7 +1012,7 @@ cudaError_t launch_t(bdg_sw2d *s, StageArgs a, const FusedOps *ops) {
       // while a halo exchange is in flight leave a few SMs one CTA short, so the NCCL send/recv kernel finds room
       if (s->comm && !s->peer_ok && s->n_nbr > 0 && a.k0 == 0 && a.k1 < s->v.K) grid -= 16;
       if (grid > m.ntiles) grid = m.ntiles;
-      k_fused_persistent<NP, NFP, FULL><<<grid, kThreadsWS, smem_pers, s->stream>>>(s->v, m);
+      k_fused_persistent<NP, NFP, FULL><<<grid, C::NTWS, smem_pers, s->stream>>>(s->v, m);
       s->launches++;
     }
     const int jb0 = (int)(std::lower_bound(big_tiles.begin(), big_tiles.end(), p0) - big_tiles.begin());
@@ -1007,7 +1024,7 @@ cudaError_t launch_t(bdg_sw2d *s, StageArgs a, const FusedOps *ops) {
       h.G = ops->Gmax;
       h.biglist = FULL ? ops->biglist_full : ops->biglist;
       h.use_list = 1; h.tile0 = 0; h.list_first = jb0; h.ntiles = jb1 - jb0;
-      k_fused_edge<NP, NFP, FULL><<<jb1 - jb0, kThreads, smem_edge, s->stream>>>(s->v, h);
+      k_fused_edge<NP, NFP, FULL><<<jb1 - jb0, C::NCT, smem_edge, s->stream>>>(s->v, h);
       s->launches++;
     }
   }
@@ -1285,8 +1302,8 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
     return e;
   }
 #ifdef BDG_PHASEPROF
-  cudaMalloc((void **)&ops->prof, sizeof(long long) * kWarps * 12);
-  cudaMemset(ops->prof, 0, sizeof(long long) * kWarps * 12);
+  cudaMalloc((void **)&ops->prof, sizeof(long long) * 8 * 12);
+  cudaMemset(ops->prof, 0, sizeof(long long) * 8 * 12);
 #endif
   ops->n_slots = (long long)ntiles * kTile * Nfn;
   s->fused_ops = ops;
@@ -1323,7 +1340,7 @@ void fused_release(bdg_sw2d *s) {
   FusedOps *ops = static_cast<FusedOps *>(s->fused_ops);
 #ifdef BDG_PHASEPROF
   if (ops->prof) {
-    long long h[kWarps * 12];
+    long long h[8 * 12];
     cudaMemcpy(h, ops->prof, sizeof(h), cudaMemcpyDeviceToHost);
     static const char *nm[12] = {"top+gather", "wait tile", "phase1", "sync1", "phase2", "sync2", "wait res", "phase3", "fence+sync3", "store+reissue", "", ""};
     for (int w = 0; w < kWarps; ++w) {

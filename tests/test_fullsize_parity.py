@@ -73,18 +73,7 @@ def geometry_noise(ctx):
     return worst
 
 
-def mean_geometry(ctx):
-    """The context with every affine geometry factor replaced by its element / face mean, as bdg_sw2d_create folds them."""
-    import copy
-
-    c = copy.copy(ctx)
-    for name in ("rx", "sx", "ry", "sy"):
-        a = getattr(ctx, name)
-        setattr(c, name, np.ascontiguousarray(np.broadcast_to(a.mean(axis=0, keepdims=True), a.shape)))
-    for name in ("nx", "ny", "Fscale"):
-        a = getattr(ctx, name).reshape(ctx.Nfaces, ctx.Nfp, -1)
-        setattr(c, name, np.ascontiguousarray(np.broadcast_to(a.mean(axis=1, keepdims=True), a.shape).reshape(ctx.Nfaces * ctx.Nfp, -1)))
-    return c
+from conftest import mean_geometry  # noqa: E402
 
 
 def record(name, row):

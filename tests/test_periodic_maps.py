@@ -7,7 +7,7 @@ neighbour: the device element order, the fused kernel's tiles and the global-spe
 """
 import numpy as np
 import pytest
-from conftest import kernel_variants
+from conftest import kernel_variants, mean_geometry
 
 from blitzdg_b200.synthetic import provision, structured_mesh
 
@@ -109,12 +109,27 @@ def test_cuda_periodic_seam(shape, N, mode):
     res = [np.zeros_like(h) for _ in range(3)]
     dt = 1e-3
     orc.step(ho, huo, hvo, res, 50, dt)
+    # The fused kernel reads 13 geometry doubles per straight-sided triangle -- the element / face means of the per-node copies
+    # the reference stores.  Those copies scatter by the rounding noise of the reference's own setup; where a field's RHS is a
+    # small remainder of large terms (RHS1 here: 0.65 against flux derivatives of 50-160) that scatter alone moves the
+    # reference-ordered result by more than 1e-12 at N = 7 (5e-12, measured with the extended-precision arbiter on both
+    # geometries -- no kernel involved).  Variant 2 is therefore held to the oracle on the SAME averaged geometry at 1e-12,
+    # and to the plain oracle within that measured effect.
+    Rom = None
+    if 2 in variants and ctx.Nfaces == 3:
+        om = _oracle(mean_geometry(ctx), lf_mode=int(full), sources=int(full))
+        om.set_bathymetry(H, z, z)
+        Rom = om.rhs(h, hu, hv)
     for var in variants:
         sol.set_variant(var)
         sol.set_state(h, hu, hv)
         R = sol.computeRHS()
         for c in range(3):
-            assert relerr(R[c], Ro[c]) < RHS_TOL, (var, c)
+            if var == 2 and Rom is not None:
+                assert relerr(R[c], Rom[c]) < RHS_TOL, (var, c)
+                assert relerr(R[c], Ro[c]) < RHS_TOL + 1.1 * relerr(Rom[c], Ro[c]), (var, c)
+            else:
+                assert relerr(R[c], Ro[c]) < RHS_TOL, (var, c)
         sol.step(50, dt)
         out = sol.get_state()
         for a, b in zip(out[:3], (ho, huo, hvo)):
