@@ -869,6 +869,10 @@ static int enqueue_tracer_stage(bdg_sw2d *s, double a, double b, int mode) {
 // ====================================================================================== hot path
 static int use_fused(const bdg_sw2d *s) {
   if (s->variant == 1) return 0;
+  // variant 0 (auto) = the faster path as measured on B200 (profiles/r02_fused_orders.md): the fused single-launch kernel
+  // for N <= 5 and N = 8; at N = 6, 7 (one CTA of four compute warps per SM) the two-launch DMMA path is ahead (66 vs 58 and
+  // 64 vs 58 G DSU/s), so auto keeps it there; variant 2 still selects the fused kernel explicitly.
+  if (s->variant == 0 && (s->v.Np == 28 || s->v.Np == 36)) return 0;
   return s->fused_ok;
 }
 

@@ -196,7 +196,9 @@ struct Cfg {
   // the A-fragment loads and the DMMA latency (measured: DMMA pipe 47 % active at N = 8); there TWO warps share each group
   // of 8 elements and split the row blocks of the contraction (WH = 2): both build the same B fragments (pointwise work
   // that is small against 560 DMMAs per group), each owns half of the accumulators and of the epilogue rows.
-  static constexpr int WH = (CTAS == 1 && MB >= 2) ? 2 : 1;
+  // Measured (profiles/r02_fused_orders.md): N = 8 62.9 -> 67.0 G DSU/s; at N = 6, 7 (4-5 row blocks) the duplicated phase 2 costs
+  // more than the split saves (58 -> 51 G), so those keep four warps.
+  static constexpr int WH = (CTAS == 1 && MB >= 6) ? 2 : 1;
   static constexpr int NCW = 4 * WH, NCT = 32 * NCW;  // compute warps / threads
   static constexpr int NTWS = NCT + 128;              // persistent kernel: + the copy warpgroup
   static constexpr int RBH = (MB + WH - 1) / WH;      // row blocks per warp
