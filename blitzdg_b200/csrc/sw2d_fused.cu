@@ -1166,6 +1166,7 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
 
   const int ntiles = (K + kTile - 1) / kTile;
   const int tnp = kTile * Np;
+  const long long nT = (long long)Np * K;  // first halo slot
   std::vector<uint32_t> lmap((size_t)ntiles * kTile * Nfn);
   std::vector<int32_t> gflat;           // ghosts of all tiles back to back
   std::vector<size_t> goff(ntiles + 1, 0);
@@ -1178,7 +1179,8 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
       for (int sl = 0; sl < Nfn; ++sl) {
         const int32_t mP = vmapP[(kt0 + el) * Nfn + sl];
         const long long r = (long long)mP - base;
-        if (r < 0 || r >= tnp) ext.push_back(mP);
+        // (halo slots Np*K + g are ALWAYS external: in the ragged last tile they would otherwise alias the padding nodes)
+        if (r < 0 || r >= tnp || mP >= nT) ext.push_back(mP);
       }
     std::sort(ext.begin(), ext.end());
     ext.erase(std::unique(ext.begin(), ext.end()), ext.end());
@@ -1195,7 +1197,7 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
           const int32_t mP = vmapP[(kt0 + el) * Nfn + sl];
           const long long r = (long long)mP - base;
           uint32_t loc;
-          if (r >= 0 && r < tnp)
+          if (r >= 0 && r < tnp && mP < nT)
             loc = (uint32_t)r;
           else
             loc = (uint32_t)(tnp + (std::lower_bound(ext.begin(), ext.end(), mP) - ext.begin()));

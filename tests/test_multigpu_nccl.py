@@ -85,6 +85,7 @@ def _worker(rank, world, idfile, N, mode, variant, how, halo_path, sequence, out
     Ro = orc.rhs(h, hu, hv)
     R = sol.computeRHS()
     e_rhs = max(np.abs(R[c] - Ro[c][:, el]).max() / np.abs(Ro[c]).max() for c in range(3))
+    phases = [("rhs0", e_rhs)]
     dt = 0.4 * orc.timestep(h, hu, hv, use_abs=True)[0]
     nsteps = 25
     sol.step(nsteps, dt)
@@ -93,6 +94,7 @@ def _worker(rank, world, idfile, N, mode, variant, how, halo_path, sequence, out
     orc.step(ho, huo, hvo, res, nsteps, dt)
     hg, hug, hvg, _ = sol.get_state()
     e_step = _relmax(((hg, ho), (hug, huo), (hvg, hvo)), el)
+    phases.append(("lserk4_25", e_step))
     if sequence:
         # step -> step_ssprk2 -> limiter -> step -> computeRHS on ONE handle: every switch between the peer-store path
         # (LSERK4, fused) and the NCCL path (SSP-RK2 runs on the two-launch kernels) must re-validate the ghost traces
@@ -100,13 +102,17 @@ def _worker(rank, world, idfile, N, mode, variant, how, halo_path, sequence, out
 
         sol.step_ssprk2(6, 0.5 * dt)
         orc.step_ssprk2(ho, huo, hvo, 6, 0.5 * dt, t=nsteps * dt)
+        phases.append(("ssprk2_6", _relmax(zip(sol.get_state()[:3], (ho, huo, hvo)), el)))
         sol.positivityPreservingLimiter2D()
         ho, huo, hvo = (np.ascontiguousarray(a) for a in positivity_limiter(ho, huo, hvo))
+        phases.append(("limiter", _relmax(zip(sol.get_state()[:3], (ho, huo, hvo)), el)))
         sol.step(4, dt)
         orc.step(ho, huo, hvo, res, 4, dt)  # the residual carries over in both (a_0 = 0 wipes it in the first stage)
+        phases.append(("lserk4_4", _relmax(zip(sol.get_state()[:3], (ho, huo, hvo)), el)))
         Rg = sol.computeRHS()
         Ro2 = orc.rhs(ho, huo, hvo)
         e_rhs = max(e_rhs, max(np.abs(Rg[c] - Ro2[c][:, el]).max() / np.abs(Ro2[c]).max() for c in range(3)))
+        phases.append(("rhs1", e_rhs))
         sol.step(3, dt)
         orc.step(ho, huo, hvo, res, 3, dt)
         hg, hug, hvg, _ = sol.get_state()
@@ -121,7 +127,7 @@ def _worker(rank, world, idfile, N, mode, variant, how, halo_path, sequence, out
     sol.check()  # raises on a halo timeout (sticky flag) or a blow-up
     var = sol.variant
     sol.close()
-    out.put((rank, e_rhs, e_step, var, len(halo["nbr_rank"]), int(halo["n_interior"]), len(el), stats["neighbours"]))
+    out.put((rank, e_rhs, e_step, var, len(halo["nbr_rank"]), int(halo["n_interior"]), len(el), stats["neighbours"], [(n, float("%.2e" % v)) for n, v in phases]))
 
 
 CASES = [  # world, N, mode, variant, partition, halo path, mixed call sequence
@@ -130,6 +136,10 @@ CASES = [  # world, N, mode, variant, partition, halo path, mixed call sequence
     (2, 3, "full", 0, "strips", "nccl", False),
     (2, 4, "simple", 2, "metis", "peer", True),
     (2, 4, "simple", 2, "strips", "nccl", False),   # the fused kernel over ncclSend/ncclRecv
+    (2, 4, "simple", 2, "metis", "peer", False),
+    (2, 4, "simple", 2, "strips", "peer", True),
+    (2, 4, "simple", 2, "metis", "nccl", True),
+    (2, 4, "simple", 1, "metis", "nccl", True),
     (4, 4, "simple", 2, "strips", "peer", False),   # two neighbours per rank: what the scaling bench times
     (4, 4, "simple", 2, "metis", "peer", True),
     (4, 4, "simple", 2, "metis", "nccl", True),
