@@ -502,6 +502,16 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
         sSg[r][cc] = __ldg(v.sponge + min(kt0 + (cc ? e1 : e0), (long long)v.K - 1) * NP + n);
       }
   }
+  // Full physics: phase 2 needs most of the register file, so operator fragments that live across the tile loop get
+  // rematerialised by the compiler one at a time right at their DMMA (a global load + the dt scaling in front of every
+  // DMMA: 14 % of the stall samples).  Here they are re-read explicitly instead -- 24 independent L1 hits issued together at
+  // the start of the contraction, when the phase-2 temporaries are dead -- unscaled; dt is applied to the accumulators.
+  constexpr bool A_RELOAD = FULL && C::A_REGS;
+  double Aloc[A_RELOAD ? MB * KB : 1];
+  if constexpr (A_RELOAD) {
+#pragma unroll
+    for (int i = 0; i < MB * KB; ++i) asm volatile("ld.global.nc.f64 %0, [%1];" : "=d"(Aloc[i]) : "l"(p.Afrag + i * 32 + lane));
+  }
   double acc[3][RBH][2];
 #pragma unroll
   for (int r = 0; r < RBH; ++r)
@@ -518,8 +528,8 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
 #pragma unroll
     for (int r = 0; r < RBH; ++r) {
       const int rb = min(rb0 + r, MB - 1);
-      const double a1 = C::A_REGS ? Areg[r * KB + kb] : sA[(rb * KB + kb) * 32 + lane];
-      const double a2 = C::A_REGS ? Areg[r * KB + NPB + kb] : sA[(rb * KB + NPB + kb) * 32 + lane];
+      const double a1 = C::A_REGS ? (A_RELOAD ? Aloc[r * KB + kb] : Areg[r * KB + kb]) : sA[(rb * KB + kb) * 32 + lane];
+      const double a2 = C::A_REGS ? (A_RELOAD ? Aloc[r * KB + NPB + kb] : Areg[r * KB + NPB + kb]) : sA[(rb * KB + NPB + kb) * 32 + lane];
 #pragma unroll
       for (int i = 0; i < 3; ++i) dmma884(acc[i][r][0], acc[i][r][1], a1, ba[i]);
 #pragma unroll
@@ -531,7 +541,7 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
 #pragma unroll
     for (int r = 0; r < RBH; ++r) {
       const int rb = min(rb0 + r, MB - 1);
-      const double a3 = C::A_REGS ? Areg[r * KB + 2 * NPB + kb] : sA[(rb * KB + 2 * NPB + kb) * 32 + lane];
+      const double a3 = C::A_REGS ? (A_RELOAD ? Aloc[r * KB + 2 * NPB + kb] : Areg[r * KB + 2 * NPB + kb]) : sA[(rb * KB + 2 * NPB + kb) * 32 + lane];
 #pragma unroll
       for (int i = 0; i < 3; ++i) dmma884(acc[i][r][0], acc[i][r][1], a3, sfl[kb][i]);
     }
@@ -543,6 +553,12 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   // every B-fragment read of an element precedes its in-place update below: the readers are the lanes of this warp
   // (WH = 1) or of the two warps that share the element group (WH = 2: a CTA-wide barrier of the compute warps)
   if constexpr (C::WH > 1) compute_sync<NT>(); else __syncwarp();
+  if constexpr (A_RELOAD) {  // the operator was not pre-scaled: acc = RHS -> dt * RHS
+#pragma unroll
+    for (int r = 0; r < RBH; ++r)
+#pragma unroll
+      for (int i = 0; i < 3; ++i) { acc[i][r][0] *= dtv; acc[i][r][1] *= dtv; }
+  }
   // sources (main.cpp:460-483) at my C-fragment nodes: g h Hx - CD u |u| + f hv  and  g h Hy - CD v |u| - f hu, times dt
   if constexpr (FULL) {
 #pragma unroll
@@ -640,11 +656,13 @@ __device__ __forceinline__ void publish_speed(const Sw2dView &v, const StageArgs
 
 // per-thread constants: operator fragments scaled by `scale` (dt, or 1 in write_rhs mode), and for each of my
 // B-fragment positions 4*kb+t the face slot that sits there: '-' node offset | face << 16 | slot << 20
-template <int NP, int NFP>
+template <int NP, int NFP, bool FULL = false>
 __device__ __forceinline__ void load_constants(const StageArgs &p, const Sw2dView &v, double *Areg, double *sA, int *fm, double scale) {
   using C = Cfg<NP, NFP>;
   const int tid = threadIdx.x, lane = tid & 31;
-  if (C::A_REGS) {
+  if (C::A_REGS && FULL) {
+    // full physics: the operator fragments are re-read (L1) at the start of every contraction, see compute_tile
+  } else if (C::A_REGS) {
 #pragma unroll
     for (int i = 0; i < C::MB * C::KB; ++i) Areg[i] = scale * __ldg(p.Afrag + i * 32 + lane);
   } else {
@@ -697,7 +715,7 @@ __global__ void __launch_bounds__(Cfg<NP, NFP>::NCT, (FULL || Cfg<NP, NFP>::CTAS
   double Areg[C::A_REGS ? C::MB * C::KB : 1];
   int fm[C::NFB];
   const double dtv = p.write_rhs ? 1.0 : v.scal[S_DT];
-  load_constants<NP, NFP>(p, v, Areg, S.A(), fm, dtv);
+  load_constants<NP, NFP, FULL>(p, v, Areg, S.A(), fm, dtv);
   double tide = 0.0, tide_next = 0.0, lam_next = 0.0;
   const double lamg = (FULL || v.lf_global) ? v.scal[p.slot] : 0.0;
   if (FULL) {
@@ -905,7 +923,7 @@ __global__ void __launch_bounds__(Cfg<NP, NFP>::NTWS, FULL ? Cfg<NP, NFP>::CTAS_
   double Areg[C::A_REGS ? C::MB * C::KB : 1];
   int fm[C::NFB];
   const double dtv = v.scal[S_DT];
-  load_constants<NP, NFP>(p, v, Areg, S.A(), fm, dtv);
+  load_constants<NP, NFP, FULL>(p, v, Areg, S.A(), fm, dtv);
   double tide = 0.0, tide_next = 0.0, lam_next = 0.0;
   const double lamg = (FULL || v.lf_global) ? v.scal[p.slot] : 0.0;
   if (FULL) {
