@@ -307,7 +307,7 @@ def run_reference(args):
         return
     world = args.gpus
     cores = os.cpu_count() or 1
-    value, sec, sample, n_stage, t_setup, used = cpu_reference(args, world, cores, budget_s=150.0, steps=max(1, args.steps), warmup=max(1, args.warmup))
+    value, sec, sample, n_stage, t_setup, used = cpu_reference(args, world, cores, budget_s=100.0, steps=max(1, args.steps), warmup=max(1, args.warmup))
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * sec, "higher_is_better": True,

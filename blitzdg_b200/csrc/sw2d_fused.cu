@@ -189,7 +189,10 @@ struct Cfg {
   static constexpr int GFIT = gfit_best(false);
   static constexpr int GFIT_FULL = gfit_best(true);
   // register split of the persistent kernel's two warpgroups (setmaxnreg): compute / copy
-  static constexpr int regs_compute(bool full) { return ctas_best(full) >= 3 ? 136 : (ctas_best(full) == 2 ? 208 : 0); }
+#ifndef BDG_REGS_COMPUTE
+#define BDG_REGS_COMPUTE 136
+#endif
+  static constexpr int regs_compute(bool full) { return ctas_best(full) >= 3 ? BDG_REGS_COMPUTE : (ctas_best(full) == 2 ? 208 : 0); }
   static constexpr int regs_copy(bool full) { return ctas_best(full) >= 3 ? 24 : (ctas_best(full) == 2 ? 40 : 0); }
   static constexpr int CTAS = ctas_best(false), CTAS_FULL = ctas_best(true);
   // Compute warps per tile.  With ONE CTA per SM (N >= 6) four warps leave a single warp per scheduler, which cannot hide
@@ -506,7 +509,11 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   // rematerialised by the compiler one at a time right at their DMMA (a global load + the dt scaling in front of every
   // DMMA: 14 % of the stall samples).  Here they are re-read explicitly instead -- 24 independent L1 hits issued together at
   // the start of the contraction, when the phase-2 temporaries are dead -- unscaled; dt is applied to the accumulators.
+#ifdef BDG_A_RELOAD_SIMPLE
+  constexpr bool A_RELOAD = C::A_REGS;
+#else
   constexpr bool A_RELOAD = FULL && C::A_REGS;
+#endif
   double Aloc[A_RELOAD ? MB * KB : 1];
   if constexpr (A_RELOAD) {
 #pragma unroll
@@ -660,7 +667,12 @@ template <int NP, int NFP, bool FULL = false>
 __device__ __forceinline__ void load_constants(const StageArgs &p, const Sw2dView &v, double *Areg, double *sA, int *fm, double scale) {
   using C = Cfg<NP, NFP>;
   const int tid = threadIdx.x, lane = tid & 31;
-  if (C::A_REGS && FULL) {
+#ifdef BDG_A_RELOAD_SIMPLE
+  constexpr bool kReload = true;
+#else
+  constexpr bool kReload = FULL;
+#endif
+  if (C::A_REGS && kReload) {
     // full physics: the operator fragments are re-read (L1) at the start of every contraction, see compute_tile
   } else if (C::A_REGS) {
 #pragma unroll
