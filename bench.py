@@ -617,18 +617,23 @@ def parity_single(args, ctx, sol, state, device):
     if sol.variant == 2:  # the fused kernel folds the per-node copies of the affine geometry into element / face means
         import copy
 
-        cm = copy.copy(ctx)
+        cm = copy.copy(ctx)  # the geometry the fused kernel reads: element / face means, per-node normals on wall face nodes
         for name in ("rx", "sx", "ry", "sy"):
             a = getattr(ctx, name)
             setattr(cm, name, np.ascontiguousarray(np.broadcast_to(a.mean(axis=0, keepdims=True), a.shape)))
+        Nfn = ctx.Nfaces * ctx.Nfp
+        wall = np.asarray(ctx.BCmap.get(3, ()), dtype=np.int64)
         for name in ("nx", "ny", "Fscale"):
             a = getattr(ctx, name).reshape(ctx.Nfaces, ctx.Nfp, -1)
-            setattr(cm, name, np.ascontiguousarray(np.broadcast_to(a.mean(axis=1, keepdims=True), a.shape).reshape(ctx.Nfaces * ctx.Nfp, -1)))
+            m = np.ascontiguousarray(np.broadcast_to(a.mean(axis=1, keepdims=True), a.shape).reshape(Nfn, -1))
+            if name != "Fscale" and wall.size:
+                m[wall % Nfn, wall // Nfn] = getattr(ctx, name)[wall % Nfn, wall // Nfn]
+            setattr(cm, name, m)
         Rm = Arbiter(cm).rhs(h, hu, hv)
         geo = {"cuda_vs_exact_on_averaged_geometry": max(rel(R[c], Rm[c]) for c in range(3)),
                "geometry_effect": max(rel(Rm[c], Ra[c]) for c in range(3)),
-               "note": "geometry_effect = arbiter(per-node rx..Fscale as the reference stores them) vs arbiter(their element/face means, "
-                       "what the 104 B/element affine kernel reads): the scatter of the reference's own geometry arrays, no kernel involved"}
+               "note": "geometry_effect = arbiter(per-node rx..Fscale as the reference stores them) vs arbiter(their element/face means + per-node "
+                       "wall normals, what the 104 B/element affine kernel reads): the scatter of the reference's own geometry arrays, no kernel involved"}
     out = {"rhs_state": "Gaussian hump + smooth velocity field without normal flow at the walls, whole mesh (%d elements), kernel variant %d" % (ctx.K, sol.variant),
            "geometry": geo,
            "max_rel_err_rhs": max(rel(R[c], Ro[c]) for c in range(3)),

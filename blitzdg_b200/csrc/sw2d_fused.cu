@@ -287,6 +287,19 @@ __device__ __forceinline__ void phase1_nodes(const double *__restrict__ sQ, doub
   }
 }
 
+// Unit normal of ONE wall face node as the reference stores it (nx, ny [K][Nfn]), straight from global memory.  Everywhere else
+// the kernel uses the 13 geometry doubles per element (element / face means of the reference's per-node copies); on a
+// wall the reflection hu+ = hu- - 2 nx (hu- nx + hv- ny) turns a normal that is off by the reference's own setup noise
+// (~1e-13) into a spurious jump of the tangential momentum that Fscale*LIFT ~ 1e4 / h_cell amplifies: with the mean normal
+// the result moves by 5e-10 (config 2) to 4e-8 (config 3) of max|RHS| relative to the reference's, with the face node's own
+// normal by < 1e-11 (measured with the extended-precision arbiter).  Walls are rare: a warp that holds one
+// takes this path.
+__device__ __forceinline__ void wall_normal(const Sw2dView &v, long long k, int slot, int NFN, double &ux, double &uy) {
+  const long long gi = min(k, (long long)v.K - 1) * NFN + slot;
+  ux = __ldg(v.nx + gi);
+  uy = __ldg(v.ny + gi);
+}
+
 // tidal free surface of the Out faces at time t (main.cpp:352): amp cos(om t) (tanh(ramp (t - T)) + 1) / 2
 __device__ __forceinline__ double tide_level(const Sw2dView &v, double t) {
   const double om = 2.0 * 3.1415926535897932 / v.tide_period;
@@ -373,16 +386,20 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
       for (int kb = 0; kb < NFB; ++kb) {
         const int f = (C::FACE_BLOCKS && kb < 3) ? kb : (fm[kb] >> 16) & 15;
         const int m = eo + (fm[kb] & 0xffff), r = word[kb] & 0xffffu;
-        const double nx = af[4 + 3 * f], ny = af[5 + 3 * f], hfs = af[6 + 3 * f];  // (nx, ny, 1) * Fscale/2
+        double nx = af[4 + 3 * f], ny = af[5 + 3 * f];
+        const double hfs = af[6 + 3 * f];  // (nx, ny, 1) * Fscale/2
         double hM = sQ[m], huM = sQ[PS + m], hvM = sQ[2 * PS + m];
         double hP = sQ[r], huP = sQ[PS + r], hvP = sQ[2 * PS + r];
         double dlt = sDl[e * NFN + (fm[kb] >> 20)];
         if (decltype(with_bc)::value && ((bcmask >> kb) & 1u)) {
-          if ((word[kb] >> 16) == 3u) {  // Wall (main.cpp:340-345)
-            const double ih = frcp(hfs), ux = nx * ih, uy = ny * ih, d = huM * ux + hvM * uy;
+          if ((word[kb] >> 16) == 3u) {  // Wall (main.cpp:340-345), with the reference's OWN normal of this face node (see wall_normal)
+            double ux, uy;
+            wall_normal(v, kt0 + e, fm[kb] >> 20, NFN, ux, uy);
+            const double d = huM * ux + hvM * uy;
             hP = hM;
             huP = fma(-2.0 * ux, d, huM);
             hvP = fma(-2.0 * uy, d, hvM);
+            nx = ux * hfs; ny = uy * hfs;
           } else {  // Out (main.cpp:348-353): the slot carries H-
             hP = dlt + tide;
             huP = huM; hvP = hvM;
@@ -451,17 +468,19 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   for (int kb = 0; kb < NFB; ++kb) {
     const int f = (C::FACE_BLOCKS && kb < 3) ? kb : (fm[kb] >> 16) & 15;
     const int m = eo + (fm[kb] & 0xffff), r = word[kb] & 0xffffu;
-    const double nx = af[4 + 3 * f], ny = af[5 + 3 * f], hfs = af[6 + 3 * f];  // (nx, ny, 1) * Fscale/2
+    double nx = af[4 + 3 * f], ny = af[5 + 3 * f];
+    const double hfs = af[6 + 3 * f];  // (nx, ny, 1) * Fscale/2
     const double l = hfs * (f == 0 ? lam0 : (f == 1 ? lam1 : lam2));
     const double hM = sQ[m], huM = sQ[PS + m], hvM = sQ[2 * PS + m];
     const double F2M = sFl[m], G2M = sFl[PS + m], G3M = sFl[2 * PS + m];
     double hP = sQ[r], huP = sQ[PS + r], hvP = sQ[2 * PS + r];
     double F2P = sFl[r], G2P = sFl[PS + r], G3P = sFl[2 * PS + r];
     if (decltype(with_wall)::value && ((wallmask >> kb) & 1u)) {
-      double spd_unused;
+      double spd_unused, ux, uy;
       hP = hM;
-      const double ih = frcp(hfs);
-      wall_trace(nx * ih, ny * ih, hM, huM, hvM, huP, hvP, F2P, G2P, G3P, spd_unused);
+      wall_normal(v, kt0 + e, fm[kb] >> 20, NFN, ux, uy);
+      wall_trace(ux, uy, hM, huM, hvM, huP, hvP, F2P, G2P, G3P, spd_unused);
+      nx = ux * hfs; ny = uy * hfs;
     }
     const double dh = hM - hP, dhu = huM - huP, dhv = hvM - hvP, dG2 = G2M - G2P;
     sfl[kb][0] = fma(-l, dh, fma(dhu, nx, dhv * ny));

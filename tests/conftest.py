@@ -70,7 +70,9 @@ def kernel_variants(sol):
 
 
 def mean_geometry(ctx):
-    """The context with every affine geometry factor replaced by its element / face mean, as bdg_sw2d_create folds them."""
+    """The context as the fused kernel reads it: every affine geometry factor replaced by its element / face mean (the 13
+    doubles per element that bdg_sw2d_create folds), EXCEPT the unit normals of wall face nodes, which the kernel takes
+    per node from the reference's own arrays (sw2d_fused.cu wall_normal)."""
     import copy
 
     import numpy as np
@@ -79,9 +81,12 @@ def mean_geometry(ctx):
     for name in ("rx", "sx", "ry", "sy"):
         a = getattr(ctx, name)
         setattr(c, name, np.ascontiguousarray(np.broadcast_to(a.mean(axis=0, keepdims=True), a.shape)))
+    Nfn = ctx.Nfaces * ctx.Nfp
+    wall = np.asarray(ctx.BCmap.get(3, ()), dtype=np.int64)
     for name in ("nx", "ny", "Fscale"):
         a = getattr(ctx, name).reshape(ctx.Nfaces, ctx.Nfp, -1)
-        setattr(c, name, np.ascontiguousarray(np.broadcast_to(a.mean(axis=1, keepdims=True), a.shape).reshape(ctx.Nfaces * ctx.Nfp, -1)))
+        m = np.ascontiguousarray(np.broadcast_to(a.mean(axis=1, keepdims=True), a.shape).reshape(Nfn, -1))
+        if name != "Fscale" and wall.size:
+            m[wall % Nfn, wall // Nfn] = getattr(ctx, name)[wall % Nfn, wall // Nfn]
+        setattr(c, name, m)
     return c
-
-

@@ -14,17 +14,16 @@ sizes the asserted bound is relative to that measured noise floor:
     cuda_vs_oracle <= 2.5 * oracle_vs_exact + 2e-13      (triangle inequality of the two)
 while the unit-size meshes of tests/test_gpu_parity.py hold the plain 1e-12.
 
-A second, independent limit applies to the fused kernel (variant 2): it reads 13 geometry doubles per straight-sided
+A second, independent effect concerns the fused kernel (variant 2): it reads 13 geometry doubles per straight-sided
 triangle (B_alg's 104 B) where the reference stores rx, sx, ry, sy per NODE and nx, ny, Fscale per FACE NODE.  On an
 affine element those per-node copies are mathematically equal, but the reference's setup computes each from nodal
-coordinates (Dr x with |x| ~ 1 and differences ~ h_cell), so they scatter by eps |Dr| |x| / h_cell: 1e-12 relative in the
-metrics and ~2.5e-13 absolute in the unit normals on the 1 M mesh (`geometry_noise`, measured from the arrays).  The
-kernel uses their mean; the oracle and the arbiter use each node's own copy.  The effect on the RHS is largest on wall
-faces, where a normal that is off by 1e-13 turns tangential momentum into a reflection jump that Fscale*LIFT ~ 1e4/h_cell
-amplifies -- the reference's OWN result there is only defined to that level (another LAPACK build scatters differently,
-SURVEY.md F9).  It is measured without any kernel: `geometry_effect` = arbiter(per-node geometry) vs arbiter(element /
-face means).  So variant 2 is held
-    to the arbiter on the SAME averaged geometry at the fp64 floor:   v2_cuda_vs_exact_meangeom <= 1.5 * floor + 2e-13
+coordinates (Dr x with |x| ~ 1 and differences ~ h_cell), so they scatter by eps |Dr| |x| / h_cell (`geometry_noise`,
+measured from the arrays: 7e-12 on config 2, 6e-11 on config 3).  The kernel uses their mean.  The one place where that
+scatter is amplified is a wall face -- a normal that is off by 1e-13 turns tangential momentum into a reflection jump that
+Fscale*LIFT ~ 1e4/h_cell multiplies (5e-10 of max|RHS| on config 2, 4e-8 on config 3 with mean normals, measured with the
+arbiter) -- so on wall face nodes the kernel reads the reference's own per-node normal.  What remains is measured without
+any kernel: `geometry_effect` = arbiter(per-node geometry) vs arbiter(the geometry the kernel reads).  Variant 2 is held
+    to the arbiter on the SAME geometry at the fp64 floor:            v2_cuda_vs_exact_meangeom <= 1.5 * floor + 2e-13
     to the reference-ordered oracle within floor + that effect:       v2_cuda_vs_oracle <= 2.5 * floor + 1.1 * geometry_effect + 2e-13
 """
 import json
