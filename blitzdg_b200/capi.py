@@ -15,6 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("BDG_B200_LIB") or os.path.join(_HERE, "csrc", "libblitzdg_b200.so")
 
 BDG_OK, BDG_E_INVALID, BDG_E_CUDA, BDG_E_UNSTABLE, BDG_E_NCCL, BDG_E_UNSUPPORTED = range(6)
+BDG_NOALLOC_MAX_FACE_NODES = 1 << 28  # include/blitzdg_b200.h
 BDG_NCCL_ID_BYTES = 128
 
 _dp = C.POINTER(C.c_double)
@@ -127,6 +128,7 @@ EXPORTS = [
     "bdg_sw2d_halo_pack_to_host", "bdg_sw2d_halo_set_ghosts", "bdg_element_order", "bdg_version",
     "bdg_sw2d_set_sponge", "bdg_sw2d_step_ssprk2", "bdg_sw2d_set_output", "bdg_sw2d_output_begin", "bdg_sw2d_output_wait",
     "bdg_sw2d_limit_positivity", "bdg_sw2d_set_tracer", "bdg_sw2d_get_tracer", "bdg_sw2d_rhs_tracer", "bdg_sw2d_stage_state", "bdg_sw2d_commit_state", "bdg_sw2d_get_state_async", "bdg_sw2d_get_state_wait",
+    "bdg_sw2d_timestep_noalloc",
 ]
 
 
@@ -188,5 +190,6 @@ def load():
     L.bdg_sw2d_halo_set_ghosts.argtypes = [vp, _dp]
     L.bdg_element_order.argtypes = [_ip, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _ip]
     L.bdg_version.restype = C.c_int
+    L.bdg_sw2d_timestep_noalloc.argtypes = [C.c_int32] * 6 + [C.c_double, C.c_double, vp, vp, vp, vp, vp, vp, vp, C.c_char_p, C.c_int32]
     _lib = L
     return L

@@ -173,6 +173,27 @@ void *bdg_sw2d_stream(bdg_sw2d *s);
 /* algorithmic bytes of one RHS+stage over this handle's elements (B_alg) */
 double bdg_sw2d_algorithmic_bytes_per_stage(const bdg_sw2d *s);
 
+/* --- allocation-free entry point ---------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The reduction of bdg_sw2d_timestep -- dt = CFL / ((N+1)^2/2 * max over face nodes of Fscale*(|u| + sqrt(g h))) -- on
+ * the CALLER's device arrays, in the reference's native layouts: d_h, d_hu, d_hv [Np][K] row-major, d_Fscale
+ * [Nfaces*Nfp][K] row-major, d_fmask [Nfaces*Nfp] int32 = local node of each face-node slot (Fmask flattened face by
+ * face; vmapM of element 0).  Every d_* pointer is memory of `device`; d_dt_out receives one double.  The kernel is
+ * enqueued on `stream` (a cudaStream_t, NULL = the default stream) and the call returns without synchronising.
+ * It calls no cudaMalloc, cudaFree or allocating library routine: its scratch (one partial maximum per 4096 face nodes
+ * and the ticket word electing the last thread block) is a static __device__ array of 512.25 KB that every GPU loading
+ * the library holds until the process exits.  Hence the limit: Nfaces*Nfp*K <= BDG_NOALLOC_MAX_FACE_NODES, beyond it
+ * BDG_E_UNSUPPORTED (bdg_sw2d_timestep has no such limit).  All calls on a device share that array, which keeps the
+ * last call's contents (the ticket word is cleared on the stream before each launch): calls that overlap on the GPU --
+ * different streams, or host threads without ordering -- race on it and must be serialised by the caller.
+ * err (may be NULL): receives the message of a failed call, at most err_cap bytes including the terminator. */
+#define BDG_NOALLOC_MAX_FACE_NODES (1 << 28)
+int bdg_sw2d_timestep_noalloc(int32_t device, int32_t N, int32_t Np, int32_t Nfp, int32_t Nfaces, int32_t K, double g,
+                              double CFL, const double *d_h, const double *d_hu, const double *d_hv,
+                              const double *d_Fscale, const int32_t *d_fmask, double *d_dt_out, void *stream, char *err,
+                              int32_t err_cap);
+
 /* --- multi-GPU (one process per GPU) ------------------------------------------------------- */
 #define BDG_NCCL_ID_BYTES 128
 int bdg_nccl_unique_id(void *id_out /* BDG_NCCL_ID_BYTES */);
