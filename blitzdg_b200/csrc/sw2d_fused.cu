@@ -207,6 +207,19 @@ struct Cfg {
   static constexpr int RBH = (MB + WH - 1) / WH;      // row blocks per warp
   static constexpr int REGS_COMPUTE = regs_compute(false), REGS_COMPUTE_FULL = regs_compute(true);
   static constexpr int REGS_COPY = regs_copy(false), REGS_COPY_FULL = regs_copy(true);
+  // Residual in C-FRAGMENT order in HBM (simple physics, LSERK4): the residual is private to these kernels, so a tile's block
+  // is stored as [field][row block][4 warps x 32 lanes][2 columns] -- every compute thread reads and writes exactly the
+  // accumulator positions it owns with 16-byte accesses (a warp instruction covers 512 contiguous bytes), and the residual
+  // never passes through shared memory: no R planes, no bulk load / store of them, no barrier between the copy warp and the
+  // epilogue.  Rows NP..8*MB-1 are padding (+1/15 of the residual's traffic at N = 4), so only orders with little padding use it.
+  // Measured at N = 4 (profiles/r02_rfrag_ab.md): the epilogue's waits on the R planes were the largest stall site of the
+  // kernel (21 % of the samples); 119.7 -> 123.5 G DSU/s on the same box.  -DBDG_NO_RES_FRAG restores the staged residual.
+#ifndef BDG_NO_RES_FRAG
+  static constexpr bool RFRAG = (NP == 15);
+#else
+  static constexpr bool RFRAG = false;
+#endif
+  static constexpr int RBLK = 3 * MB * 256;  // doubles per tile of the fragment-ordered residual
 };
 
 struct StageArgs {
@@ -324,8 +337,10 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
                                              const double *__restrict__ sAff, const uint32_t *__restrict__ sLm, const double *__restrict__ sDl,
                                              double *__restrict__ sFl, const double *__restrict__ sA, const double *Areg, const int *fm, int PS,
                                              int nnodes, long long kt0, bool need_res, uint64_t *bar_res, uint32_t res_parity, double dtv,
-                                             double lamg, double tide, double tide_next, double &lam_next PROF_ARGS) {
+                                             double lamg, double tide, double tide_next, double &lam_next, double *__restrict__ gres,
+                                             bool guard PROF_ARGS) {
   using C = Cfg<NP, NFP>;
+  constexpr bool RF = C::RFRAG && !FULL;  // gres: this tile's residual block in C-fragment order; guard: store active elements only
   constexpr int NFN = C::NFN, NPB = C::NPB, NFB = C::NFB, KB = C::KB, MB = C::MB, TNP = C::TNP, NT = C::NCT, RBH = C::RBH;
   static_assert(!(C::A_REGS && C::WH > 1) && !(FULL && C::WH > 1), "the split-row-block layout is built for the big orders");
   const int FPS = FULL ? TNP : PS;  // stride of the flux planes
@@ -543,38 +558,71 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
   for (int r = 0; r < RBH; ++r)
 #pragma unroll
     for (int i = 0; i < 3; ++i) acc[i][r][0] = acc[i][r][1] = 0.0;
-#pragma unroll
-  for (int kb = 0; kb < NPB; ++kb) {
-    const int n = eo + min(4 * kb + t, NP - 1);  // padding rows of B meet zero columns of A
-    const double hu = sQ[PS + n], hv = sQ[2 * PS + n], F2 = sFl[n], G2 = sFl[FPS + n], G3 = sFl[2 * FPS + n];
-    double ba[3], bb[3];
-    ba[0] = fma(rx, hu, ry * hv); bb[0] = fma(sx, hu, sy * hv);
-    ba[1] = fma(rx, F2, ry * G2); bb[1] = fma(sx, F2, sy * G2);
-    ba[2] = fma(rx, G2, ry * G3); bb[2] = fma(sx, G2, sy * G3);
-#pragma unroll
-    for (int r = 0; r < RBH; ++r) {
-      const int rb = min(rb0 + r, MB - 1);
-      const double a1 = C::A_REGS ? (A_RELOAD ? Aloc[r * KB + kb] : Areg[r * KB + kb]) : sA[(rb * KB + kb) * 32 + lane];
-      const double a2 = C::A_REGS ? (A_RELOAD ? Aloc[r * KB + NPB + kb] : Areg[r * KB + NPB + kb]) : sA[(rb * KB + NPB + kb) * 32 + lane];
-#pragma unroll
-      for (int i = 0; i < 3; ++i) dmma884(acc[i][r][0], acc[i][r][1], a1, ba[i]);
-#pragma unroll
-      for (int i = 0; i < 3; ++i) dmma884(acc[i][r][0], acc[i][r][1], a2, bb[i]);
+  auto vol_part = [&] {
+  #pragma unroll
+    for (int kb = 0; kb < NPB; ++kb) {
+      const int n = eo + min(4 * kb + t, NP - 1);  // padding rows of B meet zero columns of A
+      const double hu = sQ[PS + n], hv = sQ[2 * PS + n], F2 = sFl[n], G2 = sFl[FPS + n], G3 = sFl[2 * FPS + n];
+      double ba[3], bb[3];
+      ba[0] = fma(rx, hu, ry * hv); bb[0] = fma(sx, hu, sy * hv);
+      ba[1] = fma(rx, F2, ry * G2); bb[1] = fma(sx, F2, sy * G2);
+      ba[2] = fma(rx, G2, ry * G3); bb[2] = fma(sx, G2, sy * G3);
+  #pragma unroll
+      for (int r = 0; r < RBH; ++r) {
+        const int rb = min(rb0 + r, MB - 1);
+        const double a1 = C::A_REGS ? (A_RELOAD ? Aloc[r * KB + kb] : Areg[r * KB + kb]) : sA[(rb * KB + kb) * 32 + lane];
+        const double a2 = C::A_REGS ? (A_RELOAD ? Aloc[r * KB + NPB + kb] : Areg[r * KB + NPB + kb]) : sA[(rb * KB + NPB + kb) * 32 + lane];
+  #pragma unroll
+        for (int i = 0; i < 3; ++i) dmma884(acc[i][r][0], acc[i][r][1], a1, ba[i]);
+  #pragma unroll
+        for (int i = 0; i < 3; ++i) dmma884(acc[i][r][0], acc[i][r][1], a2, bb[i]);
+      }
     }
-  }
-#pragma unroll
-  for (int kb = 0; kb < NFB; ++kb) {
-#pragma unroll
-    for (int r = 0; r < RBH; ++r) {
-      const int rb = min(rb0 + r, MB - 1);
-      const double a3 = C::A_REGS ? (A_RELOAD ? Aloc[r * KB + 2 * NPB + kb] : Areg[r * KB + 2 * NPB + kb]) : sA[(rb * KB + 2 * NPB + kb) * 32 + lane];
-#pragma unroll
-      for (int i = 0; i < 3; ++i) dmma884(acc[i][r][0], acc[i][r][1], a3, sfl[kb][i]);
+  };
+  auto lift_part = [&] {
+  #pragma unroll
+    for (int kb = 0; kb < NFB; ++kb) {
+  #pragma unroll
+      for (int r = 0; r < RBH; ++r) {
+        const int rb = min(rb0 + r, MB - 1);
+        const double a3 = C::A_REGS ? (A_RELOAD ? Aloc[r * KB + 2 * NPB + kb] : Areg[r * KB + 2 * NPB + kb]) : sA[(rb * KB + 2 * NPB + kb) * 32 + lane];
+  #pragma unroll
+        for (int i = 0; i < 3; ++i) dmma884(acc[i][r][0], acc[i][r][1], a3, sfl[kb][i]);
+      }
     }
+  };
+  double rres[RF ? 3 : 1][RF ? RBH : 1][2], qold[RF ? 3 : 1][RF ? RBH : 1][2];
+  const int tslot = (wfull & 3) * 32 + lane;
+  if constexpr (RF) {
+    // LIFT part first: it consumes the 3*NFB flux-jump registers; then my residual values are requested (16-byte loads, L2
+    // hits: the copy warp prefetched the block) and arrive behind the 2*NPB*MB*3 DMMAs of the volume part
+    lift_part();
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int r = 0; r < RBH; ++r) {
+        double2 x = make_double2(0.0, 0.0);  // first stage (a = 0): nothing to read, a*0 + acc below
+        if (need_res) x = __ldcg(reinterpret_cast<const double2 *>(gres) + (i * MB + rb0 + r) * 128 + tslot);
+        rres[i][r][0] = x.x; rres[i][r][1] = x.y;
+      }
+    vol_part();
+    // the old values of MY accumulator positions (nobody else writes them): requested while the last DMMAs drain, ahead of the
+    // warp barrier that orders the other lanes' B-fragment reads before my in-place update
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int r = 0; r < RBH; ++r) {
+        const int n = min(8 * (rb0 + r) + gr, NP - 1);
+        qold[i][r][0] = sQ[i * PS + e0 * NP + n];
+        qold[i][r][1] = sQ[i * PS + e1 * NP + n];
+      }
+  } else {
+    vol_part();
+    lift_part();
   }
   // res is first needed here, a whole DMMA chain after the tile's other inputs: its load (which has to wait for the
   // previous tile's store to drain from the same buffer) hides behind the contraction
-  if (bar_res) mbar_wait(bar_res, res_parity);
+  if (!RF && bar_res) mbar_wait(bar_res, res_parity);
   PROF_T(6);
   // every B-fragment read of an element precedes its in-place update below: the readers are the lanes of this warp
   // (WH = 1) or of the two warps that share the element group (WH = 2: a CTA-wide barrier of the compute warps)
@@ -609,6 +657,33 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
         if (n < NP && k >= p.k0 && k < p.k1) {
 #pragma unroll
           for (int i = 0; i < 3; ++i) p.rhs_out[(long long)i * NP * v.K + k * NP + n] = acc[i][r][cc];
+        }
+      }
+    }
+    return;
+  }
+  if constexpr (RF) {  // LSERK4 stage with the residual in registers: res = a*res + dt*rhs straight back to HBM, q += b*res in the tile
+    const bool act0 = !guard || (kt0 + e0 >= p.k0 && kt0 + e0 < p.k1), act1 = !guard || (kt0 + e1 >= p.k0 && kt0 + e1 < p.k1);
+#pragma unroll
+    for (int r = 0; r < RBH; ++r) {
+      const int n = 8 * (rb0 + r) + gr;
+      const bool real = n < NP;  // padding rows carry zeros
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        double rs[2];
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+          const int o = (cc ? e1 : e0) * NP + n;
+          rs[cc] = fma(p.a, rres[i][r][cc], acc[i][r][cc]);
+          if (real) sQ[i * PS + o] = fma(p.b, rs[cc], qold[i][r][cc]);
+          else rs[cc] = 0.0;
+        }
+        double *dst = gres + ((i * MB + rb0 + r) * 128 + tslot) * 2;
+        if (!guard) {
+          __stcg(reinterpret_cast<double2 *>(dst), make_double2(rs[0], rs[1]));
+        } else {
+          if (act0) dst[0] = rs[0];
+          if (act1) dst[1] = rs[1];
         }
       }
     }
@@ -710,6 +785,7 @@ template <int NP, int NFP, bool FULL>
 __global__ void __launch_bounds__(Cfg<NP, NFP>::NCT, (FULL || Cfg<NP, NFP>::CTAS < 3) ? (Cfg<NP, NFP>::CTAS < 2 ? 1 : 2) : 3) k_fused_edge(Sw2dView v, StageArgs p) {
   using C = Cfg<NP, NFP>;
   constexpr int NFN = C::NFN, TNP = C::TNP, kThreads = C::NCT;
+  constexpr bool RF = C::RFRAG && !FULL;  // residual in C-fragment order, read and written by compute_tile itself
   extern __shared__ __align__(128) unsigned char smem[];
   const Smem<NP, NFP, FULL> S{smem, 1, p.G};
   const int PS = S.PS();
@@ -733,7 +809,7 @@ __global__ void __launch_bounds__(Cfg<NP, NFP>::NCT, (FULL || Cfg<NP, NFP>::CTAS
     const int f = x / TNP, r = x - f * TNP;
     const bool in = r < nload * NP;
     sQ[f * PS + r] = in ? p.q_in[f * stride + base + r] : (f == 0 ? 1.0 : 0.0);
-    sR[x] = (in && need_res) ? p.r_src[f * stride + base + r] : 0.0;
+    if (!RF) sR[x] = (in && need_res) ? p.r_src[f * stride + base + r] : 0.0;
   }
   for (int x = tid; x < gc; x += kThreads) {
     const long long m = p.gflat[g0 + x];
@@ -758,7 +834,7 @@ __global__ void __launch_bounds__(Cfg<NP, NFP>::NCT, (FULL || Cfg<NP, NFP>::CTAS
 
   PROF_DECL
   compute_tile<NP, NFP, FULL>(v, p, sQ, sR, sAff, sLm, sDl, S.Fl(), S.A(), Areg, fm, PS, TNP + gc, kt0, need_res, nullptr, 0, dtv, lamg, tide,
-                              tide_next, lam_next PROF_PASS);
+                              tide_next, lam_next, RF ? p.res + tile * C::RBLK : nullptr, !all_active PROF_PASS);
   if (p.write_rhs) return;
   if (FULL) {
     // elements outside the active range / behind the mesh end must not contribute (their values are not stored)
@@ -774,7 +850,7 @@ __global__ void __launch_bounds__(Cfg<NP, NFP>::NCT, (FULL || Cfg<NP, NFP>::CTAS
     if (tid == 0) {
       for (int f = 0; f < 3; ++f) {
         bulk_s2g(p.q_out + f * stride + base, sQ + f * PS, C::txQ);
-        if (p.store_res) bulk_s2g(p.res + f * stride + base, sR + f * TNP, C::txQ);
+        if (p.store_res && !RF) bulk_s2g(p.res + f * stride + base, sR + f * TNP, C::txQ);
       }
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
@@ -786,7 +862,7 @@ __global__ void __launch_bounds__(Cfg<NP, NFP>::NCT, (FULL || Cfg<NP, NFP>::CTAS
       const long long k = kt0 + r / NP;
       if (k >= p.k0 && k < p.k1) {
         p.q_out[f * stride + base + r] = sQ[f * PS + r];
-        if (p.store_res) p.res[f * stride + base + r] = sR[x];
+        if (p.store_res && !RF) p.res[f * stride + base + r] = sR[x];
       }
     }
   }
@@ -812,6 +888,7 @@ template <int NP, int NFP, bool FULL>
 __global__ void __launch_bounds__(Cfg<NP, NFP>::NTWS, FULL ? Cfg<NP, NFP>::CTAS_FULL : Cfg<NP, NFP>::CTAS) k_fused_persistent(Sw2dView v, StageArgs p) {
   using C = Cfg<NP, NFP>;
   constexpr int TNP = C::TNP;
+  constexpr bool RF = C::RFRAG && !FULL;  // residual in C-fragment order: the compute threads move it, the copy warp only prefetches it into L2
   constexpr int GF = FULL ? C::GFIT_FULL : C::GFIT;
   extern __shared__ __align__(128) unsigned char smem[];
   const Smem<NP, NFP, FULL> S{smem, 2, GF};
@@ -884,8 +961,10 @@ __global__ void __launch_bounds__(Cfg<NP, NFP>::NTWS, FULL ? Cfg<NP, NFP>::CTAS_
       bulk_g2s(S.Aff(b), v.aff + kt0 * kAW, sizeof(double) * kTile * kAW, &bar[b]);
       if (has_rec) bulk_g2s(&ring[(j + 3) & 7], recs + pos3, 16, &bar[b]);
       if (has_ids) bulk_g2s(S.Ids(b), p.gflat + (((long long)rj1.w << 32) | (unsigned)rj1.z), idb, &bar[b]);
+      if (RF && need_res) prefetch_l2(p.res + (long long)rj.x * C::RBLK, sizeof(double) * C::RBLK);
     };
     auto res_ready = [&](int tile) {  // lane 0: R is free; fill it (a != 0) or just say so
+      if (RF) return;
       if (need_res) {
         mbar_expect_tx(&bar[2], 3 * C::txQ);
         for (int f = 0; f < 3; ++f) bulk_g2s(S.R() + f * TNP, p.r_src + f * stride + (long long)tile * kTile * NP, C::txQ, &bar[2]);
@@ -897,7 +976,7 @@ __global__ void __launch_bounds__(Cfg<NP, NFP>::NTWS, FULL ? Cfg<NP, NFP>::CTAS_
       const long long base = (long long)tile * kTile * NP;
       for (int f = 0; f < 3; ++f) {
         bulk_s2g(p.q_out + f * stride + base, S.Q(b) + f * PS, C::txQ);
-        if (p.store_res) bulk_s2g(p.res + f * stride + base, S.R() + f * TNP, C::txQ);
+        if (p.store_res && !RF) bulk_s2g(p.res + f * stride + base, S.R() + f * TNP, C::txQ);
       }
       asm volatile("cp.async.bulk.commit_group;" ::: "memory");
     };
@@ -972,7 +1051,8 @@ __global__ void __launch_bounds__(Cfg<NP, NFP>::NTWS, FULL ? Cfg<NP, NFP>::CTAS_
     mbar_wait(&bar[b], (it >> 1) & 1);
     PROF_T(1);
     compute_tile<NP, NFP, FULL>(v, p, S.Q(b), S.R(), S.Aff(b), S.Lm(b), S.Dl(b), S.Fl(), S.A(), Areg, fm, PS, TNP + rc.y, (long long)rc.x * kTile,
-                                need_res, &bar[2], it & 1, dtv, lamg, tide, tide_next, lam_next PROF_PASS);
+                                need_res, RF ? nullptr : &bar[2], it & 1, dtv, lamg, tide, tide_next, lam_next,
+                                RF ? p.res + (long long)rc.x * C::RBLK : nullptr, false PROF_PASS);
     PROF_T(7);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     compute_sync<C::NCT>();
@@ -1002,6 +1082,7 @@ struct FusedOps {
   std::vector<int> reg_tiles_full, big_tiles_full;
   int Gcap, Gmax;                         // ghost slots of the persistent / edge kernel buffers (multiples of 8)
   int Np, Nfp;
+  double *res_frag = nullptr;  // residual in C-fragment order, [ntiles][Cfg::RBLK] (orders with Cfg::RFRAG, simple physics)
   double *dl = nullptr;     // full mode: static double per face slot, [ntiles*kTile][Nfn] (k_build_delta)
   long long n_slots = 0;    // ntiles*kTile*Nfn
   long long *prof = nullptr;
@@ -1354,6 +1435,19 @@ cudaError_t fused_prepare(bdg_sw2d *s, const double *Dr, const double *Ds, const
     fused_release(s);
     return e;
   }
+  size_t rblk = 0;
+#define X(np, nfp) \
+  if (Np == np && Nfp == nfp && Cfg<np, nfp>::RFRAG) rblk = Cfg<np, nfp>::RBLK;
+  BDG_FUSED_ORDERS(X)
+#undef X
+  if (rblk && !s->v.full) {
+    if ((e = cudaMalloc((void **)&ops->res_frag, sizeof(double) * rblk * (size_t)ntiles)) != cudaSuccess ||
+        (e = cudaMemset(ops->res_frag, 0, sizeof(double) * rblk * (size_t)ntiles)) != cudaSuccess) {
+      s->fused_ops = ops;
+      fused_release(s);
+      return e;
+    }
+  }
 #ifdef BDG_PHASEPROF
   cudaMalloc((void **)&ops->prof, sizeof(long long) * 8 * 12);
   cudaMemset(ops->prof, 0, sizeof(long long) * 8 * 12);
@@ -1406,7 +1500,7 @@ void fused_release(bdg_sw2d *s) {
     cudaFree(ops->prof);
   }
 #endif
-  cudaFree(ops->sched); cudaFree(ops->slotinfo); cudaFree(ops->Afrag); cudaFree(ops->lmap); cudaFree(ops->gflat); cudaFree(ops->goff); cudaFree(ops->rec); cudaFree(ops->biglist); cudaFree(ops->rec_full); cudaFree(ops->biglist_full); cudaFree(ops->dl);
+  cudaFree(ops->sched); cudaFree(ops->slotinfo); cudaFree(ops->Afrag); cudaFree(ops->lmap); cudaFree(ops->gflat); cudaFree(ops->goff); cudaFree(ops->rec); cudaFree(ops->biglist); cudaFree(ops->rec_full); cudaFree(ops->biglist_full); cudaFree(ops->dl); cudaFree(ops->res_frag);
   delete ops;
   s->fused_ops = nullptr;
 }
@@ -1430,6 +1524,10 @@ cudaError_t launch_fused_stage(bdg_sw2d *s, const double *q_in, double *q_out, d
   args.last_stage = fs ? fs->last_stage : 0;
   // R planes: the residual (LSERK4, unless a = 0 wipes it), q^n still sitting in the destination buffer (second SSP-RK2
   // stage), nothing (first SSP-RK2 stage, RHS evaluation)
+  if (ops->res_frag && !s->v.full) {  // this order keeps the residual in C-fragment order, private to the fused kernels
+    if (args.mode != 1) return cudaErrorNotSupported;
+    args.res = res = ops->res_frag;
+  }
   args.r_src = write_rhs ? nullptr : (args.mode == 1 ? (a != 0.0 ? res : nullptr) : (args.mode == 3 ? q_out : nullptr));
   args.store_res = !write_rhs && args.mode == 1;
   if (s->v.full) {
