@@ -49,6 +49,18 @@ class bdg_halo(C.Structure):
     ]
 
 
+class bdg_curved2d(C.Structure):
+    """include/blitzdg_b200.h: cubature volume mesh + Gauss face nodes as sw2dComputeRHS_curved reads them."""
+    _fields_ = [
+        ("Ncub", C.c_int32), ("NGauss", C.c_int32),
+        ("cubV", _dp), ("cubDr", _dp), ("cubDs", _dp),
+        ("cubW", _dp), ("cub_rx", _dp), ("cub_sx", _dp), ("cub_ry", _dp), ("cub_sy", _dp),
+        ("MMChol", _dp), ("curvedEls", _ip), ("n_curved", C.c_int32), ("n_gmapW", C.c_int32),
+        ("gInterp", _dp), ("gW", _dp), ("gnx", _dp), ("gny", _dp),
+        ("gmapM", _ip), ("gmapP", _ip), ("gmapW", _ip), ("V", _dp), ("J", _dp),
+    ]
+
+
 def _d(a):
     return a.ctypes.data_as(_dp) if a is not None else _dp()
 
@@ -61,6 +73,35 @@ def make_params(g=9.81, CD=2.5e-3, f=1.0070e-4, CFL=0.25, lf_mode=0, sources=0, 
                 tide_amp=3.0, tide_period=3600 * 12.42, tide_ramp=0.15 / 3600):
     """Defaults are the literals of the reference drivers (src/sw2d/main.cpp:49-60,281-283, SW2d.hpp:16)."""
     return bdg_sw2d_params(g, CD, f, CFL, int(lf_mode), int(sources), int(filter), 0, tide_amp, tide_period, tide_ramp)
+
+
+def pack_curved(ctx, cub, gauss, curvedEls, J=None, gmapM=None, gmapP=None):
+    """(DGContext2D, cubature context, Gauss face context, curved element list) -> (bdg_curved2d, keepalive list).
+    gmapM / gmapP default to the Gauss context's own maps (sw2d_curved.py passes periodic ones)."""
+    keep = []
+
+    def dd(a):
+        b = np.ascontiguousarray(a, dtype=np.float64)
+        keep.append(b)
+        return _d(b)
+
+    def ii(a):
+        b = np.ascontiguousarray(a, dtype=np.int32).reshape(-1)
+        keep.append(b)
+        return _i(b), len(b)
+
+    s = bdg_curved2d()
+    s.Ncub, s.NGauss = int(cub.V.shape[0]), int(gauss.Interp.shape[0]) // 3
+    s.cubV, s.cubDr, s.cubDs = dd(cub.V), dd(cub.Dr), dd(cub.Ds)
+    s.cubW, s.cub_rx, s.cub_sx, s.cub_ry, s.cub_sy = dd(cub.W), dd(cub.rx), dd(cub.sx), dd(cub.ry), dd(cub.sy)
+    s.curvedEls, s.n_curved = ii(curvedEls)
+    s.MMChol = dd(cub.MMChol) if s.n_curved else _dp()
+    s.gInterp, s.gW, s.gnx, s.gny = dd(gauss.Interp), dd(gauss.W), dd(gauss.nx), dd(gauss.ny)
+    s.gmapM, _ = ii(gauss.mapM if gmapM is None else gmapM)
+    s.gmapP, _ = ii(gauss.mapP if gmapP is None else gmapP)
+    s.gmapW, s.n_gmapW = ii(gauss.BCmap.get(3, np.zeros(0, np.int32)))
+    s.V, s.J = dd(ctx.V), dd(ctx.J if J is None else J)
+    return s, keep
 
 
 def pack_context(ctx):
@@ -128,7 +169,7 @@ EXPORTS = [
     "bdg_sw2d_halo_pack_to_host", "bdg_sw2d_halo_set_ghosts", "bdg_element_order", "bdg_version",
     "bdg_sw2d_set_sponge", "bdg_sw2d_step_ssprk2", "bdg_sw2d_set_output", "bdg_sw2d_output_begin", "bdg_sw2d_output_wait",
     "bdg_sw2d_limit_positivity", "bdg_sw2d_set_tracer", "bdg_sw2d_get_tracer", "bdg_sw2d_rhs_tracer", "bdg_sw2d_stage_state", "bdg_sw2d_commit_state", "bdg_sw2d_get_state_async", "bdg_sw2d_get_state_wait",
-    "bdg_sw2d_timestep_noalloc",
+    "bdg_sw2d_timestep_noalloc", "bdg_sw2d_set_curved", "bdg_sw2d_rhs_curved",
 ]
 
 
@@ -190,6 +231,8 @@ def load():
     L.bdg_sw2d_halo_set_ghosts.argtypes = [vp, _dp]
     L.bdg_element_order.argtypes = [_ip, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _ip]
     L.bdg_version.restype = C.c_int
+    L.bdg_sw2d_set_curved.argtypes = [vp, C.POINTER(bdg_curved2d)]
+    L.bdg_sw2d_rhs_curved.argtypes = [vp, _dp, _dp, _dp, _dp, _dp]
     L.bdg_sw2d_timestep_noalloc.argtypes = [C.c_int32] * 6 + [C.c_double, C.c_double, vp, vp, vp, vp, vp, vp, vp, C.c_char_p, C.c_int32]
     _lib = L
     return L

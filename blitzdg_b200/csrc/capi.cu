@@ -136,6 +136,8 @@ int dev_upload(bdg_sw2d *s, T **p, const T *host, size_t n) {
 
 }  // namespace
 
+static void curved_free(bdg_sw2d *s);
+
 // ====================================================================================== lifetime
 extern "C" int bdg_version(void) { return 102; }
 
@@ -162,6 +164,7 @@ extern "C" void bdg_sw2d_destroy(bdg_sw2d *s) {
   if (s->d_put_counter) cudaFree(s->d_put_counter);
   if (s->d_put_dst) cudaFree(s->d_put_dst);
   fused_release(s);
+  curved_free(s);
   void *ptrs[] = {s->q[0], s->q[1], s->res, s->rhs, s->sflux, s->d_Dr, s->d_Ds, s->d_Lift, s->d_Filt, s->d_rx, s->d_sx,
                   s->d_ry, s->d_sy, s->d_nx, s->d_ny, s->d_Fscale, s->d_aff, s->d_H, s->d_Hx, s->d_Hy, s->d_vmapP,
                   s->d_fmask, s->d_bctag, s->d_facetag, s->d_scal, s->d_send_nodes, s->d_sendbuf, s->d_perm, s->d_vfrag, s->d_Dq, s->d_sponge, s->d_IM, s->d_out, s->in_raw, s->dl_raw, s->stage_buf, s->qN[0], s->qN[1], s->resN};
@@ -852,6 +855,134 @@ extern "C" int bdg_sw2d_rhs_tracer(bdg_sw2d *s, double *RHS4) {
   cudaError_t e = launch_tracer(s, s->q[s->cur], s->qN[s->curN], nullptr, s->rhs, 0, 0.0, 0.0);
   if (e != cudaSuccess) return fail(s, BDG_E_CUDA, "tracer: %s", cudaGetErrorString(e));
   if ((rc = download_transposed(s, s->rhs, RHS4, s->v.Np, s->v.K))) return rc;
+  CU(cudaStreamSynchronize(s->stream));
+  return BDG_OK;
+}
+
+// ---- over-integrated RHS on curved triangles (sw2d_curved.cu; reference swhelpers/rhs.py:6-176) -------------------------
+static void curved_free(bdg_sw2d *s) {
+  CurvedOps *o = s->curved;
+  if (!o) return;
+  const void *ptrs[] = {o->V, o->Dr, o->Ds, o->cW, o->crx, o->csx, o->cry, o->csy, o->gInterp, o->gW, o->gnx, o->gny, o->mapM, o->mapP,
+                        o->wall, o->J, o->mminv, o->chol_idx, o->chol, o->gq, o->CD, o->out};
+  for (const void *p : ptrs)
+    if (p) cudaFree(const_cast<void *>(p));
+  delete o;
+  s->curved = nullptr;
+}
+
+extern "C" int bdg_sw2d_set_curved(bdg_sw2d *s, const bdg_curved2d *c) {
+  if (!s) return BDG_E_INVALID;
+  CU(cudaSetDevice(s->device));
+  CU(cudaStreamSynchronize(s->stream));
+  curved_free(s);
+  if (!c) return BDG_OK;
+  const int Np = s->v.Np, K = s->v.K, Ncub = c->Ncub, NG3 = 3 * c->NGauss;
+  if (s->v.Nf != 3) return fail(s, BDG_E_UNSUPPORTED, "the over-integrated RHS is built for triangles (the reference has no quad cubature context)");
+  if (s->nranks > 1 || s->n_ghost > 0) return fail(s, BDG_E_UNSUPPORTED, "the over-integrated RHS runs on a single rank");
+  if (Ncub <= 0 || c->NGauss <= 0 || Ncub > 1024 || NG3 > 768) return fail(s, BDG_E_INVALID, "bad sizes Ncub=%d NGauss=%d", Ncub, c->NGauss);
+  if (!c->cubV || !c->cubDr || !c->cubDs || !c->cubW || !c->cub_rx || !c->cub_sx || !c->cub_ry || !c->cub_sy || !c->gInterp || !c->gW ||
+      !c->gnx || !c->gny || !c->gmapM || !c->gmapP || !c->V || !c->J)
+    return fail(s, BDG_E_INVALID, "NULL array in bdg_curved2d");
+  if (c->n_curved < 0 || c->n_gmapW < 0 || (c->n_curved > 0 && (!c->MMChol || !c->curvedEls)) || (c->n_gmapW > 0 && !c->gmapW))
+    return fail(s, BDG_E_INVALID, "curved element / wall lists: count without array");
+  const long long nG = (long long)NG3 * K;
+  // every per-element table goes to DEVICE element order (sw2d_order.cu): perm[k_dev] = caller's element
+  std::vector<int32_t> perm((size_t)K), inv((size_t)K);
+  if (s->d_perm) {
+    CU(cudaMemcpy(perm.data(), s->d_perm, sizeof(int32_t) * (size_t)K, cudaMemcpyDeviceToHost));
+  } else {
+    for (int k = 0; k < K; ++k) perm[k] = k;
+  }
+  for (int k = 0; k < K; ++k) inv[perm[k]] = k;
+  std::vector<int32_t> mM((size_t)nG), mP((size_t)nG), cidx((size_t)K, -1);
+  std::vector<uint8_t> wall((size_t)nG, 0);
+  for (long long kd = 0; kd < K; ++kd)
+    for (int g = 0; g < NG3; ++g) {
+      const long long ic = g + (long long)NG3 * perm[kd];
+      const long long a = c->gmapM[ic], b = c->gmapP[ic];
+      if (a < 0 || a >= nG || b < 0 || b >= nG) return fail(s, BDG_E_INVALID, "gmapM/gmapP[%lld] out of range", ic);
+      mM[g + NG3 * kd] = (int32_t)(a % NG3 + (long long)NG3 * inv[a / NG3]);
+      mP[g + NG3 * kd] = (int32_t)(b % NG3 + (long long)NG3 * inv[b / NG3]);
+    }
+  for (int i = 0; i < c->n_gmapW; ++i) {
+    const long long a = c->gmapW[i];
+    if (a < 0 || a >= nG) return fail(s, BDG_E_INVALID, "gmapW[%d]=%lld out of range", i, a);
+    wall[a % NG3 + (long long)NG3 * inv[a / NG3]] = 1;
+  }
+  std::vector<double> chol((size_t)(c->n_curved > 0 ? c->n_curved : 1) * Np * Np, 0.0), mminv((size_t)Np * Np);
+  for (int ci = 0; ci < c->n_curved; ++ci) {
+    const int kc = c->curvedEls[ci];
+    if (kc < 0 || kc >= K) return fail(s, BDG_E_INVALID, "curvedEls[%d]=%d out of range", ci, kc);
+    cidx[inv[kc]] = ci;
+    for (int i = 0; i < Np * Np; ++i) chol[(size_t)ci * Np * Np + i] = c->MMChol[(size_t)i * K + kc];  // [Np][Np][K], k fastest
+  }
+  for (int i = 0; i < Np; ++i)
+    for (int j = 0; j < Np; ++j) {
+      double a = 0.0;
+      for (int m = 0; m < Np; ++m) a += c->V[i * Np + m] * c->V[j * Np + m];  // V V^T (rhs.py:152-154)
+      mminv[i * Np + j] = a;
+    }
+  CurvedOps *o = new (std::nothrow) CurvedOps();
+  if (!o) return fail(s, BDG_E_INVALID, "out of host memory");
+  memset(o, 0, sizeof(*o));
+  s->curved = o;
+  o->Ncub = Ncub;
+  o->NG3 = NG3;
+  int rc = BDG_OK;
+  auto up = [&](const double **dst, const double *host, size_t n) {
+    double *d = nullptr;
+    if (!rc) rc = dev_upload(s, &d, host, n);
+    *dst = d;
+  };
+  auto upT = [&](const double **dst, const double *host, int R) {  // [R][K] row-major -> [K][R] in device element order
+    double *d = nullptr;
+    if (!rc) rc = dev_alloc(s, &d, (size_t)R * K);
+    *dst = d;
+    if (!rc) rc = upload_transposed(s, host, d, R, K);
+  };
+  up(&o->V, c->cubV, (size_t)Ncub * Np); up(&o->Dr, c->cubDr, (size_t)Ncub * Np); up(&o->Ds, c->cubDs, (size_t)Ncub * Np);
+  up(&o->gInterp, c->gInterp, (size_t)NG3 * Np); up(&o->mminv, mminv.data(), mminv.size()); up(&o->chol, chol.data(), chol.size());
+  upT(&o->cW, c->cubW, Ncub); upT(&o->crx, c->cub_rx, Ncub); upT(&o->csx, c->cub_sx, Ncub); upT(&o->cry, c->cub_ry, Ncub); upT(&o->csy, c->cub_sy, Ncub);
+  upT(&o->gW, c->gW, NG3); upT(&o->gnx, c->gnx, NG3); upT(&o->gny, c->gny, NG3); upT(&o->J, c->J, Np);
+  {
+    int32_t *d = nullptr;
+    if (!rc) rc = dev_upload(s, &d, mM.data(), mM.size());
+    o->mapM = d; d = nullptr;
+    if (!rc) rc = dev_upload(s, &d, mP.data(), mP.size());
+    o->mapP = d; d = nullptr;
+    if (!rc) rc = dev_upload(s, &d, cidx.data(), cidx.size());
+    o->chol_idx = d;
+    uint8_t *w = nullptr;
+    if (!rc) rc = dev_upload(s, &w, wall.data(), wall.size());
+    o->wall = w;
+  }
+  if (!rc) rc = dev_alloc(s, &o->gq, (size_t)4 * nG);
+  if (!rc) rc = dev_alloc(s, &o->CD, s->nT);
+  if (!rc) rc = dev_alloc(s, &o->out, 4 * s->nT);
+  cudaStreamSynchronize(s->stream);  // the host vectors above go out of scope
+  if (rc) curved_free(s);
+  return rc;
+}
+
+extern "C" int bdg_sw2d_rhs_curved(bdg_sw2d *s, const double *CD_nodal, double *RHS1, double *RHS2, double *RHS3, double *RHS4) {
+  if (!s) return BDG_E_INVALID;
+  if (!s->curved) return fail(s, BDG_E_INVALID, "bdg_sw2d_set_curved first");
+  CU(cudaSetDevice(s->device));
+  int rc;
+  const double *CDn = nullptr;
+  if (CD_nodal) {
+    if ((rc = upload_transposed(s, CD_nodal, s->curved->CD, s->v.Np, s->v.K))) return rc;
+    CDn = s->curved->CD;
+  }
+  cudaError_t e = launch_curved_rhs(s, s->q[s->cur], s->qN[0] ? s->qN[s->curN] : nullptr, CDn, s->curved->out);
+  if (e != cudaSuccess) return fail(s, BDG_E_CUDA, "curved rhs: %s", cudaGetErrorString(e));
+  double *dst[4] = {RHS1, RHS2, RHS3, RHS4};
+  for (int i = 0; i < 4; ++i)
+    if (dst[i]) {
+      if ((rc = download_transposed(s, s->curved->out + (size_t)i * s->nT, dst[i], s->v.Np, s->v.K))) return rc;
+      CU(cudaStreamSynchronize(s->stream));  // one staging buffer
+    }
   CU(cudaStreamSynchronize(s->stream));
   return BDG_OK;
 }

@@ -64,6 +64,25 @@ struct PeerTable {
   unsigned long long *flags[kMaxNbr];  // the peer's flag array [nranks]; I write entry [my rank]
 };
 
+// Device copies of the cubature volume mesh and the Gauss face nodes (sw2d_curved.cu; bdg_curved2d of the header), every
+// per-element table element-major in DEVICE element order.
+struct CurvedOps {
+  int Ncub, NG3;                              // cubature points per element, Gauss nodes per element (3 faces)
+  const double *V, *Dr, *Ds;                  // [Ncub][Np]
+  const double *cW, *crx, *csx, *cry, *csy;   // [K][Ncub]
+  const double *gInterp;                      // [NG3][Np]
+  const double *gW, *gnx, *gny;               // [K][NG3]
+  const int32_t *mapM, *mapP;                 // [K][NG3], device numbering g + NG3*k
+  const uint8_t *wall;                        // [K][NG3] 1 on Wall faces
+  const double *J;                            // [K][Np]
+  const double *mminv;                        // [Np][Np] V V^T
+  const int32_t *chol_idx;                    // [K]: index into chol, -1 = straight element
+  const double *chol;                         // [n_curved][Np][Np] upper Cholesky factors
+  double *gq;                                 // [4][NG3*K] scratch: fields at the Gauss nodes
+  double *CD;                                 // [K][Np] scratch: nodal drag coefficient of the current call
+  double *out;                                // [4][Np*K] scratch: RHS in device order
+};
+
 struct bdg_sw2d {
   int device;
   cudaStream_t stream, comm_stream;
@@ -127,6 +146,7 @@ struct bdg_sw2d {
   cudaEvent_t ev_in_done, ev_in_free, ev_dl_conv, ev_dl_done;
   int staged, dl_pending;
   double staged_t;
+  CurvedOps *curved;              // cubature / Gauss contexts of the over-integrated RHS (bdg_sw2d_set_curved), NULL = none
   int64_t launches;
   char err[512];
 };
@@ -138,6 +158,8 @@ cudaError_t launch_generic_face(bdg_sw2d *s, const double *q, int k0, int k1, in
 // mode 0: write RHS to out (3 planes of nT); mode 1: LSERK4 stage update of q/res in place; modes 2, 3: the two
 // SSP-RK2 stages of the src/sw2d driver, state read from q, result stored to qdst (see stepper_value)
 cudaError_t launch_generic_volume(bdg_sw2d *s, double *q, double *res, double *out, int mode, double a, double b, double *qdst);
+// over-integrated RHS on curved triangles (sw2d_curved.cu): out [4][Np*K] in device order
+cudaError_t launch_curved_rhs(bdg_sw2d *s, const double *q, const double *qN, const double *CDn, double *out);
 cudaError_t launch_dt_reduce(bdg_sw2d *s, const double *q);
 cudaError_t launch_dt_finalize(bdg_sw2d *s);
 cudaError_t launch_advance_time(bdg_sw2d *s);

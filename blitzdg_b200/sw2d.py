@@ -190,6 +190,24 @@ class SW2dSolver:
         self._ck(self.lib.bdg_sw2d_rhs_tracer(self.h, _dp(out)))
         return out
 
+    # over-integrated RHS on curved triangles (swhelpers/rhs.py:6-176; contexts: blitzdg_b200/curved.py) --------------------
+    def set_curved(self, cub_ctx, gauss_ctx, curvedEls, J=None, gmapM=None, gmapP=None):
+        """Uploads the cubature volume mesh, the Gauss face nodes and the list of curved elements (None removes them)."""
+        if cub_ctx is None:
+            self._ck(self.lib.bdg_sw2d_set_curved(self.h, None))
+            return
+        c, keep = capi.pack_curved(self.ctx, cub_ctx, gauss_ctx, curvedEls, J, gmapM, gmapP)
+        self._ck(self.lib.bdg_sw2d_set_curved(self.h, C.byref(c)))
+        del keep  # copied by the library
+
+    def computeRHS_curved(self, CD=None):
+        """sw2dComputeRHS_curved on the device state: (RHS1, RHS2, RHS3, RHS4) as [Np][K].  hN = the tracer (zero if none),
+        zx, zy = -Hx, -Hy of set_bathymetry, CD = nodal array [Np][K] or None for the parameters' scalar."""
+        R = [np.empty(self.shape) for _ in range(4)]
+        cd = self._in(np.broadcast_to(np.asarray(CD, dtype=np.float64), self.shape)) if CD is not None else None
+        self._ck(self.lib.bdg_sw2d_rhs_curved(self.h, _dp(cd), _dp(R[0]), _dp(R[1]), _dp(R[2]), _dp(R[3])))
+        return R
+
     def sync(self):
         self._ck(self.lib.bdg_sw2d_sync(self.h))
 

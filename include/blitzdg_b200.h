@@ -148,6 +148,42 @@ int bdg_sw2d_set_tracer(bdg_sw2d *s, const double *hN);
 int bdg_sw2d_get_tracer(bdg_sw2d *s, double *hN);
 int bdg_sw2d_rhs_tracer(bdg_sw2d *s, double *RHS4);
 
+/* --- over-integrated RHS on curved triangles -----------------------------------------------------
+ * sw2dComputeRHS_curved of the reference's Python drivers (swhelpers/rhs.py:6-176, called by sw2d_curved.py:240-262): the
+ * fluxes are evaluated at the cubature points of the elements and at the Gauss nodes of their faces, tested against the
+ * nodal basis, and each element's mass matrix is inverted (V V^T / J on straight elements, the stored Cholesky factor on
+ * the curved ones), then the nodal sources (Coriolis, drag, bed slope) are added.
+ * bdg_curved2d carries what that function reads from its three contexts, in the reference's native layouts:
+ *   cub_ctx   (include/CubatureContext2D.hpp, built by TriangleNodesProvisioner::buildCubatureVolumeMesh,
+ *              src/TriangleNodesProvisioner.cpp:81-202):  V, Dr, Ds [Ncub][Np]; W, rx, sx, ry, sy [Ncub][K];
+ *              MMChol [Np][Np][K] (upper factors; only the curved elements are read)
+ *   gauss_ctx (include/GaussFaceContext2D.hpp, buildGaussFaceNodes, src/TriangleNodesProvisioner.cpp:205-381):
+ *              Interp [3*NGauss][Np]; W, nx, ny [3*NGauss][K]; mapM, mapP [3*NGauss*K] (possibly made periodic by the
+ *              caller, swhelpers/maps.py); BCmap[Wall] as a list of Gauss-node ids
+ *   ctx.V [Np][Np], the nodal Jacobian J [Np][K] and the list of curved elements (the function's own arguments).
+ * set_curved copies everything (NULL removes it).  rhs_curved evaluates the function once on the device state: h, hu, hv
+ * of set_state, hN of set_tracer (zero if none), zx = -Hx, zy = -Hy of set_bathymetry (z = -H; zero if unset), g and f of
+ * the parameters, CD = CD_nodal [Np][K] (sw2d_curved.py:166-177 builds a nodal drag coefficient) or, if NULL, the
+ * parameters' scalar.  Results in host arrays [Np][K], any may be NULL.  Triangles, single rank. */
+typedef struct {
+  int32_t Ncub;                                      /* cubature points per element                          */
+  int32_t NGauss;                                    /* Gauss nodes per FACE (gauss_ctx.NGauss)              */
+  const double *cubV, *cubDr, *cubDs;                /* [Ncub][Np]                                           */
+  const double *cubW, *cub_rx, *cub_sx, *cub_ry, *cub_sy; /* [Ncub][K]                                       */
+  const double *MMChol;                              /* [Np][Np][K] or NULL when n_curved = 0                */
+  const int32_t *curvedEls;                          /* [n_curved] element ids                               */
+  int32_t n_curved;
+  int32_t n_gmapW;
+  const double *gInterp;                             /* [3*NGauss][Np]                                       */
+  const double *gW, *gnx, *gny;                      /* [3*NGauss][K]                                        */
+  const int32_t *gmapM, *gmapP;                      /* [3*NGauss*K], values g + 3*NGauss*k                  */
+  const int32_t *gmapW;                              /* [n_gmapW] gauss_ctx.BCmap[Wall]                      */
+  const double *V;                                   /* [Np][Np] ctx.V                                       */
+  const double *J;                                   /* [Np][K]                                              */
+} bdg_curved2d;
+int bdg_sw2d_set_curved(bdg_sw2d *s, const bdg_curved2d *c);
+int bdg_sw2d_rhs_curved(bdg_sw2d *s, const double *CD_nodal, double *RHS1, double *RHS2, double *RHS3, double *RHS4);
+
 /* --- output path ---------------------------------------------------------------------------
  * Every outputInterval steps the drivers derive eta = h - H, u = hu/h, v = hv/h (reference src/sw2d/main.cpp:199-210)
  * and VtkOutputter::writeFieldToFile (reference include/VtkOutputter.hpp:48-101) interpolates each to the equispaced

@@ -1,0 +1,93 @@
+"""Generate curved_reference_rhs.npz: outputs of the REFERENCE'S OWN sw2dComputeRHS_curved (swhelpers/rhs.py:6-176).
+
+Run once in the build container (reads /root/reference, which does not exist on the GPU box):
+    python tests/golden/make_curved_reference_vectors.py
+
+swhelpers/rhs.py and swhelpers/flux.py are imported as they stand.  Only compatibility shim: `np.float`, a NumPy 1.x
+alias that NumPy 2.x removed (rhs.py:101), is mapped to float64.  No arithmetic is touched.
+
+The function reads three contexts.  pyblitzdg's are replaced by this repo's host mirrors: DGContext2D (checked against the
+reference's C++ specs in tests/test_setup_golden.py) and the cubature / Gauss-face contexts of blitzdg_b200/curved.py
+(the cubature points come from a product rule, not from the reference's tables -- the function only sees the arrays).
+Inputs are stored beside the outputs, and so is everything needed to rebuild the contexts: mesh size, order, the
+deformation that curves the elements, the cubature and Gauss orders, the list of elements sent through the Cholesky path.
+"""
+import os
+import sys
+import types
+
+import numpy as np
+
+REF = "/root/reference"
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, REF)
+
+CASES = {  # name -> (nx, ny, N, cubature order, Gauss points per face)
+    "curved_N4": (6, 5, 4, 15, 10),
+    "curved_N2": (5, 4, 2, 9, 6),
+}
+
+
+def deformation(x, y):
+    """Smooth map of [-1,1]^2 onto itself that keeps the boundary: every element becomes a genuinely curved triangle."""
+    return x + 0.04 * np.sin(np.pi * y) * (1 - x * x), y + 0.03 * np.sin(np.pi * x) * (1 - y * y)
+
+
+def build_case(nx, ny, N, ncub, ngauss):
+    from blitzdg_b200.curved import build_cubature_volume_mesh, build_gauss_face_nodes, set_coordinates
+    from blitzdg_b200.synthetic import provision, structured_mesh
+
+    nodes = provision(structured_mesh("tri", nx, ny), N)
+    xd, yd = deformation(nodes.xGrid, nodes.yGrid)
+    set_coordinates(nodes, xd, yd)
+    cub = build_cubature_volume_mesh(nodes, ncub)  # also repairs the nodal metrics, as the reference does
+    gauss = build_gauss_face_nodes(nodes, ngauss)
+    ctx = nodes.get_DGContext()
+    K = ctx.K
+    curved = np.arange(0, K, 3, dtype=np.int32)  # every third element through the Cholesky path, the rest through V V^T / J
+    return nodes, ctx, cub, gauss, curved
+
+
+def state(ctx):
+    x, y = ctx.x, ctx.y
+    H = 7.5 + 0.5 * x - 0.25 * y * y
+    h = H + 0.8 * np.exp(-6 * x * x - 6 * y * y) + 0.05 * np.sin(7 * x - 3 * y)
+    hu = 0.5 * np.sin(3 * x + y) + 0.1 * x * y
+    hv = 0.3 * np.cos(2 * y - x) - 0.2 * x
+    hN = h * np.exp(-4 * ((x - 0.2) ** 2 + (y + 0.1) ** 2))
+    z = -H
+    zx = ctx.rx * (ctx.Dr @ z) + ctx.sx * (ctx.Ds @ z)
+    zy = ctx.ry * (ctx.Dr @ z) + ctx.sy * (ctx.Ds @ z)
+    CD = 2.5e-3 * (0.5 + 0.5 * np.tanh(3 * x))  # nodal drag coefficient, as sw2d_curved.py:166-177 builds one
+    return H, h, hu, hv, hN, zx, zy, CD
+
+
+def py_view(ctx):
+    return types.SimpleNamespace(numElements=ctx.K, numLocalPoints=ctx.Np, V=ctx.V)
+
+
+def main():
+    if not hasattr(np, "float"):
+        np.float = np.float64  # swhelpers/rhs.py:101 (NumPy 1.x alias)
+    from swhelpers.rhs import sw2dComputeRHS_curved
+
+    out = {}
+    g, f = 9.81 * 1e-3, 7.8825e-5  # reduced gravity and Coriolis parameter of sw2d_curved.py:20-26,158
+    for name, (nx, ny, N, ncub, ngauss) in CASES.items():
+        nodes, ctx, cub, gauss, curved = build_case(nx, ny, N, ncub, ngauss)
+        H, h, hu, hv, hN, zx, zy, CD = state(ctx)
+        R = sw2dComputeRHS_curved(h.copy(), hu.copy(), hv.copy(), hN.copy(), zx, zy, g, H, f, CD, py_view(ctx), cub, gauss,
+                                  curved.tolist(), ctx.J, gauss.mapM, gauss.mapP)
+        for i in range(4):
+            out["%s_RHS%d" % (name, i + 1)] = np.ascontiguousarray(R[i])
+        for nm, a in (("H", H), ("h", h), ("hu", hu), ("hv", hv), ("hN", hN), ("zx", zx), ("zy", zy), ("CD", CD), ("curved", curved)):
+            out["%s_%s" % (name, nm)] = a
+        out["%s_params" % name] = np.array([nx, ny, N, ncub, ngauss, g, f])
+        print(name, "K", ctx.K, "Ncub", cub.NumCubaturePoints, "max|RHS|", [float(np.abs(r).max()) for r in R])
+    np.savez_compressed(os.path.join(HERE, "curved_reference_rhs.npz"), **out)
+
+
+if __name__ == "__main__":
+    main()

@@ -45,6 +45,7 @@ def test_struct_layout_matches_c():
     assert ctypes.sizeof(capi.bdg_sw2d_params) == 4 * 8 + 4 * 4 + 3 * 8
     assert ctypes.sizeof(capi.bdg_dgcontext2d) == 24 + 13 * 8 + 9 * 8 + 9 * 4 + 4
     assert ctypes.sizeof(capi.bdg_halo) == 16 + 4 * 8 + 8
+    assert ctypes.sizeof(capi.bdg_curved2d) == 8 + 10 * 8 + 8 + 9 * 8  # 2 ints, 10 pointers, 2 ints, 9 pointers
 
 
 def test_null_handle_is_rejected_by_every_entry_point():
@@ -58,6 +59,7 @@ def test_null_handle_is_rejected_by_every_entry_point():
         "bdg_sw2d_step": (nul, 1, 0.1), "bdg_sw2d_step_ssprk2": (nul, 1, 0.1), "bdg_sw2d_sync": (nul,), "bdg_sw2d_check": (nul, dp),
         "bdg_sw2d_set_sponge": (nul, dp), "bdg_sw2d_set_output": (nul, dp, 3), "bdg_sw2d_output_begin": (nul, dp, dp, dp),
         "bdg_sw2d_output_wait": (nul,), "bdg_sw2d_limit_positivity": (nul,), "bdg_sw2d_stage_state": (nul, dp, dp, dp, 0.0),
+        "bdg_sw2d_set_curved": (nul, None), "bdg_sw2d_rhs_curved": (nul, dp, dp, dp, dp, dp),
         "bdg_sw2d_commit_state": (nul,), "bdg_sw2d_get_state_async": (nul, dp, dp, dp), "bdg_sw2d_get_state_wait": (nul,),
         "bdg_sw2d_set_variant": (nul, 1), "bdg_sw2d_comm_init": (nul, nul), "bdg_sw2d_halo_pack_to_host": (nul, dp),
         "bdg_sw2d_halo_set_ghosts": (nul, dp), "bdg_sw2d_set_tracer": (nul, dp), "bdg_sw2d_get_tracer": (nul, dp),

@@ -9,7 +9,7 @@ src=$here/blitzdg_b200/csrc
 obj=$here/build/variant_$name
 mkdir -p $obj
 nccl=$(python -c "import nvidia.nccl; print(list(nvidia.nccl.__path__)[0])")
-for f in capi sw2d_generic sw2d_fused sw2d_halo sw2d_order sw2d_volume_dmma sw2d_output sw2d_tracer sw2d_noalloc; do
+for f in capi sw2d_generic sw2d_fused sw2d_halo sw2d_order sw2d_volume_dmma sw2d_output sw2d_tracer sw2d_noalloc sw2d_curved; do
   /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -I$nccl/include \
     -Xptxas -v "$@" -c $src/$f.cu -o $obj/$f.o 2> $obj/$f.ptxas.log &
 done
