@@ -341,6 +341,11 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
                                              bool guard PROF_ARGS) {
   using C = Cfg<NP, NFP>;
   constexpr bool RF = C::RFRAG && !FULL;  // gres: this tile's residual block in C-fragment order; guard: store active elements only
+#ifdef BDG_RES_FRAG_PAD_IO
+  constexpr bool kPadIO = true;   // study: move the padding rows of the fragment-ordered residual as well
+#else
+  constexpr bool kPadIO = false;
+#endif
   constexpr int NFN = C::NFN, NPB = C::NPB, NFB = C::NFB, KB = C::KB, MB = C::MB, TNP = C::TNP, NT = C::NCT, RBH = C::RBH;
   static_assert(!(C::A_REGS && C::WH > 1) && !(FULL && C::WH > 1), "the split-row-block layout is built for the big orders");
   const int FPS = FULL ? TNP : PS;  // stride of the flux planes
@@ -602,7 +607,8 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
 #pragma unroll
       for (int r = 0; r < RBH; ++r) {
         double2 x = make_double2(0.0, 0.0);  // first stage (a = 0): nothing to read, a*0 + acc below
-        if (need_res) x = __ldcg(reinterpret_cast<const double2 *>(gres) + (i * MB + rb0 + r) * 128 + tslot);
+        // lanes of a padding row (n >= NP) neither read nor write their slots: those 64-byte pieces never move
+        if (need_res && (kPadIO || 8 * (rb0 + r) + gr < NP)) x = __ldcg(reinterpret_cast<const double2 *>(gres) + (i * MB + rb0 + r) * 128 + tslot);
         rres[i][r][0] = x.x; rres[i][r][1] = x.y;
       }
     vol_part();
@@ -679,6 +685,7 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
           else rs[cc] = 0.0;
         }
         double *dst = gres + ((i * MB + rb0 + r) * 128 + tslot) * 2;
+        if (!real && !kPadIO) continue;
         if (!guard) {
           __stcg(reinterpret_cast<double2 *>(dst), make_double2(rs[0], rs[1]));
         } else {
@@ -961,7 +968,9 @@ __global__ void __launch_bounds__(Cfg<NP, NFP>::NTWS, FULL ? Cfg<NP, NFP>::CTAS_
       bulk_g2s(S.Aff(b), v.aff + kt0 * kAW, sizeof(double) * kTile * kAW, &bar[b]);
       if (has_rec) bulk_g2s(&ring[(j + 3) & 7], recs + pos3, 16, &bar[b]);
       if (has_ids) bulk_g2s(S.Ids(b), p.gflat + (((long long)rj1.w << 32) | (unsigned)rj1.z), idb, &bar[b]);
+#ifndef BDG_NO_RES_PREFETCH
       if (RF && need_res) prefetch_l2(p.res + (long long)rj.x * C::RBLK, sizeof(double) * C::RBLK);
+#endif
     };
     auto res_ready = [&](int tile) {  // lane 0: R is free; fill it (a != 0) or just say so
       if (RF) return;
