@@ -332,7 +332,7 @@ __device__ __forceinline__ double tide_level(const Sw2dView &v, double t) {
 // faces, where that is 0, H- for the tidal hP), every trace flux re-evaluated from its star state, global LF speed from
 // scal[p.slot], bed-slope / drag / Coriolis sources in the epilogue (Hx, Hy straight from global memory: a thread's
 // C fragment covers 4 nodes), and the global LF speed of the NEW state collected for the next stage (lam_next).
-template <int NP, int NFP, bool FULL>
+template <int NP, int NFP, bool FULL, bool RFK = false>
 __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs &p, double *__restrict__ sQ, double *__restrict__ sR,
                                              const double *__restrict__ sAff, const uint32_t *__restrict__ sLm, const double *__restrict__ sDl,
                                              double *__restrict__ sFl, const double *__restrict__ sA, const double *Areg, const int *fm, int PS,
@@ -340,7 +340,8 @@ __device__ __forceinline__ void compute_tile(const Sw2dView &v, const StageArgs 
                                              double lamg, double tide, double tide_next, double &lam_next, double *__restrict__ gres,
                                              bool guard PROF_ARGS) {
   using C = Cfg<NP, NFP>;
-  constexpr bool RF = C::RFRAG && !FULL;  // gres: this tile's residual block in C-fragment order; guard: store active elements only
+  constexpr bool RF = RFK;  // gres: this tile's residual block in C-fragment order; guard: store active elements only
+  static_assert(!(RFK && FULL) && (!RFK || C::RFRAG), "the fragment-ordered residual serves the LSERK4 stages of the simple physics");
 #ifdef BDG_RES_FRAG_PAD_IO
   constexpr bool kPadIO = true;   // study: move the padding rows of the fragment-ordered residual as well
 #else
@@ -788,11 +789,11 @@ __device__ __forceinline__ void load_constants(const StageArgs &p, const Sw2dVie
 
 // ---- edge kernel: one tile per CTA, any tile (ragged mesh end, partially active range, write_rhs, tiles with
 // more ghost nodes than the persistent kernel's buffers hold) --------------------------------------------------
-template <int NP, int NFP, bool FULL>
+template <int NP, int NFP, bool FULL, bool RFK = false>
 __global__ void __launch_bounds__(Cfg<NP, NFP>::NCT, (FULL || Cfg<NP, NFP>::CTAS < 3) ? (Cfg<NP, NFP>::CTAS < 2 ? 1 : 2) : 3) k_fused_edge(Sw2dView v, StageArgs p) {
   using C = Cfg<NP, NFP>;
   constexpr int NFN = C::NFN, TNP = C::TNP, kThreads = C::NCT;
-  constexpr bool RF = C::RFRAG && !FULL;  // residual in C-fragment order, read and written by compute_tile itself
+  constexpr bool RF = RFK;  // residual in C-fragment order, read and written by compute_tile itself
   extern __shared__ __align__(128) unsigned char smem[];
   const Smem<NP, NFP, FULL> S{smem, 1, p.G};
   const int PS = S.PS();
@@ -840,7 +841,7 @@ __global__ void __launch_bounds__(Cfg<NP, NFP>::NCT, (FULL || Cfg<NP, NFP>::CTAS
   __syncthreads();
 
   PROF_DECL
-  compute_tile<NP, NFP, FULL>(v, p, sQ, sR, sAff, sLm, sDl, S.Fl(), S.A(), Areg, fm, PS, TNP + gc, kt0, need_res, nullptr, 0, dtv, lamg, tide,
+  compute_tile<NP, NFP, FULL, RFK>(v, p, sQ, sR, sAff, sLm, sDl, S.Fl(), S.A(), Areg, fm, PS, TNP + gc, kt0, need_res, nullptr, 0, dtv, lamg, tide,
                               tide_next, lam_next, RF ? p.res + tile * C::RBLK : nullptr, !all_active PROF_PASS);
   if (p.write_rhs) return;
   if (FULL) {
@@ -891,11 +892,11 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-template <int NP, int NFP, bool FULL>
+template <int NP, int NFP, bool FULL, bool RFK = false>
 __global__ void __launch_bounds__(Cfg<NP, NFP>::NTWS, FULL ? Cfg<NP, NFP>::CTAS_FULL : Cfg<NP, NFP>::CTAS) k_fused_persistent(Sw2dView v, StageArgs p) {
   using C = Cfg<NP, NFP>;
   constexpr int TNP = C::TNP;
-  constexpr bool RF = C::RFRAG && !FULL;  // residual in C-fragment order: the compute threads move it, the copy warp only prefetches it into L2
+  constexpr bool RF = RFK;  // residual in C-fragment order: the compute threads move it, the copy warp only prefetches it into L2
   constexpr int GF = FULL ? C::GFIT_FULL : C::GFIT;
   extern __shared__ __align__(128) unsigned char smem[];
   const Smem<NP, NFP, FULL> S{smem, 2, GF};
@@ -1059,7 +1060,7 @@ __global__ void __launch_bounds__(Cfg<NP, NFP>::NTWS, FULL ? Cfg<NP, NFP>::CTAS_
     PROF_T(0);
     mbar_wait(&bar[b], (it >> 1) & 1);
     PROF_T(1);
-    compute_tile<NP, NFP, FULL>(v, p, S.Q(b), S.R(), S.Aff(b), S.Lm(b), S.Dl(b), S.Fl(), S.A(), Areg, fm, PS, TNP + rc.y, (long long)rc.x * kTile,
+    compute_tile<NP, NFP, FULL, RFK>(v, p, S.Q(b), S.R(), S.Aff(b), S.Lm(b), S.Dl(b), S.Fl(), S.A(), Areg, fm, PS, TNP + rc.y, (long long)rc.x * kTile,
                                 need_res, RF ? nullptr : &bar[2], it & 1, dtv, lamg, tide, tide_next, lam_next,
                                 RF ? p.res + (long long)rc.x * C::RBLK : nullptr, false PROF_PASS);
     PROF_T(7);
@@ -1099,7 +1100,7 @@ struct FusedOps {
 
 int g_sm_count[16] = {};
 
-template <int NP, int NFP, bool FULL>
+template <int NP, int NFP, bool FULL, bool RFK = false>
 cudaError_t launch_t(bdg_sw2d *s, StageArgs a, const FusedOps *ops) {
   using C = Cfg<NP, NFP>;
   static int ctas_per_sm[16] = {};
@@ -1112,11 +1113,11 @@ cudaError_t launch_t(bdg_sw2d *s, StageArgs a, const FusedOps *ops) {
 #endif
   cudaError_t e;
   if (attr_key[dev] != ops->Gmax * 4096 + Gcap + 1) {
-    if ((e = cudaFuncSetAttribute(k_fused_edge<NP, NFP, FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_edge)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_fused_persistent<NP, NFP, FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pers)) != cudaSuccess) return e;
-    cudaFuncSetAttribute(k_fused_edge<NP, NFP, FULL>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    cudaFuncSetAttribute(k_fused_persistent<NP, NFP, FULL>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm[dev], k_fused_persistent<NP, NFP, FULL>, C::NTWS, smem_pers)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_fused_edge<NP, NFP, FULL, RFK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_edge)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_fused_persistent<NP, NFP, FULL, RFK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pers)) != cudaSuccess) return e;
+    cudaFuncSetAttribute(k_fused_edge<NP, NFP, FULL, RFK>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(k_fused_persistent<NP, NFP, FULL, RFK>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm[dev], k_fused_persistent<NP, NFP, FULL, RFK>, C::NTWS, smem_pers)) != cudaSuccess) return e;
     if ((e = cudaDeviceGetAttribute(&g_sm_count[dev], cudaDevAttrMultiProcessorCount, s->device)) != cudaSuccess) return e;
     if (ctas_per_sm[dev] < 1) return cudaErrorLaunchOutOfResources;
     attr_key[dev] = ops->Gmax * 4096 + Gcap + 1;
@@ -1137,7 +1138,7 @@ cudaError_t launch_t(bdg_sw2d *s, StageArgs a, const FusedOps *ops) {
     h.tile0 = use_list ? 0 : first;
     h.list_first = use_list ? first : 0;
     h.ntiles = count;
-    k_fused_edge<NP, NFP, FULL><<<count, C::NCT, smem_edge, s->stream>>>(s->v, h);
+    k_fused_edge<NP, NFP, FULL, RFK><<<count, C::NCT, smem_edge, s->stream>>>(s->v, h);
     s->launches++;
   };
   edge(t0, p0 - t0, 0);
@@ -1153,7 +1154,7 @@ cudaError_t launch_t(bdg_sw2d *s, StageArgs a, const FusedOps *ops) {
       // while a halo exchange is in flight leave a few SMs one CTA short, so the NCCL send/recv kernel finds room
       if (s->comm && !s->peer_ok && s->n_nbr > 0 && a.k0 == 0 && a.k1 < s->v.K) grid -= 16;
       if (grid > m.ntiles) grid = m.ntiles;
-      k_fused_persistent<NP, NFP, FULL><<<grid, C::NTWS, smem_pers, s->stream>>>(s->v, m);
+      k_fused_persistent<NP, NFP, FULL, RFK><<<grid, C::NTWS, smem_pers, s->stream>>>(s->v, m);
       s->launches++;
     }
     const int jb0 = (int)(std::lower_bound(big_tiles.begin(), big_tiles.end(), p0) - big_tiles.begin());
@@ -1165,7 +1166,7 @@ cudaError_t launch_t(bdg_sw2d *s, StageArgs a, const FusedOps *ops) {
       h.G = ops->Gmax;
       h.biglist = FULL ? ops->biglist_full : ops->biglist;
       h.use_list = 1; h.tile0 = 0; h.list_first = jb0; h.ntiles = jb1 - jb0;
-      k_fused_edge<NP, NFP, FULL><<<jb1 - jb0, C::NCT, smem_edge, s->stream>>>(s->v, h);
+      k_fused_edge<NP, NFP, FULL, RFK><<<jb1 - jb0, C::NCT, smem_edge, s->stream>>>(s->v, h);
       s->launches++;
     }
   }
@@ -1533,10 +1534,10 @@ cudaError_t launch_fused_stage(bdg_sw2d *s, const double *q_in, double *q_out, d
   args.last_stage = fs ? fs->last_stage : 0;
   // R planes: the residual (LSERK4, unless a = 0 wipes it), q^n still sitting in the destination buffer (second SSP-RK2
   // stage), nothing (first SSP-RK2 stage, RHS evaluation)
-  if (ops->res_frag && !s->v.full) {  // this order keeps the residual in C-fragment order, private to the fused kernels
-    if (args.mode != 1) return cudaErrorNotSupported;
-    args.res = res = ops->res_frag;
-  }
+  // LSERK4 stages of an order with Cfg::RFRAG run the kernels that keep the residual in C-fragment order (private to them:
+  // ops->res_frag); the SSP-RK2 stages (R planes = q^n, no residual) and every other order run the staged instantiation
+  const bool rf = ops->res_frag && !s->v.full && args.mode == 1;
+  if (rf) args.res = res = ops->res_frag;
   args.r_src = write_rhs ? nullptr : (args.mode == 1 ? (a != 0.0 ? res : nullptr) : (args.mode == 3 ? q_out : nullptr));
   args.store_res = !write_rhs && args.mode == 1;
   if (s->v.full) {
@@ -1546,8 +1547,13 @@ cudaError_t launch_fused_stage(bdg_sw2d *s, const double *q_in, double *q_out, d
 #undef X
     return cudaErrorNotSupported;
   }
-#define X(np, nfp) \
-  if (ops->Np == np && ops->Nfp == nfp) return launch_t<np, nfp, false>(s, args, ops);
+#define X(np, nfp)                                                                  \
+  if (ops->Np == np && ops->Nfp == nfp) {                                           \
+    if constexpr (Cfg<np, nfp>::RFRAG) {                                            \
+      if (rf) return launch_t<np, nfp, false, true>(s, args, ops);                  \
+    }                                                                               \
+    return launch_t<np, nfp, false, false>(s, args, ops);                           \
+  }
   BDG_FUSED_ORDERS(X)
 #undef X
   return cudaErrorNotSupported;
