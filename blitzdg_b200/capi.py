@@ -169,7 +169,7 @@ EXPORTS = [
     "bdg_sw2d_halo_pack_to_host", "bdg_sw2d_halo_set_ghosts", "bdg_element_order", "bdg_version",
     "bdg_sw2d_set_sponge", "bdg_sw2d_step_ssprk2", "bdg_sw2d_set_output", "bdg_sw2d_output_begin", "bdg_sw2d_output_wait",
     "bdg_sw2d_limit_positivity", "bdg_sw2d_set_tracer", "bdg_sw2d_get_tracer", "bdg_sw2d_rhs_tracer", "bdg_sw2d_stage_state", "bdg_sw2d_commit_state", "bdg_sw2d_get_state_async", "bdg_sw2d_get_state_wait",
-    "bdg_sw2d_timestep_noalloc", "bdg_sw2d_set_curved", "bdg_sw2d_rhs_curved",
+    "bdg_sw2d_timestep_noalloc", "bdg_sw2d_set_curved", "bdg_sw2d_rhs_curved", "bdg_sw2d_step_curved",
 ]
 
 
@@ -233,6 +233,7 @@ def load():
     L.bdg_version.restype = C.c_int
     L.bdg_sw2d_set_curved.argtypes = [vp, C.POINTER(bdg_curved2d)]
     L.bdg_sw2d_rhs_curved.argtypes = [vp, _dp, _dp, _dp, _dp, _dp]
+    L.bdg_sw2d_step_curved.argtypes = [vp, C.c_int32, C.c_double, _dp]
     L.bdg_sw2d_timestep_noalloc.argtypes = [C.c_int32] * 6 + [C.c_double, C.c_double, vp, vp, vp, vp, vp, vp, vp, C.c_char_p, C.c_int32]
     _lib = L
     return L

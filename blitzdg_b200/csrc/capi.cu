@@ -987,6 +987,37 @@ extern "C" int bdg_sw2d_rhs_curved(bdg_sw2d *s, const double *CD_nodal, double *
   return BDG_OK;
 }
 
+// The time loop of the curved driver (sw2d_curved.py:240-262), device resident: per step
+//   R = Filt * RHS_curved(q);  q1 = q + dt/2 R;  R = Filt * RHS_curved(q1);  q += dt R;  t += dt
+// for h, hu, hv and (if set) the tracer.  Filt = the context's filter when prm.filter = 1 (the driver always filters), else none.
+extern "C" int bdg_sw2d_step_curved(bdg_sw2d *s, int32_t nsteps, double dt, const double *CD_nodal) {
+  if (!s || nsteps < 0 || !(dt > 0.0)) return BDG_E_INVALID;
+  if (!s->curved) return fail(s, BDG_E_INVALID, "bdg_sw2d_set_curved first");
+  CU(cudaSetDevice(s->device));
+  int rc;
+  const double *CDn = nullptr;
+  if (CD_nodal) {
+    if ((rc = upload_transposed(s, CD_nodal, s->curved->CD, s->v.Np, s->v.K))) return rc;
+    CDn = s->curved->CD;
+  }
+  const double *Filt = (s->prm.filter && s->d_Filt) ? s->d_Filt : nullptr;
+  cudaError_t e;
+  for (int st = 0; st < nsteps; ++st) {
+    double *q = s->q[s->cur], *q1 = s->q[s->cur ^ 1];
+    double *qN = s->qN[0] ? s->qN[s->curN] : nullptr, *qN1 = s->qN[0] ? s->qN[s->curN ^ 1] : nullptr;
+    if ((e = launch_curved_rhs(s, q, qN, CDn, s->curved->out)) != cudaSuccess ||
+        (e = launch_curved_update(s, Filt, s->curved->out, 0.5 * dt, q, qN, q1, qN1)) != cudaSuccess ||
+        (e = launch_curved_rhs(s, q1, qN1, CDn, s->curved->out)) != cudaSuccess ||
+        (e = launch_curved_update(s, Filt, s->curved->out, dt, q, qN, q, qN)) != cudaSuccess)
+      return fail(s, BDG_E_CUDA, "curved step: %s", cudaGetErrorString(e));
+    s->t += dt;
+  }
+  s->lam_valid = 0;
+  s->ghost_valid = 0;
+  if (nsteps > 0) CU(cudaMemcpyAsync(s->d_scal + S_T, &s->t, sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  return BDG_OK;
+}
+
 // tracer stage beside a flow stage: reads the PRE-stage flow state q[cur] (the flow kernels write the other buffer or,
 // on the in-place LSERK4 two-launch path, run after this launch on the same stream)
 static int enqueue_tracer_stage(bdg_sw2d *s, double a, double b, int mode) {

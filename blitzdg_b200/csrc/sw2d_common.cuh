@@ -160,6 +160,8 @@ cudaError_t launch_generic_face(bdg_sw2d *s, const double *q, int k0, int k1, in
 cudaError_t launch_generic_volume(bdg_sw2d *s, double *q, double *res, double *out, int mode, double a, double b, double *qdst);
 // over-integrated RHS on curved triangles (sw2d_curved.cu): out [4][Np*K] in device order
 cudaError_t launch_curved_rhs(bdg_sw2d *s, const double *q, const double *qN, const double *CDn, double *out);
+cudaError_t launch_curved_update(bdg_sw2d *s, const double *Filt, const double *R, double c, const double *base, const double *baseN, double *dst,
+                                 double *dstN);
 cudaError_t launch_dt_reduce(bdg_sw2d *s, const double *q);
 cudaError_t launch_dt_finalize(bdg_sw2d *s);
 cudaError_t launch_advance_time(bdg_sw2d *s);

@@ -197,6 +197,34 @@ __host__ __device__ __forceinline__ void curved_element(const Sw2dView &v, const
   }
 }
 
+// One stage of the driver's midpoint scheme (sw2d_curved.py:244-262): dst = base + c * (Filt * R) at node (i, k), all four
+// fields; Filt = NULL: no filter.  R [4][nT] element-major as k_curved_rhs wrote it; q planes are `stride` apart.
+__host__ __device__ __forceinline__ void curved_update_node(long long m, int Np, long long nT, long long stride, const double *__restrict__ Filt,
+                                                            const double *__restrict__ R, double c, const double *base, const double *baseN,
+                                                            double *dst, double *dstN) {  // dst may be base (corrector stage)
+  const long long k = m / Np;
+  const int i = (int)(m - k * Np);
+#pragma unroll
+  for (int f = 0; f < 4; ++f) {
+    if (f == 3 && !dstN) break;
+    double a;
+    if (Filt) {
+      a = 0.0;
+      for (int j = 0; j < Np; ++j) a += CURVED_LDG(Filt + i * Np + j) * R[f * nT + k * Np + j];
+    } else {
+      a = R[f * nT + m];
+    }
+    if (f < 3) dst[f * stride + m] = base[f * stride + m] + c * a;
+    else dstN[m] = baseN[m] + c * a;
+  }
+}
+
+__global__ void k_curved_update(int Np, long long nT, long long stride, const double *__restrict__ Filt, const double *__restrict__ R, double c,
+                                const double *base, const double *baseN, double *dst, double *dstN) {
+  for (long long m = blockIdx.x * (long long)blockDim.x + threadIdx.x; m < nT; m += (long long)gridDim.x * blockDim.x)
+    curved_update_node(m, Np, nT, stride, Filt, R, c, base, baseN, dst, dstN);
+}
+
 __global__ void __launch_bounds__(kCurvedThreads) k_curved_rhs(Sw2dView v, CurvedOps c, const double *__restrict__ q, const double *__restrict__ qN,
                                                               const double *__restrict__ CDn, double *__restrict__ out) {
   extern __shared__ double sm[];
@@ -214,6 +242,10 @@ extern "C" void bdg_curved_host_emulation(int Np, int K, long long stride, doubl
   v.Np = Np; v.K = K; v.stride = stride; v.g = g; v.fcor = fcor; v.CD = CD; v.Hx = Hx; v.Hy = Hy;
   for (long long i = 0; i < (long long)c->NG3 * K; ++i) gauss_node(i, q, stride, qN, c->gInterp, c->gq, Np, c->NG3, K);
   for (long long k = 0; k < K; ++k) curved_element<1>(v, *c, q, qN, CDn, out, sm, 0, k);
+}
+extern "C" void bdg_curved_update_host_emulation(int Np, int K, long long stride, const double *Filt, const double *R, double c, const double *base,
+                                                 const double *baseN, double *dst, double *dstN) {
+  for (long long m = 0; m < (long long)Np * K; ++m) curved_update_node(m, Np, (long long)Np * K, stride, Filt, R, c, base, baseN, dst, dstN);
 }
 #endif
 
@@ -234,6 +266,16 @@ cudaError_t launch_curved_rhs(bdg_sw2d *s, const double *q, const double *qN, co
     if ((e = cudaFuncSetAttribute(k_curved_rhs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
   }
   k_curved_rhs<<<(unsigned)s->v.K, kCurvedThreads, smem, s->stream>>>(s->v, c, q, qN, CDn, out);
+  s->launches++;
+  return cudaGetLastError();
+}
+
+// dst = base + c * (Filt * R) for the flow planes and, if dstN, the tracer (in place allowed: dst == base)
+cudaError_t launch_curved_update(bdg_sw2d *s, const double *Filt, const double *R, double c, const double *base, const double *baseN, double *dst,
+                                 double *dstN) {
+  const long long nT = (long long)s->nT;
+  const int grid = (int)((nT + 255) / 256 < 148 * 8 ? (nT + 255) / 256 : 148 * 8);
+  k_curved_update<<<grid, 256, 0, s->stream>>>(s->v.Np, nT, s->v.stride, Filt, R, c, base, baseN, dst, dstN);
   s->launches++;
   return cudaGetLastError();
 }

@@ -208,6 +208,12 @@ class SW2dSolver:
         self._ck(self.lib.bdg_sw2d_rhs_curved(self.h, _dp(cd), _dp(R[0]), _dp(R[1]), _dp(R[2]), _dp(R[3])))
         return R
 
+    def step_curved(self, nsteps, dt, CD=None):
+        """The curved driver's midpoint predictor / corrector loop on the device (sw2d_curved.py:240-262); the RHS is filtered
+        between the stages when the solver was created with use_filter=True."""
+        cd = self._in(np.broadcast_to(np.asarray(CD, dtype=np.float64), self.shape)) if CD is not None else None
+        self._ck(self.lib.bdg_sw2d_step_curved(self.h, int(nsteps), float(dt), _dp(cd)))
+
     def sync(self):
         self._ck(self.lib.bdg_sw2d_sync(self.h))
 

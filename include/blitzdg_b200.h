@@ -183,6 +183,12 @@ typedef struct {
 } bdg_curved2d;
 int bdg_sw2d_set_curved(bdg_sw2d *s, const bdg_curved2d *c);
 int bdg_sw2d_rhs_curved(bdg_sw2d *s, const double *CD_nodal, double *RHS1, double *RHS2, double *RHS3, double *RHS4);
+/* The curved driver's time loop on the device (sw2d_curved.py:240-262), nsteps times:
+ *   R = Filt*RHS_curved(q);  q1 = q + dt/2 R;  R = Filt*RHS_curved(q1);  q += dt R;  t += dt
+ * for h, hu, hv and the tracer (if set).  Filt = the context's Filt when the parameters' `filter` is 1 (the driver always
+ * filters, sw2d_curved.py:244-247), else none.  dt > 0 (the driver's own dt formula, :236, is host arithmetic on u, v).
+ * Only enqueues, like bdg_sw2d_step. */
+int bdg_sw2d_step_curved(bdg_sw2d *s, int32_t nsteps, double dt, const double *CD_nodal);
 
 /* --- output path ---------------------------------------------------------------------------
  * Every outputInterval steps the drivers derive eta = h - H, u = hu/h, v = hv/h (reference src/sw2d/main.cpp:199-210)

@@ -24,6 +24,7 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, REF)
 
+NSTEPS = 4
 CASES = {  # name -> (nx, ny, N, cubature order, Gauss points per face)
     "curved_N4": (6, 5, 4, 15, 10),
     "curved_N2": (5, 4, 2, 9, 6),
@@ -40,6 +41,7 @@ def build_case(nx, ny, N, ncub, ngauss):
     from blitzdg_b200.synthetic import provision, structured_mesh
 
     nodes = provision(structured_mesh("tri", nx, ny), N)
+    nodes.buildFilter(0.9 * N, 4)  # sw2d_curved.py:49-53
     xd, yd = deformation(nodes.xGrid, nodes.yGrid)
     set_coordinates(nodes, xd, yd)
     cub = build_cubature_volume_mesh(nodes, ncub)  # also repairs the nodal metrics, as the reference does
@@ -85,6 +87,23 @@ def main():
         for nm, a in (("H", H), ("h", h), ("hu", hu), ("hv", hv), ("hN", hN), ("zx", zx), ("zy", zy), ("CD", CD), ("curved", curved)):
             out["%s_%s" % (name, nm)] = a
         out["%s_params" % name] = np.array([nx, ny, N, ncub, ngauss, g, f])
+        # the driver's time loop (sw2d_curved.py:240-262): filtered RHS, midpoint predictor, corrector
+        c0 = np.sqrt(g * H.mean())
+        u, v = hu / h, hv / h
+        dt = 0.5 * 0.75 / np.max(((N + 1) ** 2) * 0.5 * np.abs(ctx.Fscale.flatten("F")) * (c0 + np.hypot(u, v).flatten("F")[ctx.vmapM]))
+        q = [a.copy() for a in (h, hu, hv, hN)]
+        Filt = ctx.Filt
+        for _ in range(NSTEPS):
+            R = sw2dComputeRHS_curved(q[0], q[1], q[2], q[3], zx, zy, g, H, f, CD, py_view(ctx), cub, gauss, curved.tolist(), ctx.J, gauss.mapM,
+                                      gauss.mapP)
+            q1 = [q[i] + 0.5 * dt * np.dot(Filt, R[i]) for i in range(4)]
+            R = sw2dComputeRHS_curved(q1[0], q1[1], q1[2], q1[3], zx, zy, g, H, f, CD, py_view(ctx), cub, gauss, curved.tolist(), ctx.J,
+                                      gauss.mapM, gauss.mapP)
+            for i in range(4):
+                q[i] += dt * np.dot(Filt, R[i])
+        for i, nm in enumerate(("h", "hu", "hv", "hN")):
+            out["%s_step_%s" % (name, nm)] = q[i]
+        out["%s_step_params" % name] = np.array([NSTEPS, dt])
         print(name, "K", ctx.K, "Ncub", cub.NumCubaturePoints, "max|RHS|", [float(np.abs(r).max()) for r in R])
     np.savez_compressed(os.path.join(HERE, "curved_reference_rhs.npz"), **out)
 

@@ -39,6 +39,8 @@ def case(request, fixture):
     d = {k: fixture["%s_%s" % (name, k)] for k in ("H", "h", "hu", "hv", "hN", "zx", "zy", "CD", "curved")}
     d["g"], d["f"] = (float(x) for x in fixture[name + "_params"][5:7])
     d["R"] = [fixture["%s_RHS%d" % (name, i + 1)] for i in range(4)]
+    d["nsteps"], d["dt"] = int(fixture[name + "_step_params"][0]), float(fixture[name + "_step_params"][1])
+    d["q_end"] = [fixture["%s_step_%s" % (name, k)] for k in ("h", "hu", "hv", "hN")]
     # the contexts are rebuilt here, the inputs come from the fixture: the rebuilt state must be the stored one
     H, h, hu, hv, hN, zx, zy, CD = gen.state(ctx)
     assert np.array_equal(h, d["h"]) and np.array_equal(zx, d["zx"]) and np.array_equal(curved, d["curved"])
@@ -98,6 +100,27 @@ def test_oracle_matches_the_reference_function(case):
     # both mass-matrix paths are exercised and differ on a curved element (V V^T / J is only exact on straight ones)
     Rs = rhs_curved(d["h"], d["hu"], d["hv"], d["hN"], d["zx"], d["zy"], d["g"], d["f"], d["CD"], ctx, cub, gauss, [], ctx.J, gauss.mapM, gauss.mapP)
     assert relerr(Rs[0], d["R"][0]) > 1e-6
+
+
+def test_oracle_time_loop_matches_the_reference_driver_loop(case):
+    """sw2d_curved.py:240-262 with the reference's own RHS function (fixture) against the same loop around the oracle."""
+    from oracle.curved_numpy import rhs_curved
+
+    name, ctx, cub, gauss, d = case
+    q = [d[k].copy() for k in ("h", "hu", "hv", "hN")]
+
+    def rhs(q):
+        R = rhs_curved(q[0], q[1], q[2], q[3], d["zx"], d["zy"], d["g"], d["f"], d["CD"], ctx, cub, gauss, d["curved"], ctx.J, gauss.mapM, gauss.mapP)
+        return [ctx.Filt @ r for r in R]
+
+    for _ in range(d["nsteps"]):
+        R = rhs(q)
+        q1 = [q[i] + 0.5 * d["dt"] * R[i] for i in range(4)]
+        R = rhs(q1)
+        q = [q[i] + d["dt"] * R[i] for i in range(4)]
+    for i in range(4):
+        assert relerr(q[i], d["q_end"][i]) < 1e-12, (name, i)
+    assert relerr(d["q_end"][0], d["h"]) > 1e-3  # the state has moved
 
 
 class _CurvedOps(C.Structure):  # blitzdg_b200/csrc/sw2d_common.cuh: struct CurvedOps
@@ -162,6 +185,51 @@ def test_kernel_element_functions_on_the_host_match_reference_and_oracle(case):
     R = [out[i * Np * K:(i + 1) * Np * K].reshape(K, Np).T for i in range(4)]
     for i in range(4):
         assert relerr(R[i], d["R"][i]) < TOL, (name, i, relerr(R[i], d["R"][i]))
+
+
+def test_kernel_update_function_on_the_host(case):
+    """curved_update_node (the stage update of bdg_sw2d_step_curved): dst = base + c Filt R, in place as well."""
+    name, ctx, cub, gauss, d = case
+    lib = _emulation_lib()
+    Np, K = ctx.Np, ctx.K
+    nT, stride = Np * K, Np * K + 8
+    rng = np.random.default_rng(11)
+    R = rng.standard_normal((4, Np, K))
+    base = rng.standard_normal((3, Np, K))
+    baseN = rng.standard_normal((Np, K))
+    em = lambda a: np.ascontiguousarray(a.T).reshape(-1)  # noqa: E731  [Np][K] -> element-major
+    Rd = np.concatenate([em(R[f]) for f in range(4)])
+    qd = np.zeros(3 * stride)
+    for f in range(3):
+        qd[f * stride:f * stride + nT] = em(base[f])
+    qN = em(baseN).copy()
+    Filt = np.ascontiguousarray(ctx.Filt)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    lib.bdg_curved_update_host_emulation.argtypes = [C.c_int, C.c_int, C.c_longlong, C.c_void_p, C.c_void_p, C.c_double] + [C.c_void_p] * 4
+    lib.bdg_curved_update_host_emulation(Np, K, stride, p(Filt), p(Rd), 0.37, p(qd), p(qN), p(qd), p(qN))  # in place
+    for f in range(3):
+        got = qd[f * stride:f * stride + nT].reshape(K, Np).T
+        assert relerr(got, base[f] + 0.37 * (Filt @ R[f])) < 1e-14
+    assert relerr(qN.reshape(K, Np).T, baseN + 0.37 * (Filt @ R[3])) < 1e-14
+
+
+@pytest.mark.gpu
+def test_cuda_curved_time_loop_matches_the_reference_driver_loop(case):
+    from blitzdg_b200.sw2d import SW2dSolver, physParams
+
+    name, ctx, cub, gauss, d = case
+    sol = SW2dSolver(ctx, phys=physParams(g=d["g"], CD=0.0, f=d["f"]), use_filter=True)
+    sol.set_bathymetry(d["H"], -d["zx"], -d["zy"])
+    sol.set_state(d["h"], d["hu"], d["hv"])
+    sol.set_tracer(d["hN"])
+    sol.set_curved(cub, gauss, d["curved"])
+    sol.step_curved(d["nsteps"], d["dt"], CD=d["CD"])
+    h, hu, hv, t = sol.get_state()
+    hN = sol.get_tracer()
+    for i, a in enumerate((h, hu, hv, hN)):
+        assert relerr(a, d["q_end"][i]) < 1e-10, (name, i, relerr(a, d["q_end"][i]))
+    assert abs(t - d["nsteps"] * d["dt"]) < 1e-15
+    sol.close()
 
 
 @pytest.mark.gpu
