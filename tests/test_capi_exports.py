@@ -59,7 +59,7 @@ def test_null_handle_is_rejected_by_every_entry_point():
         "bdg_sw2d_step": (nul, 1, 0.1), "bdg_sw2d_step_ssprk2": (nul, 1, 0.1), "bdg_sw2d_sync": (nul,), "bdg_sw2d_check": (nul, dp),
         "bdg_sw2d_set_sponge": (nul, dp), "bdg_sw2d_set_output": (nul, dp, 3), "bdg_sw2d_output_begin": (nul, dp, dp, dp),
         "bdg_sw2d_output_wait": (nul,), "bdg_sw2d_limit_positivity": (nul,), "bdg_sw2d_stage_state": (nul, dp, dp, dp, 0.0),
-        "bdg_sw2d_set_curved": (nul, None), "bdg_sw2d_rhs_curved": (nul, dp, dp, dp, dp, dp),
+        "bdg_sw2d_set_curved": (nul, None), "bdg_sw2d_rhs_curved": (nul, dp, dp, dp, dp, dp), "bdg_sw2d_step_curved": (nul, 1, 0.1, dp),
         "bdg_sw2d_commit_state": (nul,), "bdg_sw2d_get_state_async": (nul, dp, dp, dp), "bdg_sw2d_get_state_wait": (nul,),
         "bdg_sw2d_set_variant": (nul, 1), "bdg_sw2d_comm_init": (nul, nul), "bdg_sw2d_halo_pack_to_host": (nul, dp),
         "bdg_sw2d_halo_set_ghosts": (nul, dp), "bdg_sw2d_set_tracer": (nul, dp), "bdg_sw2d_get_tracer": (nul, dp),

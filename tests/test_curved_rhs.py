@@ -213,6 +213,57 @@ def test_kernel_update_function_on_the_host(case):
     assert relerr(qN.reshape(K, Np).T, baseN + 0.37 * (Filt @ R[3])) < 1e-14
 
 
+def _periodic_in_x(gauss):
+    """What sw2d_curved.py:141-142 does to the Gauss maps with makeMapsPeriodic (swhelpers/maps.py): the wall Gauss nodes on
+    x = -1 and x = +1 are paired by their y coordinate and become each other's '+' side; they leave the wall list."""
+    import dataclasses
+
+    gx, gy = gauss.x.flatten("F"), gauss.y.flatten("F")
+    wall = np.asarray(gauss.BCmap[3], dtype=np.int64)
+    left, right = wall[np.abs(gx[wall] + 1) < 1e-12], wall[np.abs(gx[wall] - 1) < 1e-12]
+    assert len(left) == len(right) > 0
+    mapP = gauss.mapP.copy()
+    for i in left:
+        j = right[np.argmin(np.abs(gy[right] - gy[i]))]
+        assert abs(gy[j] - gy[i]) < 1e-12
+        mapP[i], mapP[j] = j, i
+    keep = np.setdiff1d(wall, np.concatenate([left, right])).astype(np.int32)
+    return dataclasses.replace(gauss, mapP=mapP, BCmap={3: keep})
+
+
+def test_oracle_follows_periodic_gauss_maps(case):
+    from oracle.curved_numpy import rhs_curved
+
+    name, ctx, cub, gauss, d = case
+    gp = _periodic_in_x(gauss)
+    args = (d["h"], d["hu"], d["hv"], d["hN"], d["zx"], d["zy"], d["g"], d["f"], d["CD"], ctx, cub)
+    Rw = rhs_curved(*args, gauss, d["curved"], ctx.J, gauss.mapM, gauss.mapP)
+    Rp = rhs_curved(*args, gp, d["curved"], ctx.J, gp.mapM, gp.mapP)
+    touched = np.unique(np.concatenate([np.nonzero(gp.mapP != gauss.mapP)[0]]) // gauss.Interp.shape[0])
+    other = np.setdiff1d(np.arange(ctx.K), touched)
+    assert np.abs(Rp[0][:, touched] - Rw[0][:, touched]).max() > 1e-6 and np.array_equal(Rp[0][:, other], Rw[0][:, other])
+
+
+@pytest.mark.gpu
+def test_cuda_curved_rhs_with_periodic_gauss_maps(case):
+    """Caller-supplied gmapM / gmapP (periodic in x) and the reduced wall list go through the element renumbering of set_curved."""
+    from blitzdg_b200.sw2d import SW2dSolver, physParams
+    from oracle.curved_numpy import rhs_curved
+
+    name, ctx, cub, gauss, d = case
+    gp = _periodic_in_x(gauss)
+    sol = SW2dSolver(ctx, phys=physParams(g=d["g"], CD=0.0, f=d["f"]))
+    sol.set_bathymetry(d["H"], -d["zx"], -d["zy"])
+    sol.set_state(d["h"], d["hu"], d["hv"])
+    sol.set_tracer(d["hN"])
+    sol.set_curved(cub, gp, d["curved"], gmapM=gp.mapM, gmapP=gp.mapP)
+    R = sol.computeRHS_curved(CD=d["CD"])
+    Ro = rhs_curved(d["h"], d["hu"], d["hv"], d["hN"], d["zx"], d["zy"], d["g"], d["f"], d["CD"], ctx, cub, gp, d["curved"], ctx.J, gp.mapM, gp.mapP)
+    for i in range(4):
+        assert relerr(R[i], Ro[i]) < TOL, (name, i, relerr(R[i], Ro[i]))
+    sol.close()
+
+
 @pytest.mark.gpu
 def test_cuda_curved_time_loop_matches_the_reference_driver_loop(case):
     from blitzdg_b200.sw2d import SW2dSolver, physParams
