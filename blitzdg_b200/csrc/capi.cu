@@ -887,6 +887,7 @@ extern "C" int bdg_sw2d_set_curved(bdg_sw2d *s, const bdg_curved2d *c) {
   if (c->n_curved < 0 || c->n_gmapW < 0 || (c->n_curved > 0 && (!c->MMChol || !c->curvedEls)) || (c->n_gmapW > 0 && !c->gmapW))
     return fail(s, BDG_E_INVALID, "curved element / wall lists: count without array");
   const long long nG = (long long)NG3 * K;
+  if (nG >= (1LL << 31)) return fail(s, BDG_E_UNSUPPORTED, "3*NGauss*K exceeds int32 (the reference's index_type of gmapM / gmapP)");
   // every per-element table goes to DEVICE element order (sw2d_order.cu): perm[k_dev] = caller's element
   std::vector<int32_t> perm((size_t)K), inv((size_t)K);
   if (s->d_perm) {
