@@ -118,6 +118,15 @@ struct SqrtExpr : ETBase<SqrtExpr<E>> {
   Shape shape() const { return e.shape(); }
 };
 template <typename E>
+struct PowExpr : ETBase<PowExpr<E>> {  // pow(expr, scalar), element by element (std::pow on doubles)
+  typedef double value_type;
+  E e;
+  double p;
+  PowExpr(const E &x, double q) : e(x), p(q) {}
+  double eval(const int *idx) const { return std::pow((double)e.eval(idx), p); }
+  Shape shape() const { return e.shape(); }
+};
+template <typename E>
 struct AbsExpr : ETBase<AbsExpr<E>> {
   typedef typename E::value_type value_type;
   E e;
@@ -202,6 +211,8 @@ template <typename E>
 typename std::enable_if<is_et<E>::value, SqrtExpr<E>>::type sqrt(const E &e) { return SqrtExpr<E>(e); }
 template <typename E>
 typename std::enable_if<is_et<E>::value, AbsExpr<E>>::type abs(const E &e) { return AbsExpr<E>(e); }
+template <typename E, typename S>
+typename std::enable_if<is_et<E>::value && std::is_arithmetic<S>::value, PowExpr<E>>::type pow(const E &e, S p) { return PowExpr<E>(e, (double)p); }
 template <typename E, int D>
 typename std::enable_if<is_et<E>::value, SumExpr<E, D>>::type sum(const E &e, IndexPlaceholder<D>) { return SumExpr<E, D>(e); }
 
@@ -240,9 +251,28 @@ typename std::enable_if<is_et<E>::value, typename E::value_type>::type sum(const
   return acc;
 }
 
+// `A = v0, v1, v2;` (blitz list initialisation): scalar assignment hands back this proxy; a following comma turns the fill into
+// an element list in storage order, otherwise the destructor fills the whole array with the scalar (blitz's
+// ListInitializationSwitch).
+template <typename T, int N>
+struct ListInit {
+  Array<T, N> *a;
+  T first;
+  int pos;
+  bool list;
+  ListInit(Array<T, N> *arr, T f) : a(arr), first(f), pos(1), list(false) {}
+  ListInit(ListInit &&o) : a(o.a), first(o.first), pos(o.pos), list(o.list) { o.a = nullptr; }
+  ListInit(const ListInit &) = delete;
+  ~ListInit();
+  template <typename S>
+  typename std::enable_if<std::is_arithmetic<S>::value, ListInit &>::type operator,(S x);
+  operator Array<T, N> &();
+};
+
 template <typename T, int N>
 class Array : public ETBase<Array<T, N>> {
   static_assert(N >= 1 && N <= 3, "blitz shim: rank 1..3");
+  template <typename, int> friend class Array;
   std::shared_ptr<std::vector<T>> store_;
   T *data_;
   int ext_[3];
@@ -301,6 +331,12 @@ class Array : public ETBase<Array<T, N>> {
   int cols() const { return ext_[1]; }
   int depth() const { return ext_[2]; }
   int length(int d) const { return ext_[d]; }
+  struct Extents {  // x.length() of blitz returns a TinyVector; the reference reads (x.length())(0)
+    int e[3];
+    int operator()(int d) const { return e[d]; }
+    int operator[](int d) const { return e[d]; }
+  };
+  Extents length() const { return Extents{{ext_[0], ext_[1], ext_[2]}}; }
   int extent(int d) const { return ext_[d]; }
   int size() const { return numElements(); }
   int numElements() const { return N == 1 ? ext_[0] : (N == 2 ? ext_[0] * ext_[1] : ext_[0] * ext_[1] * ext_[2]); }
@@ -325,6 +361,22 @@ class Array : public ETBase<Array<T, N>> {
   const T &operator[](int i) const { return data_[i]; }
   template <int P0, int P1>
   IndexedArray<T, N, P0, P1> operator()(IndexPlaceholder<P0>, IndexPlaceholder<P1>) const { return IndexedArray<T, N, P0, P1>(*this); }
+  // A(i, Range::all()) / A(Range::all(), j): rank-1 VIEWS of a row / column of a matrix (aliases, like blitz)
+  Array<T, 1> operator()(int i, Range) const { return slice1(data_ + (size_t)i * stride_[0], ext_[1], stride_[1]); }
+  Array<T, 1> operator()(Range, int j) const { return slice1(data_ + (size_t)j * stride_[1], ext_[0], stride_[0]); }
+
+ private:
+  Array<T, 1> slice1(T *first, int n, int stride) const {
+    static_assert(N == 2, "blitz shim: slices of matrices only");
+    Array<T, 1> v;
+    v.store_ = store_;
+    v.data_ = first;
+    v.ext_[0] = n; v.ext_[1] = 1; v.ext_[2] = 1;
+    v.stride_[0] = stride; v.stride_[1] = v.stride_[2] = 0;
+    return v;
+  }
+
+ public:
 
   // as an expression operand: rank-1 arrays live on tensor index 0, rank-2 on (0, 1)
   T eval(const int *idx) const { return N == 1 ? (*this)(idx[0]) : (N == 2 ? (*this)(idx[0], idx[1]) : (*this)(idx[0], idx[1], idx[2])); }
@@ -367,13 +419,41 @@ class Array : public ETBase<Array<T, N>> {
     assign(Constant<T>((T)v), [](T &a, T b) { a OP b; });                                                   \
     return *this;                                                                                           \
   }
-  BDG_ASSIGN(=)
+  template <typename E>
+  typename std::enable_if<is_et<E>::value, Array &>::type operator=(const E &e) {
+    assign(e, [](T &a, T b) { a = b; });
+    return *this;
+  }
+  template <typename S>
+  typename std::enable_if<std::is_arithmetic<S>::value, ListInit<T, N>>::type operator=(S v) { return ListInit<T, N>(this, (T)v); }
+  void fill(T v) { assign(Constant<T>(v), [](T &a, T b) { a = b; }); }
   BDG_ASSIGN(+=)
   BDG_ASSIGN(-=)
   BDG_ASSIGN(*=)
   BDG_ASSIGN(/=)
 #undef BDG_ASSIGN
 };
+
+template <typename T, int N>
+ListInit<T, N>::~ListInit() {
+  if (a && !list) a->fill(first);
+}
+template <typename T, int N>
+template <typename S>
+typename std::enable_if<std::is_arithmetic<S>::value, ListInit<T, N> &>::type ListInit<T, N>::operator,(S x) {
+  if (!list) {
+    (*a)[0] = first;
+    list = true;
+  }
+  (*a)[pos++] = (T)x;
+  return *this;
+}
+template <typename T, int N>
+ListInit<T, N>::operator Array<T, N> &() {
+  if (!list) a->fill(first);
+  list = true;
+  return *a;
+}
 
 // A(ii,kk): rank-2 array whose dimensions ride on tensor indices P0, P1
 template <typename T, int N, int P0, int P1>

@@ -1,0 +1,90 @@
+"""Output path against the REFERENCE'S OWN code, compiled verbatim from /root/reference by
+oracle/make_ref_output.py (oracle/_ref/libsplit_ref.so): TriangleNodesProvisioner::splitElements, computeInterpMatrix,
+computeVandermondeMatrix (+ evaluateSimplexPolynomial, rsToab) and JacobiBuilders::computeJacobiPolynomial.
+
+Held to it: the host mirror (blitzdg_b200/triangle_nodes.py: the interpolation matrix the device output kernel is given, and
+splitElements) and the loop-level oracle of the output path (oracle/output_numpy.py).  The library is prebuilt where the
+reference tree exists and travels with the snapshot; absent library and absent reference => skip.
+"""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB = os.path.join(ROOT, "oracle", "_ref", "libsplit_ref.so")
+_dp = C.POINTER(C.c_double)
+
+
+def _p(a):
+    return a.ctypes.data_as(_dp)
+
+
+@pytest.fixture(scope="module")
+def ref():
+    if not os.path.exists(LIB):
+        if not os.path.exists("/root/reference/src/TriangleNodesProvisioner.cpp"):
+            pytest.skip("compiled reference not built and reference tree not present")
+        subprocess.run([sys.executable, os.path.join(ROOT, "oracle", "make_ref_output.py")], check=True, capture_output=True)
+    return C.CDLL(LIB)
+
+
+@pytest.fixture(scope="module", params=[1, 2, 4, 7])
+def nodes(request, coarse_box_mesh):
+    from blitzdg_b200 import TriangleNodesProvisioner
+
+    return TriangleNodesProvisioner(request.param, coarse_box_mesh)
+
+
+def test_vandermonde_and_interpolation_matrix_match_the_compiled_reference(ref, nodes):
+    N, Np = nodes.NOrder, nodes.NumLocalPoints
+    rng = np.random.default_rng(N)
+    # points inside the reference triangle, plus its three corners (s = 1 takes the a = -1 branch of rsToab, :398-401)
+    a, b = rng.random(12), rng.random(12)
+    r = np.concatenate([2 * a * (1 - b) - 1 + 0 * b, [-1.0, 1.0, -1.0]])
+    s = np.concatenate([2 * b - 1, [-1.0, -1.0, 1.0]])
+    r = np.minimum(r, -s)
+    n = len(r)
+    V = np.zeros((n, Np))
+    ref.ref_vandermonde(N, n, _p(r), _p(s), _p(V))
+    mine = nodes.computeVandermondeMatrix(N, r, s)
+    assert np.abs(mine - V).max() <= 4e-15 * max(1.0, np.abs(V).max())
+    IM = np.zeros((n, Np))
+    Vinv = np.ascontiguousarray(nodes.Vinv)
+    ref.ref_interp_matrix(N, n, _p(Vinv), _p(r), _p(s), _p(IM))
+    assert np.abs(nodes.computeInterpMatrix(r, s) - IM).max() <= 1e-13 * max(1.0, np.abs(IM).max())
+    # the nodal Vandermonde matrix itself: V(r_nodes) V^-1 = I through the reference's code
+    I = np.zeros((Np, Np))
+    rn, sn = np.ascontiguousarray(nodes.rGrid), np.ascontiguousarray(nodes.sGrid)
+    ref.ref_interp_matrix(N, Np, _p(Vinv), _p(rn), _p(sn), _p(I))
+    assert np.abs(I - np.eye(Np)).max() < 1e-11
+
+
+def test_split_elements_matches_the_compiled_reference(ref, nodes):
+    from oracle.output_numpy import split_elements
+
+    N, Np, K = nodes.NOrder, nodes.NumLocalPoints, nodes.NumElements
+    if N == 1:
+        pytest.skip("N = 1 is written as is (VtkOutputter.hpp:55)")
+    x, y = np.ascontiguousarray(nodes.xGrid), np.ascontiguousarray(nodes.yGrid)
+    f = np.ascontiguousarray(np.sin(3 * x) * np.cos(2 * y) + 0.3 * x * y)
+    tot = N * N * K
+    want = [np.zeros((3, tot)) for _ in range(3)]
+    Vinv = np.ascontiguousarray(nodes.Vinv)
+    n = ref.ref_split_elements(N, K, _p(Vinv), _p(x), _p(y), _p(f), _p(want[0]), _p(want[1]), _p(want[2]))
+    assert n == tot
+    got = nodes.splitElements(x, y, f)
+    rout, sout, _ = nodes.splitTable()
+    orc = split_elements(Np, N, False, nodes.computeInterpMatrix(rout, sout), x, y, f)
+    for g, o, w in zip(got, orc, want):
+        assert g.shape == w.shape == o.shape
+        scale = max(1.0, np.abs(w).max())
+        assert np.abs(o - w).max() <= 1e-13 * scale   # the loop-level oracle of the output path
+        assert np.abs(g - w).max() <= 1e-13 * scale   # the host mirror (BLAS summation order)
+    # corner order of the sub-elements is the reference's: counter-clockwise linear triangles with positive area
+    xa, ya = want[0], want[1]
+    area = (xa[1] - xa[0]) * (ya[2] - ya[0]) - (xa[2] - xa[0]) * (ya[1] - ya[0])
+    assert (area > 0).all()
