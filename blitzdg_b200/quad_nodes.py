@@ -130,6 +130,20 @@ class QuadNodesProvisioner(TriangleNodesProvisioner):
         self.Filter = np.ascontiguousarray(self.V @ (np.diag(d) @ self.Vinv))
         return self.Filter
 
+    def computeInterpMatrix(self, rout, sout):
+        """QuadNodesProvisioner::computeInterpMatrix AS THE REFERENCE EXECUTES IT (src/QuadNodesProvisioner.cpp:707-719): its
+        computeVandermondeMatrix (:76-92) ends with `Inverter.computeInverse(V, *Vinv)`, so the call that evaluates the basis at
+        the output points overwrites Vinv with the inverse of THAT matrix, and IM = Vout * Vinv = Vout * Vout^-1 -- the identity
+        up to rounding (found by compiling the reference's own functions, tests/test_reference_compiled_output.py).  The quad
+        output path therefore writes the NODAL values at the nodal (Gauss-Lobatto) positions, in nodal order, connected by the
+        lattice table below; nothing is resampled to equispaced points.  Reproduced as executed, except that this mirror leaves
+        its own Vinv intact (the reference's stays clobbered for whatever runs next).  Only defined for as many output points
+        as nodes, which is how splitElements calls it."""
+        Vout = self.computeVandermondeMatrix(self.NOrder, np.asarray(rout, float), np.asarray(sout, float))
+        if Vout.shape[0] != Vout.shape[1]:
+            raise ValueError("the reference inverts the output Vandermonde matrix: it needs NumLocalPoints output points")
+        return np.ascontiguousarray(Vout @ lapack.inverse(Vout))
+
     def splitTable(self):
         """Equispaced (N+1)x(N+1) output lattice, one linear quad (v1,v2,v3,v4) per cell (src/QuadNodesProvisioner.cpp:728-770)."""
         N = self.NumFacePoints - 1

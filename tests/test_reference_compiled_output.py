@@ -88,3 +88,41 @@ def test_split_elements_matches_the_compiled_reference(ref, nodes):
     xa, ya = want[0], want[1]
     area = (xa[1] - xa[0]) * (ya[2] - ya[0]) - (xa[2] - xa[0]) * (ya[1] - ya[0])
     assert (area > 0).all()
+
+
+@pytest.mark.parametrize("N", [1, 2, 4, 6])
+def test_quad_output_path_follows_the_reference_as_executed(ref, coarse_quads_mesh, N):
+    """QuadNodesProvisioner::computeVandermondeMatrix ends with Inverter.computeInverse(V, *Vinv) (src/QuadNodesProvisioner.cpp:90-91),
+    so computeInterpMatrix (:707-719) overwrites Vinv with the inverse of the OUTPUT Vandermonde matrix and returns
+    Vout * Vout^-1: the identity.  The reference's quad splitElements therefore emits the nodal values at the nodal positions,
+    in nodal order, connected by the lattice table.  The host mirror reproduces that (blitzdg_b200/quad_nodes.py)."""
+    from blitzdg_b200 import QuadNodesProvisioner
+    from oracle.output_numpy import split_elements
+
+    P = QuadNodesProvisioner(N, coarse_quads_mesh)
+    Np, K = P.NumLocalPoints, P.NumElements
+    rout, sout, _ = P.splitTable()
+    rout, sout = np.ascontiguousarray(rout), np.ascontiguousarray(sout)
+    Vinv = np.ascontiguousarray(P.Vinv)
+    IM, after = np.zeros((Np, Np)), np.zeros((Np, Np))
+    ref.ref_quad_interp_matrix(N, _p(Vinv), _p(rout), _p(sout), _p(IM), _p(after))
+    assert np.abs(IM - np.eye(Np)).max() < 1e-12                      # what the reference's function returns
+    assert np.abs(after - Vinv).max() > 1e-2                          # ... and it has clobbered Vinv on the way
+    assert np.abs(P.computeInterpMatrix(rout, sout) - IM).max() < 1e-12
+    assert np.array_equal(np.asarray(P.Vinv), Vinv)                   # the mirror leaves its own intact
+    if N == 1:
+        return
+    x, y = np.ascontiguousarray(P.xGrid), np.ascontiguousarray(P.yGrid)
+    f = np.ascontiguousarray(np.sin(3 * x) * np.cos(2 * y) + 0.3 * x * y)
+    tot = N * N * K
+    want = [np.zeros((4, tot)) for _ in range(3)]
+    assert ref.ref_quad_split_elements(N, K, _p(Vinv), _p(x), _p(y), _p(f), _p(want[0]), _p(want[1]), _p(want[2])) == tot
+    got = P.splitElements(x, y, f)
+    orc = split_elements(Np, N, True, P.computeInterpMatrix(rout, sout), x, y, f)
+    for g, o, w in zip(got, orc, want):
+        assert g.shape == w.shape == o.shape
+        assert np.abs(g - w).max() <= 1e-13 * max(1.0, np.abs(w).max())
+        assert np.abs(o - w).max() <= 1e-13 * max(1.0, np.abs(w).max())
+    # nodal values, not resampled ones: every emitted corner value is one of the element's nodal values
+    k = 0
+    assert np.abs(np.sort(np.unique(np.round(want[2][:, :N * N], 12))) - np.sort(np.unique(np.round(f[:, k], 12)))).max() < 1e-11
