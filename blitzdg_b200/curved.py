@@ -12,6 +12,8 @@ One deviation, stated here and in DESIGN.md: the reference takes its cubature po
 mirror uses the Gauss-Legendre x Gauss-Jacobi(1,0) product rule on the collapsed square, exact to the same total
 degree with more points (64 instead of 54 at order 15).  sw2dComputeRHS_curved only sees the resulting arrays, so the
 device kernel and the oracle are independent of which rule produced them.
+A caller who holds the reference's points passes them as build_cubature_volume_mesh(..., rule=(r, s, w)); with them every
+array built here agrees with the reference's compiled builders (tests/test_reference_compiled_curved.py).
 """
 from dataclasses import dataclass, field
 from typing import Dict
@@ -83,9 +85,11 @@ def set_coordinates(nodes, x, y):
     nodes.yGrid = np.ascontiguousarray(y, dtype=np.float64)
 
 
-def build_cubature_volume_mesh(nodes, NCubature):
+def build_cubature_volume_mesh(nodes, NCubature, rule=None):
+    """rule: (r, s, w) of the cubature points to use instead of this mirror's product rule -- e.g. the reference's own table
+    of that order, which a caller holding pyblitzdg (or the tests, through the compiled TriangleCubatureRules.hpp) can supply."""
     Np, K = nodes.NumLocalPoints, nodes.NumElements
-    rc, sc, wc = triangle_cubature(NCubature)
+    rc, sc, wc = triangle_cubature(NCubature) if rule is None else (np.asarray(a, dtype=np.float64) for a in rule)
     Ncub = len(rc)
     Vcub = nodes.computeInterpMatrix(rc, sc)
     V2Dr, V2Ds = nodes.computeGradVandermondeMatrix(nodes.NOrder, rc, sc)

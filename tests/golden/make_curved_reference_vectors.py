@@ -28,7 +28,12 @@ NSTEPS = 4
 CASES = {  # name -> (nx, ny, N, cubature order, Gauss points per face)
     "curved_N4": (6, 5, 4, 15, 10),
     "curved_N2": (5, 4, 2, 9, 6),
+    "curved_N4_reftable": (6, 5, 4, 15, 10),
 }
+# cases whose cubature points are the REFERENCE'S OWN tabulated rule of that order (include/TriangleCubatureRules.hpp; 54 points
+# at order 15), read at generation time through the compiled header (oracle/make_ref_curved.py -> ref_cubature_rule) and stored
+# beside the vectors as <case>_rule = [r; s; w], so the tests rebuild the same contexts without the reference tree
+TABLE_RULE_CASES = ("curved_N4_reftable",)
 
 
 def deformation(x, y):
@@ -36,7 +41,21 @@ def deformation(x, y):
     return x + 0.04 * np.sin(np.pi * y) * (1 - x * x), y + 0.03 * np.sin(np.pi * x) * (1 - y * y)
 
 
-def build_case(nx, ny, N, ncub, ngauss):
+def reference_table_rule(order):
+    """(r, s, w) of the reference's tabulated rule, from oracle/_ref/libcurved_ref.so (generation time only)."""
+    import ctypes as C
+    import subprocess
+
+    lib = os.path.join(ROOT, "oracle", "_ref", "libcurved_ref.so")
+    if not os.path.exists(lib):
+        subprocess.check_call([sys.executable, os.path.join(ROOT, "oracle", "make_ref_curved.py")])
+    ref = C.CDLL(lib)
+    buf = [np.zeros(256) for _ in range(3)]
+    n = ref.ref_cubature_rule(int(order), *[b.ctypes.data_as(C.POINTER(C.c_double)) for b in buf])
+    return np.stack([b[:n] for b in buf])
+
+
+def build_case(nx, ny, N, ncub, ngauss, rule=None):
     from blitzdg_b200.curved import build_cubature_volume_mesh, build_gauss_face_nodes, set_coordinates
     from blitzdg_b200.synthetic import provision, structured_mesh
 
@@ -44,7 +63,7 @@ def build_case(nx, ny, N, ncub, ngauss):
     nodes.buildFilter(0.9 * N, 4)  # sw2d_curved.py:49-53
     xd, yd = deformation(nodes.xGrid, nodes.yGrid)
     set_coordinates(nodes, xd, yd)
-    cub = build_cubature_volume_mesh(nodes, ncub)  # also repairs the nodal metrics, as the reference does
+    cub = build_cubature_volume_mesh(nodes, ncub, rule=rule)  # also repairs the nodal metrics, as the reference does
     gauss = build_gauss_face_nodes(nodes, ngauss)
     ctx = nodes.get_DGContext()
     K = ctx.K
@@ -78,7 +97,10 @@ def main():
     out = {}
     g, f = 9.81 * 1e-3, 7.8825e-5  # reduced gravity and Coriolis parameter of sw2d_curved.py:20-26,158
     for name, (nx, ny, N, ncub, ngauss) in CASES.items():
-        nodes, ctx, cub, gauss, curved = build_case(nx, ny, N, ncub, ngauss)
+        rule = reference_table_rule(ncub) if name in TABLE_RULE_CASES else None
+        if rule is not None:
+            out[name + "_rule"] = rule
+        nodes, ctx, cub, gauss, curved = build_case(nx, ny, N, ncub, ngauss, rule=rule)
         H, h, hu, hv, hN, zx, zy, CD = state(ctx)
         R = sw2dComputeRHS_curved(h.copy(), hu.copy(), hv.copy(), hN.copy(), zx, zy, g, H, f, CD, py_view(ctx), cub, gauss,
                                   curved.tolist(), ctx.J, gauss.mapM, gauss.mapP)

@@ -35,7 +35,9 @@ def fixture():
 def case(request, fixture):
     name = request.param
     nx, ny, N, ncub, ng = gen.CASES[name]
-    nodes, ctx, cub, gauss, curved = gen.build_case(nx, ny, N, ncub, ng)
+    rule = fixture[name + "_rule"] if name in gen.TABLE_RULE_CASES else None  # the reference's own tabulated points
+    nodes, ctx, cub, gauss, curved = gen.build_case(nx, ny, N, ncub, ng, rule=rule)
+    assert cub.NumCubaturePoints == (len(rule[0]) if rule is not None else (ncub // 2 + 1) ** 2)
     d = {k: fixture["%s_%s" % (name, k)] for k in ("H", "h", "hu", "hv", "hN", "zx", "zy", "CD", "curved")}
     d["g"], d["f"] = (float(x) for x in fixture[name + "_params"][5:7])
     d["R"] = [fixture["%s_RHS%d" % (name, i + 1)] for i in range(4)]
