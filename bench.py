@@ -303,6 +303,38 @@ def cpu_reference(args, world, threads, budget_s, steps=1, warmup=0, max_element
     return dsu, sec, sample, n_stage, t_setup, threads
 
 
+def verbatim_reference_rate(args):
+    """Courtesy figure beside the reference arm: the reference's OWN computeRHS, compiled verbatim from /root/reference behind the
+    blitz stand-in (oracle/_ref/libsw2d_ref.so, oracle/make_ref.py), against the oracle port on the same slab, one thread each,
+    RHS evaluations only.  Says which of the two is the faster CPU code (the arm times the port); None where the library or the
+    case (quads / full physics need more set-up than a courtesy figure is worth) is absent."""
+    try:
+        from oracle import ref_binding
+
+        if args.shape != "tri" or args.mode == "full" or not ref_binding.available():
+            return None
+        from blitzdg_b200.initial_conditions import gaussian_hump
+        from blitzdg_b200.synthetic import provision, structured_mesh
+        from oracle.binding import Oracle
+
+        rows = max(4, 50_000 // (2 * args.nx))
+        ctx = provision(structured_mesh("tri", args.nx, rows), args.order).get_DGContext()
+        H, h, hu, hv = gaussian_hump(ctx.x, ctx.y)
+        ref, orc = ref_binding.CompiledReference(ctx), Oracle(ctx, CFL=0.65, lf_mode=0, sources=0)
+        out = {}
+        for name, f in (("verbatim", lambda: ref.rhs_simple(h, hu, hv)), ("port", lambda: orc.rhs(h, hu, hv))):
+            f()
+            t0 = time.perf_counter()
+            for _ in range(3):
+                f()
+            out[name] = 3.0 * ctx.Np * ctx.K / ((time.perf_counter() - t0) / 3)
+        return {"verbatim_rhs_per_s": out["verbatim"], "port_rhs_per_s": out["port"], "unit": "DOF RHS evaluations/s", "cores": 1,
+                "sample": "3 RHS evaluations each on a %d x %d-cell slab (%d triangles, N=%d) of the arm's mesh; verbatim = the reference's "
+                          "sw2d-simple computeRHS compiled from /root/reference behind oracle/blitz_shim (not blitz++ itself)" % (args.nx, rows, ctx.K, args.order)}
+    except Exception as e:  # a courtesy figure never costs the arm its line
+        return {"unavailable": repr(e)[:200]}
+
+
 def run_reference(args):
     rank, world, _ = dist_env()
     if rank != 0:
@@ -316,7 +348,7 @@ def run_reference(args):
         "scaling": scaling_kind(args), "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": workload_config(args, world, None, None),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": used, "kind": "port", "sample": sample, "stages_per_step": n_stage,
-                         "host_setup_s": t_setup},
+                         "host_setup_s": t_setup, "verbatim_reference": verbatim_reference_rate(args)},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
