@@ -100,6 +100,8 @@ BDG_BINOP(AddExpr, +)
 BDG_BINOP(SubExpr, -)
 BDG_BINOP(MulExpr, *)
 BDG_BINOP(DivExpr, /)
+BDG_BINOP(LtExpr, <)  // comparisons give 0 / 1 per element (zf = (abs(r) < 1.0-1e-10), src/TriangleNodesProvisioner.cpp:637)
+BDG_BINOP(GtExpr, >)
 #undef BDG_BINOP
 
 template <typename E>
@@ -207,6 +209,8 @@ BDG_OPS(AddExpr, +)
 BDG_OPS(SubExpr, -)
 BDG_OPS(MulExpr, *)
 BDG_OPS(DivExpr, /)
+BDG_OPS(LtExpr, <)
+BDG_OPS(GtExpr, >)
 #undef BDG_OPS
 template <typename E>
 typename std::enable_if<is_et<E>::value, NegExpr<E>>::type operator-(const E &e) { return NegExpr<E>(e); }
