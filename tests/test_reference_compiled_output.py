@@ -126,3 +126,39 @@ def test_quad_output_path_follows_the_reference_as_executed(ref, coarse_quads_me
     # nodal values, not resampled ones: every emitted corner value is one of the element's nodal values
     k = 0
     assert np.abs(np.sort(np.unique(np.round(want[2][:, :N * N], 12))) - np.sort(np.unique(np.round(f[:, k], 12)))).max() < 1e-11
+
+
+def test_csv_outputter_writes_the_bytes_the_reference_writes(ref, tmp_path):
+    """src/CsvOutputter.cpp compiled as it stands: file names and file contents, byte for byte (ostream's default
+    formatting of a double -- six significant digits, %g -- including exponents, negative zero, inf and nan)."""
+    from blitzdg_b200.outputters import CsvOutputter
+
+    if not hasattr(ref, "ref_csv_write_field"):
+        pytest.skip("prebuilt library predates the CsvOutputter entry points")
+    rng = np.random.default_rng(5)
+    F = rng.standard_normal((7, 13)) * 10.0 ** rng.integers(-12, 12, size=(7, 13))
+    F[0, :6] = [0.0, -0.0, 1.0, -1.0, 123456.0, 1234567.0]
+    F[1, :6] = [1e-5, 1e-4, 0.1 + 0.2, 1e100, -1e-300, 5e-324]
+    F[2, :3] = [np.inf, -np.inf, np.nan]
+    F[3, :4] = [999999.5, 99999.95, 0.000123456789, 2.5]
+    F = np.ascontiguousarray(F)
+    mine = CsvOutputter(str(tmp_path))
+    for delim in (" ", ","):
+        want = tmp_path / ("ref_%d.dat" % ord(delim))
+        ref.ref_csv_write_field(str(want).encode(), _p(F), F.shape[0], F.shape[1], C.c_char(delim.encode()))
+        mine.writeFieldToFile("mine.dat", F, delim)
+        assert (tmp_path / "mine.dat").read_bytes() == want.read_bytes()
+    buf = C.create_string_buffer(64)
+    for name, num in (("h", 7), ("eta", 0), ("hu", 1234567), ("v", 12345678)):
+        ref.ref_csv_file_name(name.encode(), num, buf, 64)
+        assert mine.generateFileName(name, num) == buf.value.decode()
+    # writeFieldsToFiles: one file per field under the generated name, space-delimited
+    cwd = os.getcwd()
+    os.makedirs(tmp_path / "r")
+    try:
+        os.chdir(tmp_path / "r")
+        ref.ref_csv_write_fields(b"h", _p(F), F.shape[0], F.shape[1], 42)
+    finally:
+        os.chdir(cwd)
+    mine.writeFieldsToFiles({"h": F}, 42)
+    assert (tmp_path / "h0000042.dat").read_bytes() == (tmp_path / "r" / "h0000042.dat").read_bytes()
