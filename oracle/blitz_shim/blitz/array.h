@@ -102,6 +102,7 @@ BDG_BINOP(MulExpr, *)
 BDG_BINOP(DivExpr, /)
 BDG_BINOP(LtExpr, <)  // comparisons give 0 / 1 per element (zf = (abs(r) < 1.0-1e-10), src/TriangleNodesProvisioner.cpp:637)
 BDG_BINOP(GtExpr, >)
+BDG_BINOP(ModExpr, %)  // integer arrays only (f1 = (f1 % NumFaces), src/MeshManager.cpp:465)
 #undef BDG_BINOP
 
 template <typename E>
@@ -118,6 +119,14 @@ struct SqrtExpr : ETBase<SqrtExpr<E>> {
   E e;
   explicit SqrtExpr(const E &x) : e(x) {}
   double eval(const int *idx) const { return std::sqrt(e.eval(idx)); }
+  Shape shape() const { return e.shape(); }
+};
+template <typename E>
+struct FloorExpr : ETBase<FloorExpr<E>> {  // floor(expr), element by element (of an integer quotient it is the identity)
+  typedef double value_type;
+  E e;
+  explicit FloorExpr(const E &x) : e(x) {}
+  double eval(const int *idx) const { return std::floor((double)e.eval(idx)); }
   Shape shape() const { return e.shape(); }
 };
 template <typename E>
@@ -211,6 +220,7 @@ BDG_OPS(MulExpr, *)
 BDG_OPS(DivExpr, /)
 BDG_OPS(LtExpr, <)
 BDG_OPS(GtExpr, >)
+BDG_OPS(ModExpr, %)
 #undef BDG_OPS
 template <typename E>
 typename std::enable_if<is_et<E>::value, NegExpr<E>>::type operator-(const E &e) { return NegExpr<E>(e); }
@@ -218,6 +228,8 @@ template <typename E>
 typename std::enable_if<is_et<E>::value, SqrtExpr<E>>::type sqrt(const E &e) { return SqrtExpr<E>(e); }
 template <typename E>
 typename std::enable_if<is_et<E>::value, AbsExpr<E>>::type abs(const E &e) { return AbsExpr<E>(e); }
+template <typename E>
+typename std::enable_if<is_et<E>::value, FloorExpr<E>>::type floor(const E &e) { return FloorExpr<E>(e); }
 template <typename E, typename S>
 typename std::enable_if<is_et<E>::value && std::is_arithmetic<S>::value, PowExpr<E>>::type pow(const E &e, S p) { return PowExpr<E>(e, (double)p); }
 template <typename E, int D>

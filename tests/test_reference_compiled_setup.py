@@ -112,3 +112,78 @@ def test_reference_setup_into_reference_rhs_against_mirror_setup(ref, quad, N, c
     Rb = ref_binding.CompiledReference(ctx).rhs_simple(h, hu, hv)
     for a, b in zip(Ra, Rb):
         assert np.abs(a - b).max() <= 1e-12 * np.abs(a).max()
+
+
+# ---------------------------------------------------------------------------------------------- mesh tables (MeshManager)
+def _raw_mesh(shape, nx, ny, seed, clockwise_fraction=0.0):
+    from blitzdg_b200.synthetic import shuffle_numbering, structured_arrays
+
+    etov, vert = structured_arrays(shape, nx, ny, jitter=0.2)
+    if seed is not None:
+        etov, vert = shuffle_numbering(etov, vert, seed)
+    etov = np.asarray(etov).copy()
+    if clockwise_fraction:
+        flip = np.random.default_rng(1).random(len(etov)) < clockwise_fraction
+        etov[flip] = etov[flip][:, ::-1]  # reversed orientation
+    if vert.shape[1] == 2:
+        vert = np.concatenate([vert, np.zeros((len(vert), 1))], axis=1)
+    return etov, vert
+
+
+@pytest.fixture(scope="module")
+def refmesh():
+    from oracle import ref_mesh_binding as rmb
+
+    if not rmb.available():
+        pytest.skip("compiled reference not built and reference tree not present")
+    return rmb
+
+
+@pytest.mark.parametrize("shape,nx,ny,seed,cw", [("tri", 9, 7, None, 0.0), ("tri", 30, 20, 3, 0.3), ("tri", 64, 48, 9, 0.5),
+                                                 ("quad", 8, 5, None, 0.0), ("quad", 25, 18, 11, 0.0)])
+def test_mesh_tables_match_the_compiled_reference(refmesh, shape, nx, ny, seed, cw):
+    """EToV after the counter-clockwise repair, EToE / EToF from the reference's sparse face-to-face product
+    (src/MeshManager.cpp:383-489), BCType from buildBCTable(Wall): the mirror's sort-based tables are the same integers, on
+    structured, randomly renumbered and partly clockwise input."""
+    from blitzdg_b200 import MeshManager
+
+    etov, vert = _raw_mesh(shape, nx, ny, seed, cw)
+    m = MeshManager()
+    m.buildMesh(etov, vert)
+    K, Nf = etov.shape
+    for mine, want in zip((m.get_Elements(), m.get_EToE(), m.get_EToF(), m.get_BCType()), refmesh.mesh_tables(etov, vert, tag=3)):
+        assert np.array_equal(np.asarray(mine).reshape(K, Nf), want)
+    if cw:
+        assert not np.array_equal(np.asarray(m.get_Elements()).reshape(K, Nf), etov)  # the repair did something
+
+
+def test_gmsh_files_of_the_reference_give_the_reference_tables(refmesh, coarse_box_mesh, coarse_quads_mesh):
+    """The parser is the mirror's (the reference's needs boost); everything after it is the reference's code."""
+    for mesh in (coarse_box_mesh, coarse_quads_mesh):
+        K, Nf = mesh.get_NumElements(), mesh.get_NumFaces()
+        etov = np.asarray(mesh.get_Elements()).reshape(K, Nf)
+        vert = np.asarray(mesh.get_Vertices()).reshape(-1, 3)
+        want = refmesh.mesh_tables(etov, vert, tag=3)
+        for mine, w in zip((mesh.get_Elements(), mesh.get_EToE(), mesh.get_EToF(), mesh.get_BCType()), want):
+            assert np.array_equal(np.asarray(mine).reshape(K, Nf), w)
+
+
+def test_clockwise_quads_are_the_one_documented_deviation(refmesh):
+    """the reference swaps local vertices 1 and 2 of a clockwise element whatever its type
+    (src/MeshManager.cpp:292-306), which makes a bow-tie of a quad; the mirror reverses the orientation (1 <-> 3)."""
+    from blitzdg_b200 import MeshManager
+
+    etov, vert = _raw_mesh("quad", 4, 3, None, 1.0)
+    m = MeshManager()
+    m.buildMesh(etov, vert)
+    mine = np.asarray(m.get_Elements()).reshape(etov.shape)
+    want = refmesh.mesh_tables(etov, vert, tag=3)[0]
+    assert np.array_equal(want, etov[:, [0, 2, 1, 3]]) and np.array_equal(mine, etov[:, [0, 3, 2, 1]])
+
+    def signed_area(e):
+        x, y = vert[e, 0], vert[e, 1]
+        return 0.5 * (x * np.roll(y, -1, axis=1) - np.roll(x, -1, axis=1) * y).sum(axis=1)
+
+    cell = signed_area(mine)
+    assert (cell > 0).all()                                    # the mirror's elements are valid counter-clockwise quads
+    assert (np.abs(signed_area(want)) < 0.2 * cell).all()      # the reference's are self-intersecting: the two lobes cancel
