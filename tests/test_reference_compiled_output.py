@@ -162,3 +162,52 @@ def test_csv_outputter_writes_the_bytes_the_reference_writes(ref, tmp_path):
         os.chdir(cwd)
     mine.writeFieldsToFiles({"h": F}, 42)
     assert (tmp_path / "h0000042.dat").read_bytes() == (tmp_path / "r" / "h0000042.dat").read_bytes()
+
+
+def _read_record(path):
+    """The flat record the recording VTK stand-in writes (oracle/ref_stub/vtk-7.1/vtk_recording.h)."""
+    raw = open(path, "rb").read()
+    npts, ncell, nconn, nlen = np.frombuffer(raw[:32], dtype="<i8")
+    pos, out = 32, {}
+    for name, dt, n in (("xyz", "<f8", 3 * npts), ("scalars", "<f8", npts), ("types", "<i8", ncell), ("offsets", "<i8", ncell), ("conn", "<i8", nconn)):
+        out[name] = np.frombuffer(raw[pos:pos + 8 * n], dtype=dt)
+        pos += 8 * n
+    out["name"] = raw[pos:pos + nlen].decode()
+    assert pos + nlen == len(raw)
+    return out
+
+
+@pytest.mark.parametrize("quad,N", [(False, 1), (False, 2), (False, 4), (True, 1), (True, 3)])
+def test_vtk_outputter_hands_vtk_what_the_mirror_writes(ref, quad, N, coarse_box_mesh, coarse_quads_mesh, tmp_path):
+    """include/VtkOutputter.hpp (writeFieldToFile, insertAllCells) and src/VtkOutputter.cpp (constructor, generateFileName,
+    writeFieldsToFiles) compiled over recording VTK stand-ins: the points, point scalars, cell types, connectivity (the quad
+    node swap included), active-scalars name and file name the reference hands to VTK are what the mirror's .vtu holds."""
+    from blitzdg_b200 import QuadNodesProvisioner, TriangleNodesProvisioner
+    from blitzdg_b200.outputters import VtkOutputter, read_vtu
+
+    if not hasattr(ref, "ref_vtk_write_fields"):
+        pytest.skip("prebuilt library predates the VtkOutputter entry points")
+    P = (QuadNodesProvisioner if quad else TriangleNodesProvisioner)(N, coarse_quads_mesh if quad else coarse_box_mesh)
+    x, y = np.ascontiguousarray(P.xGrid), np.ascontiguousarray(P.yGrid)
+    f = np.ascontiguousarray(np.exp(-3 * x * x - 2 * y * y) + 0.2 * x * y)
+    Vinv = np.ascontiguousarray(P.Vinv)
+    name = C.create_string_buffer(64)
+    cwd = os.getcwd()
+    os.makedirs(tmp_path / "r")
+    try:
+        os.chdir(tmp_path / "r")
+        ref.ref_vtk_write_fields(N, P.NumElements, int(quad), _p(Vinv), _p(x), _p(y), b"eta", _p(f), 120, name, 64)
+    finally:
+        os.chdir(cwd)
+    mine = VtkOutputter(P, str(tmp_path))
+    assert mine.generateFileName("eta", 120) == name.value.decode() == "eta0000120.vtu"
+    mine.writeFieldsToFiles({"eta": f}, 120)
+    got, want = read_vtu(str(tmp_path / "eta0000120.vtu")), _read_record(tmp_path / "r" / "eta0000120.vtu")
+    nc = 4 if quad else 3
+    ncell = P.NumElements * (N * N if N > 1 else 1)
+    assert got["ncells"] == ncell == len(want["types"]) and got["npoints"] == nc * ncell == len(want["scalars"])
+    assert got["scalars"] == want["name"] == "eta"
+    assert np.array_equal(got["arrays"]["types"].astype(np.int64), want["types"]) and set(want["types"]) == {9 if quad else 5}
+    assert np.array_equal(got["arrays"]["connectivity"], want["conn"]) and np.array_equal(got["arrays"]["offsets"], want["offsets"])
+    assert np.abs(got["arrays"]["Points"].reshape(-1) - want["xyz"]).max() <= 1e-13
+    assert np.abs(got["arrays"]["eta"] - want["scalars"]).max() <= 1e-13 * np.abs(want["scalars"]).max()
