@@ -105,7 +105,11 @@ def pack_curved(ctx, cub, gauss, curvedEls, J=None, gmapM=None, gmapP=None):
 
 
 def pack_context(ctx):
-    """DGContext2D -> (bdg_dgcontext2d, keepalive list).  Arrays are made C-contiguous float64/int32."""
+    """DGContext2D -> (bdg_dgcontext2d, keepalive list).  Arrays are made C-contiguous float64/int32.  Also accepts a context
+    with the property names of the reference's Python binding (pyblitzdg), see dgcontext.as_context."""
+    from .dgcontext import as_context
+
+    ctx = as_context(ctx)
     keep = []
 
     def dd(a):

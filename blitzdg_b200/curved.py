@@ -64,6 +64,10 @@ class GaussFaceContext2D:
     mapM: np.ndarray = None    # [3*NGauss*K] int32, g + 3*NGauss*k
     mapP: np.ndarray = None
 
+    @property
+    def J(self):  # the name pyblitzdg gives it (src/pyblitzdg/pyblitzdg.cpp:130)
+        return self.Jac
+
 
 def triangle_cubature(order):
     """Points (r, s) and weights on the reference triangle {r, s >= -1, r + s <= 0} (area 2), exact for polynomials of

@@ -45,7 +45,10 @@ class SW2dSolver:
 
     def __init__(self, ctx, phys=None, num=None, mode="simple", lf_mode=None, sources=None, use_filter=False,
                  halo=None, device=0, variant=0):
+        from .dgcontext import as_context
+
         self.lib = capi.load()
+        ctx = as_context(ctx)  # a pyblitzdg-style context (property names of the reference's Python binding) is converted here
         self.ctx = ctx
         self.phys = phys or physParams()
         self.num = num or numParams(N=ctx.N)
