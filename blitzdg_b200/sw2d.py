@@ -293,6 +293,9 @@ def readDepthData(depthFile, Np, K):
 
 def bedSlopes(ctx, H):
     """Hx, Hy of the driver (src/sw2d/main.cpp:129-133): filtered nodal gradient of H."""
+    from .dgcontext import as_context
+
+    ctx = as_context(ctx)
     dr, ds = ctx.Dr @ H, ctx.Ds @ H
     Hx, Hy = ctx.rx * dr + ctx.sx * ds, ctx.ry * dr + ctx.sy * ds
     if getattr(ctx, "Filt", None) is not None:
@@ -307,7 +310,9 @@ def buildSpongeCoeff(ctx, spongeStrength, radInfl, x=None, y=None):
     from scipy.spatial import cKDTree
 
     from .bctypes import BCTag
+    from .dgcontext import as_context
 
+    ctx = as_context(ctx)
     x = ctx.x if x is None else x
     y = ctx.y if y is None else y
     Np, K = x.shape
