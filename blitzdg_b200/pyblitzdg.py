@@ -14,6 +14,8 @@ replaces its RHS / time loop by the device path:
                                 gather, scatter, J, rx, ry, sx, sy, nx, ny, Dr, Ds, Lift, vmapM, vmapP, BCmap, V  (:160-187)
     GaussFaceContext2D / CubatureContext2D   the dataclasses of blitzdg_b200.curved (same property names, :124-158)
     VtkOutputter                (nodes); writeFieldToFile, writeFieldsToFiles                                    (:189-192)
+    VandermondeBuilder          buildVandermondeMatrix(r, includeInverse, order) -> (V, Vinv) or (V,)            (:92-93)
+    LSERK4                      numStages, rk4a, rk4b;   BCType.Wall / Dirichlet / Neuman                        (:79-99)
 
 Like the reference's accessors (src/DGContext2D.cpp:24-176), every array property returns a fresh copy.  A DGContext2D of
 this module goes straight into blitzdg_b200.sw2d.SW2dSolver (dgcontext.as_context).  `from pyblitzdg import pyblitzdg as dg`
@@ -152,3 +154,44 @@ class QuadNodesProvisioner(_Provisioner2D, _QuadNodesProvisioner):
 class VtkOutputter(_VtkOutputter):
     def __init__(self, nodesProvisioner, directory=".", fmt="binary"):
         super().__init__(nodesProvisioner, directory, fmt)
+
+
+class VandermondeBuilder:
+    """VandermondeBuilders::buildVandermondeMatrix_numpy (include/VandermondeBuilders.hpp:76-104): the 1-D orthonormal Legendre
+    Vandermonde matrix V [len(r)][order + 1] (order = -1: square) and, on request, its inverse; returned as a tuple."""
+
+    def buildVandermondeMatrix(self, r, includeInverse=True, order=-1):
+        from . import lapack
+        from .jacobi import vandermonde_1d
+
+        r = np.ascontiguousarray(r, dtype=np.float64).reshape(-1)
+        V = np.ascontiguousarray(vandermonde_1d(r, ncols=None if order < 0 else int(order) + 1))
+        if not includeInverse:
+            return (V,)
+        return V, lapack.inverse(V)
+
+
+class _LSERK4:
+    numStages = 5
+
+    @property
+    def rk4a(self):
+        from . import lserk4
+
+        return [float(a) for a in lserk4.rk4a]
+
+    @property
+    def rk4b(self):
+        from . import lserk4
+
+        return [float(b) for b in lserk4.rk4b]
+
+
+LSERK4 = _LSERK4()
+
+
+class _BCType:  # struct BCType of src/pyblitzdg/pyblitzdg.cpp:52-56, injected into the module as an instance
+    Dirichlet, Neuman, Wall = 6, 7, 3
+
+
+BCType = _BCType()

@@ -8,11 +8,15 @@ name bound to blitzdg_b200.pyblitzdg -- every set-up line, the driver's own nump
     same loop around the C oracle, the .vtu files it wrote;
   * sw2d.py (triangles, N = 6, input/R_8km_circle.msh, Coriolis + tracer): 200 steps (the fewest its output arithmetic
     allows), conservation of mass and tracer, the .vtu files;
+  * sw2d_curved.py (curved-element workflow: correctBCTable + setBCType, boundary splines, meshhelpers/curved.py, setCoordinates,
+    buildGaussFaceNodes, makeMapsPeriodic, buildCubatureVolumeMesh, filtered midpoint loop around sw2dComputeRHS_curved) on a
+    channel mesh written here in gmsh 2.2 format (the reference does not ship input/headlands_highres.msh): three steps,
+    periodic maps, conservation, outputs, and its state through the C-ABI marshalling;
   * sw2dComputeRHS_curved (swhelpers/rhs.py:6-176) with the contexts of nodes.dgContext() / buildCubatureVolumeMesh /
     buildGaussFaceNodes handed over as they are -- the stored outputs of tests/golden/curved_reference_rhs.npz were generated
     through an adapter object; here there is none.
 
-What is changed in a script: the literal assigned to `finalTime` (40 s / 3 days of model time), and `np` is numpy with the two
+What is changed in a script: the literal assigned to `finalTime` (40 s / 3 days / 1 day of model time), and `np` is numpy with the two
 NumPy-1.x aliases the scripts use (`np.float`, `np.dtype('Float64')`); matplotlib (absent, imported and never used on these
 paths) is an empty module.  Skipped where /root/reference is absent (the GPU box).  The last test needs no reference: a
 pyblitzdg-style context goes into the C-ABI structure unchanged.
@@ -69,7 +73,10 @@ def run_reference_script(name, final_time_expr, cwd, extra=None):
         os.symlink(os.path.join(REF, "input"), os.path.join(cwd, "input"))
     ns = {"__name__": "__main__", "__file__": path}
     ns.update(extra or {})
+    had_float = hasattr(np, "float")
     try:
+        if not had_float:
+            np.float = np.float64  # the modules a script imports (swhelpers/rhs.py:101) see the real numpy: NumPy 1.x alias
         os.chdir(cwd)
         sys.path.insert(0, REF)
         for node in tree.body:  # statement by statement: `np` is re-bound to the compat module right after the script imports numpy
@@ -79,6 +86,8 @@ def run_reference_script(name, final_time_expr, cwd, extra=None):
     finally:
         os.chdir(old_cwd)
         sys.path[:] = old_path
+        if not had_float and hasattr(np, "float"):
+            del np.float
         for k, v in saved.items():
             if v is None:
                 sys.modules.pop(k, None)
@@ -230,3 +239,58 @@ def test_pyblitzdg_style_context_packs_like_the_mirror_context(coarse_box_mesh):
     bt[bt == 3] = 2
     m.setBCType(bt)
     assert sorted(dg.TriangleNodesProvisioner(2, m).dgContext().BCmap) == [2]
+
+
+def _write_channel_msh(path, nx=16, ny=4, Lx=8000.0, Ly=1000.0):
+    """A gmsh 2.2 ASCII file of a structured triangle mesh of [0, Lx] x [0, Ly]: stands in for input/headlands_highres.msh,
+    which the reference does not ship.  The driver's geometry tests (a wall curve with y > 200 between x = 3250 and 4750,
+    periodic Out ends more than 1000 apart, a node within 19 of the origin) are met by this channel."""
+    xs, ys = np.linspace(0.0, Lx, nx + 1), np.linspace(0.0, Ly, ny + 1)
+    vid = lambda i, j: j * (nx + 1) + i + 1  # noqa: E731  (1-based)
+    with open(path, "w") as fh:
+        fh.write("$MeshFormat\n2.2 0 8\n$EndMeshFormat\n$Nodes\n%d\n" % ((nx + 1) * (ny + 1)))
+        for j in range(ny + 1):
+            for i in range(nx + 1):
+                fh.write("%d %.17g %.17g 0\n" % (vid(i, j), xs[i], ys[j]))
+        fh.write("$EndNodes\n$Elements\n%d\n" % (2 * nx * ny))
+        e = 1
+        for j in range(ny):
+            for i in range(nx):
+                a, b, c, d = vid(i, j), vid(i + 1, j), vid(i + 1, j + 1), vid(i, j + 1)
+                fh.write("%d 2 2 0 1 %d %d %d\n%d 2 2 0 1 %d %d %d\n" % (e, a, b, c, e + 1, a, c, d))
+                e += 2
+        fh.write("$EndElements\n")
+
+
+@needs_ref
+def test_sw2d_curved_driver_runs_unmodified_on_a_channel_mesh(tmp_path):
+    """sw2d_curved.py from its first line to its time loop: correctBCTable + setBCType, the boundary curve and its splines,
+    meshhelpers/curved.py (VandermondeBuilder, Fmask, r, s), setCoordinates, buildGaussFaceNodes, makeMapsPeriodic on the nodal
+    AND the Gauss maps, buildCubatureVolumeMesh, the drag field, three steps of the filtered midpoint loop around
+    sw2dComputeRHS_curved, the .vtu files of step 0.  Then the driver's own state goes through the C-ABI marshalling
+    (pack_curved) with its periodic Gauss maps."""
+    from blitzdg_b200 import capi
+    from blitzdg_b200.dgcontext import as_context
+    from blitzdg_b200.outputters import read_vtu
+
+    os.makedirs(tmp_path / "input")
+    _write_channel_msh(str(tmp_path / "input" / "headlands_highres.msh"))
+    ns = run_reference_script("sw2d_curved.py", "40.0", str(tmp_path))  # dt = 16.8 on this mesh: three steps
+    assert ns["step"] == 3 and 40.0 < ns["t"] < 60.0 and 10.0 < ns["dt"] < 20.0
+    ctx, cub, gauss = ns["ctx"], ns["cub_ctx"], ns["gauss_ctx"]
+    assert (ctx.numLocalPoints, ctx.numElements) == (15, 128) and sorted(ctx.BCmap) == [2, 3]
+    assert cub.NumCubaturePoints == 64 and gauss.NGauss == 10 and len(ns["curvedEls"]) > 0
+    # periodic ends: every Out node found its partner on the other end, nodal and Gauss maps alike
+    for mM, mP, ids, xf in ((ns["vmapM"], ns["vmapP"], ctx.BCmap[2], ns["xFlat"]), (ns["gmapM"], ns["gmapP"], gauss.BCmap[2], ns["gxFlat"])):
+        ids = np.asarray(ids)
+        assert (np.abs(xf[mM[ids]] - xf[mP[ids]]) > 7999.0).all()
+    # the scheme conserves mass and tracer in the periodic, walled channel; the state moved
+    w = cub.W
+    mass0 = float((w * (cub.V @ (ns["H"] + ns["amp"] * np.exp(-((ns["y"] - ns["L"]) / ns["W"]) ** 2)))).sum())
+    assert abs(float((w * (cub.V @ ns["h"])).sum()) - mass0) <= 1e-11 * mass0
+    assert np.isfinite(ns["hu"]).all() and np.abs(ns["hv"]).max() > 0
+    for f in ("eta", "u", "v", "B", "h", "vort"):
+        assert read_vtu(str(tmp_path / ("%s0000000.vtu" % f)))["ncells"] == 128 * 16
+    # what the driver holds goes into the C ABI as it is
+    c, keep = capi.pack_curved(as_context(ctx), cub, gauss, ns["curvedEls"], ns["J"], ns["gmapM"], ns["gmapP"])
+    assert (c.Ncub, c.NGauss, c.n_curved) == (64, 10, len(ns["curvedEls"]))
