@@ -291,6 +291,22 @@ def test_sw2d_curved_driver_runs_unmodified_on_a_channel_mesh(tmp_path):
     assert np.isfinite(ns["hu"]).all() and np.abs(ns["hv"]).max() > 0
     for f in ("eta", "u", "v", "B", "h", "vort"):
         assert read_vtu(str(tmp_path / ("%s0000000.vtu" % f)))["ncells"] == 128 * 16
+    # the oracle the CUDA kernel is held to, on the driver's own end state with its periodic maps, Out faces and nodal drag
+    from oracle.curved_numpy import rhs_curved
+
+    args = (ns["h"], ns["hu"], ns["hv"], ns["hN"], ns["zx"], ns["zy"], ns["g"])
+    had_float = hasattr(np, "float")
+    try:
+        if not had_float:
+            np.float = np.float64  # swhelpers/rhs.py:99-101 (NumPy 1.x alias)
+        Rd = ns["sw2dComputeRHS_curved"](*[a.copy() if hasattr(a, "copy") else a for a in args], ns["H"], ns["f"], ns["CD"], ctx, cub, gauss, ns["curvedEls"],
+                                         ns["J"], ns["gmapM"], ns["gmapP"])
+    finally:
+        if not had_float and hasattr(np, "float"):
+            del np.float
+    Ro = rhs_curved(*args, ns["f"], ns["CD"], as_context(ctx), cub, gauss, ns["curvedEls"], ns["J"], ns["gmapM"], ns["gmapP"])
+    for i in range(4):  # the jet is in geostrophic balance: RHS2 is what is left of terms 1e3 times larger, hence 1e-11 and not 1e-12
+        assert np.abs(Ro[i] - Rd[i]).max() <= 1e-11 * np.abs(Rd[i]).max(), i
     # what the driver holds goes into the C ABI as it is
     c, keep = capi.pack_curved(as_context(ctx), cub, gauss, ns["curvedEls"], ns["J"], ns["gmapM"], ns["gmapP"])
     assert (c.Ncub, c.NGauss, c.n_curved) == (64, 10, len(ns["curvedEls"]))
