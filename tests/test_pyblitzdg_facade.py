@@ -157,6 +157,16 @@ def test_sw2d_driver_with_coriolis_and_tracer_runs_unmodified(tmp_path):
     assert abs(integral(ns["h"]) - integral(H + eta0)) <= 1e-12 * integral(H)
     assert abs(integral(ns["hN"]) - integral((H + eta0) * N0)) <= 1e-12 * integral(H)
     assert np.isfinite(ns["h"]).all() and np.abs(ns["hu"]).max() > 1e-3 and np.abs(ns["h"] - (H + eta0)).max() > 1e-6
+    # the driver's own RHS (sw2d.py:30-146: per-face LF, Coriolis, tracer) on its end state against the C oracle the CUDA path is held to
+    from blitzdg_b200.dgcontext import as_context
+    from oracle.binding import Oracle
+
+    orc = Oracle(as_context(c), lf_mode=0, sources=1, g=ns["g"], CD=0.0, f=ns["f"])
+    orc.set_bathymetry(H, np.zeros_like(H), np.zeros_like(H))
+    Rd = ns["sw2dComputeRHS"](ns["h"], ns["hu"], ns["hv"], ns["hN"], ns["g"], H, ns["f"], c)
+    Ro = orc.rhs(ns["h"], ns["hu"], ns["hv"]) + [orc.rhs_tracer(ns["h"], ns["hu"], ns["hv"], ns["hN"])]
+    for i in range(4):
+        assert np.abs(Ro[i] - Rd[i]).max() <= 1e-11 * np.abs(Rd[i]).max(), i
     for stepno in (0, 1, 200):
         for f in ("eta", "u", "v", "N"):
             got = read_vtu(str(tmp_path / ("%s%07d.vtu" % (f, stepno))))
